@@ -1,0 +1,356 @@
+/*
+ * terra_b200.h — C ABI of the B200-native Terra hot path.
+ *
+ * This header is the drop-in boundary.  Every type below has the same name, field order and
+ * x86-64 layout as the corresponding type of the reference's public headers, and every
+ * `terra_*` function has the reference's signature, so a caller compiled against the
+ * reference's include/Terra.h + include/TerraPresets.h links against libterra_b200.so
+ * unchanged.  Layouts are pinned by the _Static_asserts at the end of the file (sizes/offsets
+ * measured on the reference).
+ *
+ * Reference interface each group replaces (paths relative to the reference checkout):
+ *   math PODs ............ include/TerraMath.h:20-38
+ *   shading types ........ include/Terra.h:36-99
+ *   scene types .......... include/Terra.h:104-198
+ *   scene API ............ include/Terra.h:205-211   (src/Terra.c:130-282)
+ *   framebuffer API ...... include/Terra.h:213-215   (src/Terra.c:309-345)
+ *   texture API .......... include/Terra.h:217-223   (src/Terra.c:350-507)
+ *   attribute API ........ include/Terra.h:225-227   (src/Terra.c:287-304)
+ *   terra_render ......... include/Terra.h:229       (src/Terra.c:512-635)  <- the hot path
+ *   system API ........... include/Terra.h:237-245   (src/Terra.c:640-663)
+ *   BSDF presets ......... include/TerraPresets.h:11-27 (src/TerraPresets.c:34-146)
+ *
+ * What differs from the reference, by design:
+ *   - terra_render() runs on the GPU (sm_100a wavefront kernels).  There is no CPU fallback:
+ *     without a CUDA device the call logs through terra_log() and abort()s.
+ *   - Materials are host function-pointer tables in the reference.  A GPU cannot call them,
+ *     so terra_scene_commit() classifies each TerraBSDF / TerraAttribute by POINTER IDENTITY
+ *     against this library's own exported presets (terra_bsdf_*_init, terra_texture_sample,
+ *     terra_texture_sample_latlong).  An unknown pointer is a hard error.
+ *   - terra_bsdf_ggx_init / terra_bsdf_glass_init are additive: the reference only carries
+ *     those two presets as dead code (src/TerraPresets.c:298-465).
+ *   - Everything prefixed terra_b200_ is an extension (device selection, the traversal
+ *     micro-benchmark entry points, device-pointer variants for multi-GPU, statistics).
+ */
+#ifndef TERRA_B200_H
+#define TERRA_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ math PODs ---------- */
+typedef struct TerraInt4     { int   x, y, z, w; } TerraInt4;
+typedef struct TerraFloat2   { float x, y;       } TerraFloat2;
+typedef struct TerraFloat3   { float x, y, z;    } TerraFloat3;
+typedef struct TerraFloat4   { float x, y, z, w; } TerraFloat4;
+typedef struct TerraFloat4x4 { TerraFloat4 rows[4]; } TerraFloat4x4;   /* row-major, M*v */
+
+/* The reference's constants, verbatim (include/TerraMath.h:17-18).  terra_PI is NOT pi. */
+#define terra_PI       3.1416926535f
+#define terra_Epsilon  1e-4
+#define terra_ior_air  1.f
+
+/* ------------------------------------------------------------------ shading ------------ */
+#ifndef TERRA_MATERIAL_MAX_ATTRIBUTES
+#define TERRA_MATERIAL_MAX_ATTRIBUTES 8
+#endif
+
+/* Surface record handed to the BSDF callbacks (reference: 188 bytes). */
+typedef struct {
+    TerraFloat4x4 transform;   /* tangent | normal | bitangent as COLUMNS (TerraMath.inl:251-272) */
+    TerraFloat3   normal;
+    TerraFloat3   emissive;
+    float         ior;         /* never written by the reference */
+    TerraFloat3   attributes[TERRA_MATERIAL_MAX_ATTRIBUTES];
+} TerraShadingSurface;
+
+typedef TerraFloat3 (TerraBSDFSampleRoutine)(const TerraShadingSurface* surface,
+                                             float e1, float e2, float e3, const TerraFloat3* wo);
+typedef float       (TerraBSDFPdfRoutine)   (const TerraShadingSurface* surface,
+                                             const TerraFloat3* wi, const TerraFloat3* wo);
+typedef TerraFloat3 (TerraBSDFEvalRoutine)  (const TerraShadingSurface* surface,
+                                             const TerraFloat3* wi, const TerraFloat3* wo);
+
+typedef struct {
+    TerraBSDFSampleRoutine* sample;
+    TerraBSDFPdfRoutine*    pdf;
+    TerraBSDFEvalRoutine*   eval;
+} TerraBSDF;
+
+typedef enum {
+    kTerraFilterPoint,
+    kTerraFilterBilinear,
+    kTerraFilterTrilinear,     /* returns black in the reference (Terra.c:452-458) */
+    kTerraFilterAnisotropic    /* idem */
+} TerraFilter;
+
+typedef enum {
+    kTerraTextureAddressWrap,
+    kTerraTextureAddressMirror,
+    kTerraTextureAddressClamp
+} TerraTextureAddressMode;
+
+typedef struct {
+    void*    pixels;           /* NULL = invalid texture */
+    uint16_t width;
+    uint16_t height;
+    uint8_t  components;
+    uint8_t  depth;            /* bytes per component: 1 (u8/255) or 4 (float) */
+    uint8_t  filter;           /* TerraFilter; caller sets it */
+    uint8_t  address_mode;     /* TerraTextureAddressMode; caller sets it */
+} TerraTexture;
+
+typedef void        (*TerraAttributeFinalize)(void* attribute);
+typedef TerraFloat3 (*TerraAttributeEval)(void* attribute, const void* texcoord, const void* world_pos);
+
+typedef struct {
+    void*                  state;     /* NULL => constant `value` (Terra.c:1804-1810) */
+    TerraAttributeFinalize finalize;
+    TerraAttributeEval     eval;
+    TerraFloat3            value;
+} TerraAttribute;
+
+typedef struct {
+    TerraBSDF      bsdf;
+    float          ior;
+    TerraAttribute emissive;
+    TerraAttribute attributes[TERRA_MATERIAL_MAX_ATTRIBUTES];
+    size_t         attributes_count;
+    bool           enable_bump_map_attr;
+    bool           enable_normal_map_attr;
+} TerraMaterial;
+
+/* ------------------------------------------------------------------ scene -------------- */
+typedef struct TerraAABB { TerraFloat3 min, max; } TerraAABB;
+typedef struct { TerraFloat3 a, b, c; } TerraTriangle;
+
+typedef struct {
+    TerraFloat3 normal_a, normal_b, normal_c;
+    TerraFloat2 texcoord_a, texcoord_b, texcoord_c;
+} TerraTriangleProperties;
+
+typedef struct {
+    TerraTriangle*           triangles;        /* owned by the scene, filled in place by the caller */
+    TerraTriangleProperties* properties;
+    size_t                   triangles_count;
+    TerraMaterial            material;
+} TerraObject;
+
+typedef enum {
+    kTerraTonemappingOperatorNone,
+    kTerraTonemappingOperatorLinear,
+    kTerraTonemappingOperatorReinhard,
+    kTerraTonemappingOperatorFilmic,
+    kTerraTonemappingOperatorUncharted2
+} TerraTonemappingOperator;
+
+typedef enum { kTerraAcceleratorBVH } TerraAccelerator;
+
+typedef enum {
+    kTerraSamplingMethodRandom,
+    kTerraSamplingMethodStratified,   /* only changes the spp rounding */
+    kTerraSamplingMethodHalton
+} TerraSamplingMethod;
+
+typedef enum {
+    kTerraIntegratorSimple,
+    kTerraIntegratorDirect,
+    kTerraIntegratorDirectMis,
+    kTerraIntegratorDebugMono,
+    kTerraIntegratorDebugDepth,
+    kTerraIntegratorDebugNormals,
+    kTerraIntegratorDebugMisWeights
+} TerraIntegrator;
+
+typedef struct {
+    TerraAttribute           environment_map;
+    TerraTonemappingOperator tonemapping_operator;
+    TerraAccelerator         accelerator;
+    TerraSamplingMethod      sampling_method;
+    TerraIntegrator          integrator;
+    float                    subpixel_jitter;
+    size_t                   samples_per_pixel;
+    size_t                   bounces;
+    size_t                   strata;
+    float                    manual_exposure;
+    float                    gamma;
+} TerraSceneOptions;
+
+typedef struct {
+    TerraFloat3 position, direction, up;
+    float       fov;           /* degrees */
+} TerraCamera;
+
+typedef struct {
+    TerraFloat3 acc;           /* running radiance sum */
+    int         samples;       /* running sample count */
+} TerraRawIntegrationResult;
+
+typedef struct {
+    TerraFloat3*               pixels;    /* tonemapped, row-major p = i*width + j */
+    TerraRawIntegrationResult* results;   /* accumulates across terra_render calls */
+    size_t                     width;
+    size_t                     height;
+} TerraFramebuffer;
+
+typedef struct {
+    uint32_t object_idx   : 8;            /* <= 256 objects          (TerraBVH.c:155,283-284) */
+    uint32_t triangle_idx : 24;           /* <= 2^23 triangles/object (signed shift) */
+} TerraPrimitiveRef;
+
+typedef void* HTerraScene;
+
+/* ------------------------------------------------------------------ reference API ------ */
+HTerraScene        terra_scene_create(void);
+TerraObject*       terra_scene_add_object(HTerraScene scene, size_t triangle_count);
+size_t             terra_scene_count_objects(HTerraScene scene);
+void               terra_scene_commit(HTerraScene scene);      /* BVH build + flatten + upload */
+void               terra_scene_clear(HTerraScene scene);
+TerraSceneOptions* terra_scene_get_options(HTerraScene scene); /* applied at the next commit */
+void               terra_scene_destroy(HTerraScene scene);
+
+bool terra_framebuffer_create(TerraFramebuffer* framebuffer, size_t width, size_t height);
+void terra_framebuffer_clear(TerraFramebuffer* framebuffer);
+void terra_framebuffer_destroy(TerraFramebuffer* framebuffer);
+
+bool        terra_texture_init(TerraTexture* texture, size_t width, size_t height, size_t components, const void* data);
+bool        terra_texture_init_hdr(TerraTexture* texture, size_t width, size_t height, size_t components, const float* data);
+TerraFloat3 terra_texture_read(TerraTexture* texture, size_t x, size_t y);
+TerraFloat3 terra_texture_sample(void* texture, const void* uv, const void* xyz);
+TerraFloat3 terra_texture_sample_latlong(void* texture, const void* dir, const void* xyz);
+void        terra_texture_destroy(TerraTexture* texture);
+void        terra_texture_finalize(void* texture);
+
+void terra_attribute_init_constant(TerraAttribute* attr, const TerraFloat3* value);
+void terra_attribute_init_texture(TerraAttribute* attr, TerraTexture* texture);
+void terra_attribute_init_cubemap(TerraAttribute* attr, TerraTexture* texture);
+
+/* Renders region [x,x+width) x [y,y+height): adds samples_per_pixel samples to
+ * framebuffer->results and rewrites framebuffer->pixels for the region.  Blocking; safe to call
+ * concurrently on disjoint regions of one framebuffer with one committed scene. */
+void terra_render(const TerraCamera* camera, HTerraScene scene, const TerraFramebuffer* framebuffer,
+                  size_t x, size_t y, size_t width, size_t height);
+
+void* terra_malloc(size_t size);
+void* terra_realloc(void* ptr, size_t size);
+void  terra_free(void* ptr);
+void  terra_log(const char* fmt, ...);
+
+/* ------------------------------------------------------------------ BSDF presets ------- */
+/* attribute slots, reference include/TerraPresets.h:11-26 */
+#define TERRA_DIFFUSE_ALBEDO           0
+#define TERRA_DIFFUSE_END              1
+#define TERRA_PHONG_SPECULAR_COLOR     0
+#define TERRA_PHONG_ALBEDO             1
+#define TERRA_PHONG_SPECULAR_INTENSITY 2
+#define TERRA_PHONG_SAMPLE_PICK        3
+#define TERRA_PHONG_END                4
+void terra_bsdf_diffuse_init(TerraBSDF* bsdf);
+void terra_bsdf_phong_init(TerraBSDF* bsdf);
+
+/* Additive presets: live {sample,pdf,eval} restatements of the reference's dead code
+ * (src/TerraPresets.c:298-394 rough dielectric GGX, :396-464 perfect glass).
+ *   GGX   : [0]=albedo  [1]=(roughness, metalness, ior)
+ *   GLASS : [0]=albedo  [1]=(ior, -, -)  [2].x = fresnel state written by sample() (init 0) */
+#define TERRA_GGX_ALBEDO               0
+#define TERRA_GGX_PARAMS               1
+#define TERRA_GGX_END                  2
+#define TERRA_GLASS_ALBEDO             0
+#define TERRA_GLASS_PARAMS             1
+#define TERRA_GLASS_STATE              2
+#define TERRA_GLASS_END                3
+void terra_bsdf_ggx_init(TerraBSDF* bsdf);
+void terra_bsdf_glass_init(TerraBSDF* bsdf);
+
+/* ------------------------------------------------------------------ extensions --------- */
+/* Closest-hit record of the traversal entry points (16 bytes). */
+typedef struct {
+    float    t;          /* distance from the OFFSET origin (origin + 0.001*dir, Terra.c:1628-1630); <0 = miss */
+    uint32_t prim;       /* object_idx | triangle_idx << 8   (0xFFFFFFFF = miss) */
+    float    u, v;       /* U/det, V/det of TerraGeometry.c:248-249 */
+} TerraB200Hit;
+
+typedef struct {
+    uint64_t kernel_launches;    /* CUDA kernels launched by this library since the last reset */
+    uint64_t rays_traced;        /* terra_scene_raycast equivalents */
+    uint64_t paths_traced;       /* (pixel,sample) pairs */
+    double   trace_kernel_ms;    /* device time spent in the traversal kernel (CUDA events) */
+    uint64_t trace_kernel_launches;
+    double   render_ms;          /* device time of whole terra_render calls */
+    uint64_t h2d_bytes, d2h_bytes;
+} TerraB200Stats;
+
+int  terra_b200_device_count(void);
+void terra_b200_set_device(int device);              /* before terra_scene_commit */
+void terra_b200_set_seed(HTerraScene scene, uint64_t seed);   /* default: time based, like the reference */
+void terra_b200_get_stats(HTerraScene scene, TerraB200Stats* out);
+void terra_b200_reset_stats(HTerraScene scene);
+
+/* The host BVH exactly as the reference lays it out (64-byte nodes, TerraBVH.h:13-17). */
+const void* terra_b200_bvh_nodes(HTerraScene scene, int* nodes_count);
+int         terra_b200_bvh_stack_bound(HTerraScene scene);   /* worst-case ordered-traversal stack */
+
+/* Traversal micro-benchmark / parity entry points (= terra_scene_raycast without shading).
+ * Host buffers: origins/dirs are n x 3 floats; the H2D/D2H copies are part of the call. */
+void terra_b200_trace_rays(HTerraScene scene, size_t n, const float* origins, const float* directions,
+                           TerraB200Hit* hits_out);
+/* Device buffers: float4 per ray (xyz used), caller's stream (cudaStream_t as void*). */
+void terra_b200_trace_rays_device(HTerraScene scene, size_t n, const void* d_origins, const void* d_directions,
+                                  void* d_hits_out, void* stream);
+/* Primary camera rays at subpixel_jitter = 0, one per pixel, row-major. */
+void terra_b200_primary_hits(const TerraCamera* camera, HTerraScene scene, size_t width, size_t height,
+                             TerraB200Hit* hits_out);
+
+/* Device-resident rendering for multi-GPU drivers: adds `spp` samples per pixel, sample
+ * indices [sample_base, sample_base+spp), to d_results (TerraRawIntegrationResult[width*height]
+ * in device memory) for the given region; no tonemap, no host copy. */
+void terra_b200_render_device(const TerraCamera* camera, HTerraScene scene, size_t fb_width, size_t fb_height,
+                              size_t x, size_t y, size_t width, size_t height,
+                              size_t sample_base, size_t spp, void* d_results, void* stream);
+/* acc/samples * exposure + tonemap (Terra.c:574-630) from d_results into d_pixels (float3). */
+void terra_b200_resolve_device(HTerraScene scene, size_t fb_width, size_t fb_height,
+                               const void* d_results, void* d_pixels, void* stream);
+
+/* BSDF known-answer entry point: runs sample/pdf/eval of the object's preset on the GPU for n
+ * (e1,e2,e3,wo,normal) tuples. out: n x 8 floats = wi.xyz, pdf, f.xyz, state. */
+void terra_b200_bsdf_kat(HTerraScene scene, size_t object_idx, size_t n,
+                         const float* e123, const float* wo, const float* normal, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+
+/* ------------------------------------------------------------------ ABI pins ----------- */
+#if defined(__cplusplus)
+#define TERRA_B200_SA(c, m) static_assert(c, m)
+#else
+#define TERRA_B200_SA(c, m) _Static_assert(c, m)
+#endif
+#if defined(__x86_64__) || defined(__aarch64__)
+TERRA_B200_SA(sizeof(TerraShadingSurface) == 188, "TerraShadingSurface ABI");
+TERRA_B200_SA(sizeof(TerraTexture) == 16, "TerraTexture ABI");
+TERRA_B200_SA(sizeof(TerraAttribute) == 40, "TerraAttribute ABI");
+TERRA_B200_SA(sizeof(TerraMaterial) == 408, "TerraMaterial ABI");
+TERRA_B200_SA(offsetof(TerraMaterial, emissive) == 32, "TerraMaterial.emissive ABI");
+TERRA_B200_SA(offsetof(TerraMaterial, attributes) == 72, "TerraMaterial.attributes ABI");
+TERRA_B200_SA(offsetof(TerraMaterial, attributes_count) == 392, "TerraMaterial.attributes_count ABI");
+TERRA_B200_SA(sizeof(TerraTriangle) == 36, "TerraTriangle ABI");
+TERRA_B200_SA(sizeof(TerraTriangleProperties) == 60, "TerraTriangleProperties ABI");
+TERRA_B200_SA(sizeof(TerraObject) == 432, "TerraObject ABI");
+TERRA_B200_SA(offsetof(TerraObject, material) == 24, "TerraObject.material ABI");
+TERRA_B200_SA(sizeof(TerraSceneOptions) == 96, "TerraSceneOptions ABI");
+TERRA_B200_SA(offsetof(TerraSceneOptions, subpixel_jitter) == 56, "TerraSceneOptions.subpixel_jitter ABI");
+TERRA_B200_SA(offsetof(TerraSceneOptions, samples_per_pixel) == 64, "TerraSceneOptions.spp ABI");
+TERRA_B200_SA(offsetof(TerraSceneOptions, manual_exposure) == 88, "TerraSceneOptions.exposure ABI");
+TERRA_B200_SA(sizeof(TerraCamera) == 40, "TerraCamera ABI");
+TERRA_B200_SA(sizeof(TerraRawIntegrationResult) == 16, "TerraRawIntegrationResult ABI");
+TERRA_B200_SA(sizeof(TerraFramebuffer) == 32, "TerraFramebuffer ABI");
+TERRA_B200_SA(sizeof(TerraB200Hit) == 16, "TerraB200Hit ABI");
+#endif
+
+#endif /* TERRA_B200_H */
