@@ -1,0 +1,130 @@
+// tb_internal.h — types shared by the host layer (tb_host.cpp) and the CUDA layer (tb_render.cu).
+// Not part of the ABI (include/terra_b200.h is).
+#pragma once
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include <vector_types.h>
+
+#include "../../include/terra_b200.h"
+
+// ---------------------------------------------------------------- host BVH, reference layout
+// Same 64-byte node the reference builds (src/TerraBVH.h:13-17): two child boxes, two child
+// indices, two child types (-1 inner, 1 leaf holding object | triangle << 8).
+struct TbHostNode {
+    TerraAABB aabb[2];
+    int32_t   index[2];
+    int32_t   type[2];
+};
+static_assert(sizeof(TbHostNode) == 64, "host node must stay 64 bytes");
+
+// ---------------------------------------------------------------- device layouts (HBM)
+// Node, 64 B = 4 x 128-bit loads:
+//   q0 = (min0.x, min0.y, min0.z, max0.x)   q1 = (max0.y, max0.z, min1.x, min1.y)
+//   q2 = (min1.z, max1.x, max1.y, max1.z)   q3 = (ref0, ref1, -, -) as int bits
+// ref >= 0: inner node index; ref < 0: leaf, ~ref = triangle RANK.
+//
+// Triangles are re-ordered into the reference traversal's leaf visiting order ("rank"), so an
+// exact-t tie resolves to the smaller rank exactly as the reference's first-found-wins rule
+// (src/TerraBVH.c:290) does. Per rank, 48 B = 3 x 128-bit:
+//   (a.xyz, prim bits)  (b.xyz, material/preset bits)  (c.xyz, -)
+// Shading properties per rank, 64 B = 4 x 128-bit:
+//   (na.xyz, nb.x) (nb.yz, nc.xy) (nc.z, ta.xy, tb.x) (tb.y, tc.xy, -)
+enum { TB_PRESET_DIFFUSE = 0, TB_PRESET_PHONG = 1, TB_PRESET_GGX = 2, TB_PRESET_GLASS = 3, TB_PRESET_COUNT = 4 };
+enum { TB_ATTR_CONST = 0, TB_ATTR_TEX2D = 1, TB_ATTR_LATLONG = 2 };
+
+struct TbDevAttr {            // 16 B
+    float   vx, vy, vz;       // constant value
+    int32_t kind_tex;         // kind | texture index << 2
+};
+
+struct TbDevTexture {         // 24 B
+    const void* pixels;       // device copy
+    uint16_t    width, height;
+    uint8_t     components, depth, filter, address_mode;
+    uint32_t    pad_;
+};
+
+struct TbDevMaterial {        // per object
+    int32_t   preset;
+    int32_t   attr_count;
+    float     ior;
+    int32_t   light_index;    // index into lights[] or -1
+    TbDevAttr emissive;
+    TbDevAttr attr[TERRA_MATERIAL_MAX_ATTRIBUTES];
+};
+
+struct TbDevLight {
+    int32_t  object;          // object index
+    uint32_t tri_count;
+    uint32_t tri_base;        // first entry of this light in light_tri_area[] / light_tri_rank[]
+    float    area;
+};
+
+struct TbDevScene {
+    const float4*        nodes;
+    const float4*        tris;
+    const float4*        props;
+    const TbDevMaterial* materials;
+    const TbDevTexture*  textures;
+    const TbDevLight*    lights;
+    const float*         light_tri_area;   // terra_triangle_area per light triangle (Terra.c:208-215)
+    const uint32_t*      light_tri_rank;   // rank of that triangle
+    int32_t              n_nodes, n_tris, n_objects, n_lights;
+    uint64_t             lights_triangles_count;  // never reset across commits in the reference
+    TbDevAttr            env;
+    int32_t              integrator, bounces, tonemap, preset_mask;
+    float                jitter, exposure, gamma, inv_gamma;
+};
+
+// ---------------------------------------------------------------- host scene
+struct TbTextureUpload { const TerraTexture* host; void* dev_pixels; size_t bytes; };
+
+struct TbDevice;              // opaque to the host layer: all CUDA state (tb_render.cu)
+
+struct TbCameraFrame {        // computed on the host with the reference's float ops
+    float rot[3][3];          // rows of terra_camera_to_world_frame (Terra.c:1770-1781)
+    float pos[3];
+    float tan_half_fov;       // (float) tan(double(fov * 0.0174533f) / 2), Terra.c:1794
+};
+
+// CUDA layer entry points used by the host layer ------------------------------------------
+struct TbFlatScene {          // host staging of everything the device needs
+    const float*         nodes;      size_t n_nodes;      // 16 floats per node
+    const float*         tris;       size_t n_tris;       // 12 floats per rank
+    const float*         props;                           // 16 floats per rank
+    const TbDevMaterial* materials;  size_t n_objects;
+    const TbDevLight*    lights;     size_t n_lights;
+    const float*         light_tri_area;
+    const uint32_t*      light_tri_rank;  size_t n_light_tris;
+    const TerraTexture* const* textures;  size_t n_textures;   // distinct host textures, index = TbDevAttr tex id
+    uint64_t             lights_triangles_count;
+    TbDevAttr            env;
+    int                  stack_bound;
+};
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+TbDevice* tb_device_create(int device_index);
+void      tb_device_destroy(TbDevice* dev);
+void      tb_device_upload(TbDevice* dev, const TbFlatScene* flat);
+void      tb_device_set_options(TbDevice* dev, const TerraSceneOptions* opts, const TbDevAttr* env);
+void      tb_device_render(TbDevice* dev, const TbCameraFrame* cam, const TerraFramebuffer* fb,
+                           size_t x, size_t y, size_t w, size_t h, size_t spp, uint64_t seed);
+void      tb_device_render_resident(TbDevice* dev, const TbCameraFrame* cam, size_t fbw, size_t fbh,
+                                    size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
+                                    uint64_t seed, void* d_results, void* stream);
+void      tb_device_resolve(TbDevice* dev, size_t fbw, size_t fbh, const void* d_results, void* d_pixels, void* stream);
+void      tb_device_trace_host(TbDevice* dev, size_t n, const float* origins, const float* dirs, TerraB200Hit* out);
+void      tb_device_trace_resident(TbDevice* dev, size_t n, const void* d_o, const void* d_d, void* d_hits, void* stream);
+void      tb_device_primary_hits(TbDevice* dev, const TbCameraFrame* cam, size_t w, size_t h, TerraB200Hit* out);
+void      tb_device_bsdf_kat(TbDevice* dev, size_t object_idx, size_t n, const float* e123, const float* wo,
+                             const float* normal, float* out);
+void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
+void      tb_device_reset_stats(TbDevice* dev);
+int       tb_cuda_device_count(void);
+#ifdef __cplusplus
+}
+#endif
