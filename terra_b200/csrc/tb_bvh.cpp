@@ -1,0 +1,227 @@
+// tb_bvh.cpp — host BVH: the reference's builder restated (src/TerraBVH.c:24-244 and
+// src/Terra.c:972-997), plus the flatten into the GPU layout (tb_internal.h).
+//
+// The tree must be THE reference's tree (north_star: "the reference BVH build from TerraBVH.c,
+// flattened into a GPU node/triangle layout"), because which triangles a ray may report depends on
+// which boxes it passes. What decides the tree shape is reproduced operation by
+// operation: the leaf padding (double 1e-4 subtracted/added then rounded to float), the +1e-4
+// on every max-merge (Q11), the x-only sort with a boolean "comparator" handed to libc qsort
+// (Q12: the order then depends on glibc's algorithm, so the same qsort is called on the same
+// 32-byte elements), the float SAH cost expression, and the LIFO task order that numbers nodes.
+// tests/test_bvh.py checks the node array byte-for-byte against terra_bvh_create.
+#include <float.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "tb_bvh.h"
+#include "tb_math.h"
+
+namespace {
+
+struct Volume {            // 32 bytes, like the reference's TerraBVHVolume (TerraBVH.c:11-15)
+    TerraAABB box;
+    uint32_t  index;
+    int32_t   type;
+};
+static_assert(sizeof(Volume) == 32, "qsort element size must match the reference");
+
+inline TerraAABB empty_box() {
+    TerraAABB b;
+    b.min.x = b.min.y = b.min.z = FLT_MAX;
+    b.max.x = b.max.y = b.max.z = -FLT_MAX;
+    return b;
+}
+
+// terra_aabb_fit_triangle, Terra.c:972-997. `-= 1e-4` is evaluated in double, as in the reference.
+inline void grow_by_triangle(TerraAABB* b, const TerraTriangle* t) {
+    b->min.x = tminf(tminf(tminf(b->min.x, t->a.x), t->b.x), t->c.x);
+    b->min.y = tminf(tminf(tminf(b->min.y, t->a.y), t->b.y), t->c.y);
+    b->min.z = tminf(tminf(tminf(b->min.z, t->a.z), t->b.z), t->c.z);
+    b->min.x -= TB_EPS_D;
+    b->min.y -= TB_EPS_D;
+    b->min.z -= TB_EPS_D;
+    b->max.x = tmaxf(tmaxf(tmaxf(b->max.x, t->a.x), t->b.x), t->c.x);
+    b->max.y = tmaxf(tmaxf(tmaxf(b->max.y, t->a.y), t->b.y), t->c.y);
+    b->max.z = tmaxf(tmaxf(tmaxf(b->max.z, t->a.z), t->b.z), t->c.z);
+    b->max.x += TB_EPS_D;
+    b->max.y += TB_EPS_D;
+    b->max.z += TB_EPS_D;
+}
+
+// terra_aabb_fit_aabb, TerraBVH.c:70-77: the epsilon lands on max only, on every merge.
+inline void grow_by_box(TerraAABB* b, const TerraAABB* o) {
+    b->min.x = tminf(b->min.x, o->min.x);
+    b->min.y = tminf(b->min.y, o->min.y);
+    b->min.z = tminf(b->min.z, o->min.z);
+    b->max.x = tmaxf(b->max.x, o->max.x) + TB_EPS_D;
+    b->max.y = tmaxf(b->max.y, o->max.y) + TB_EPS_D;
+    b->max.z = tmaxf(b->max.z, o->max.z) + TB_EPS_D;
+}
+
+inline float box_area(const TerraAABB* b) {                // TerraBVH.c:24-29
+    float w = b->max.x - b->min.x;
+    float h = b->max.y - b->min.y;
+    float d = b->max.z - b->min.z;
+    return 2 * (w * d + w * h + d * h);
+}
+
+inline float centre_x(const TerraAABB* b) {                // TerraBVH.c:31-35 (.x of (min+max)/2)
+    return (b->min.x + b->max.x) / 2;
+}
+
+// TerraBVH.c:37-46: returns true/false, not <0/0/>0. Kept as is; see the file header.
+int order_by_x(const void* l, const void* r) {
+    const TerraAABB* lb = &((const Volume*)l)->box;
+    const TerraAABB* rb = &((const Volume*)r)->box;
+    return centre_x(lb) < centre_x(rb) ? 1 : 0;
+}
+
+// terra_bvh_sah_split_volumes, TerraBVH.c:79-126. Returns the index (within the range) of the
+// last volume that goes left. Scratch arrays are reused across calls (the reference mallocs).
+int sah_split(Volume* v, int n, const TerraAABB* container, std::vector<float>& left_area, std::vector<float>& right_area) {
+    float container_area = container != NULL ? box_area(container) : FLT_MAX;
+    float min_cost = FLT_MAX;
+    int   min_cost_idx = -1;
+    qsort(v, (size_t)n, sizeof(Volume), order_by_x);
+    TerraAABB acc = empty_box();
+    for (int i = 0; i < n; ++i) {
+        grow_by_box(&acc, &v[i].box);
+        left_area[i] = box_area(&acc);
+    }
+    acc = empty_box();
+    for (int i = n - 1; i >= 0; --i) {
+        grow_by_box(&acc, &v[i].box);
+        right_area[i] = box_area(&acc);
+    }
+    for (int i = 0; i < n; ++i) {
+        int left_count = i + 1;
+        int right_count = n - left_count;
+        float cost = left_count * left_area[i] / container_area + right_count * right_area[i] / container_area;
+        if (cost < min_cost) {
+            min_cost = cost;
+            min_cost_idx = i;
+        }
+    }
+    return min_cost_idx;
+}
+
+struct Task { int begin, end, node; const TerraAABB* box; };
+
+}  // namespace
+
+void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes) {   // TerraBVH.c:128-244
+    TerraAABB scene_box = empty_box();
+    size_t total = 0;
+    for (int j = 0; j < objects_count; ++j) total += objects[j].triangles_count;
+    std::vector<Volume> volumes(total);
+    size_t p = 0;
+    for (int j = 0; j < objects_count; ++j)
+        for (size_t i = 0; i < objects[j].triangles_count; ++i, ++p) {
+            grow_by_triangle(&scene_box, &objects[j].triangles[i]);
+            volumes[p].box = empty_box();
+            grow_by_triangle(&volumes[p].box, &objects[j].triangles[i]);
+            volumes[p].type = 1;
+            volumes[p].index = (uint32_t)(j | ((int)i << 8));
+        }
+    nodes.assign(total * 2, TbHostNode());     // boxes are referenced by address while building: never reallocate
+    int nodes_count = 1;
+    std::vector<float> left_area(total), right_area(total);
+    std::vector<Task> stack;
+    stack.reserve(256);
+    stack.push_back(Task{ 0, (int)total, 0, &scene_box });
+    while (!stack.empty()) {
+        Task t = stack.back();
+        stack.pop_back();
+        int split = sah_split(volumes.data() + t.begin, t.end - t.begin, t.box, left_area, right_area) + t.begin;
+        TbHostNode* node = &nodes[t.node];
+        if (split == t.begin) {                 // a single volume on the left: leaf
+            node->type[0] = volumes[t.begin].type;
+            node->aabb[0] = volumes[t.begin].box;
+            node->index[0] = (int32_t)volumes[t.begin].index;
+        } else {
+            node->type[0] = -1;
+            TerraAABB b = empty_box();
+            for (int i = t.begin; i < split + 1; ++i) grow_by_box(&b, &volumes[i].box);
+            node->aabb[0] = b;
+            node->index[0] = nodes_count;
+            stack.push_back(Task{ t.begin, split + 1, nodes_count, &node->aabb[0] });
+            ++nodes_count;
+        }
+        if (split == t.end - 2) {               // a single volume on the right: leaf
+            node->type[1] = volumes[t.end - 1].type;
+            node->aabb[1] = volumes[t.end - 1].box;
+            node->index[1] = (int32_t)volumes[t.end - 1].index;
+        } else {
+            node->type[1] = -1;
+            TerraAABB b = empty_box();
+            for (int i = split + 1; i < t.end; ++i) grow_by_box(&b, &volumes[i].box);
+            node->aabb[1] = b;
+            node->index[1] = nodes_count;
+            stack.push_back(Task{ split + 1, t.end, nodes_count, &node->aabb[1] });
+            ++nodes_count;
+        }
+    }
+    nodes.resize((size_t)nodes_count);
+}
+
+// ------------------------------------------------------------------------------------ flatten
+// Rank = position of a leaf in the reference traversal's visiting order when every box is hit
+// (TerraBVH.c:266-306: pop a node, handle child 0 then child 1 — leaves are tested on the spot,
+// inner children pushed — so the later-pushed child 1 subtree is walked before child 0's).
+// Pruned traversals visit a subsequence of this order, hence "first found on an exact t tie"
+// == "smallest rank".
+void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* objects, int objects_count,
+                    TbFlatBvh* out) {
+    size_t total = 0;
+    std::vector<size_t> object_base((size_t)objects_count + 1, 0);
+    for (int j = 0; j < objects_count; ++j) { object_base[j] = total; total += objects[j].triangles_count; }
+    object_base[objects_count] = total;
+    out->nodes.assign(nodes.size() * 16, 0.f);
+    out->tris.assign(total * 12, 0.f);
+    out->props.assign(total * 16, 0.f);
+    out->rank_of_triangle.assign(total, 0u);
+    std::vector<int32_t> leaf_rank(nodes.size() * 2, -1);
+    // pass 1: ranks + depth bound, walking exactly like the reference's stack
+    std::vector<std::pair<int, int>> stack;    // node, depth (inner nodes above it)
+    stack.push_back({ 0, 0 });
+    uint32_t next_rank = 0;
+    int max_depth = 0;
+    while (!stack.empty()) {
+        std::pair<int, int> e = stack.back();
+        stack.pop_back();
+        const TbHostNode& n = nodes[(size_t)e.first];
+        if (e.second + 1 > max_depth) max_depth = e.second + 1;
+        for (int c = 0; c < 2; ++c) {
+            if (n.type[c] == -1) stack.push_back({ n.index[c], e.second + 1 });
+            else leaf_rank[(size_t)e.first * 2 + c] = (int32_t)next_rank++;
+        }
+    }
+    out->stack_bound = max_depth;
+    // pass 2: write nodes and rank-ordered triangle/property records
+    for (size_t i = 0; i < nodes.size(); ++i) {
+        const TbHostNode& n = nodes[i];
+        float* q = &out->nodes[i * 16];
+        memcpy(q, &n.aabb[0], 48);             // min0 max0 min1 max1, same order as the reference node
+        int32_t ref[4] = { 0, 0, 0, 0 };
+        for (int c = 0; c < 2; ++c) {
+            if (n.type[c] == -1) { ref[c] = n.index[c]; continue; }
+            int32_t rank = leaf_rank[i * 2 + c];
+            ref[c] = ~rank;
+            uint32_t prim = (uint32_t)n.index[c];
+            uint32_t obj = prim & 0xffu, tri = prim >> 8;
+            const TerraTriangle* t = &objects[obj].triangles[tri];
+            const TerraTriangleProperties* pr = &objects[obj].properties[tri];
+            float* d = &out->tris[(size_t)rank * 12];
+            d[0] = t->a.x; d[1] = t->a.y; d[2] = t->a.z; memcpy(&d[3], &prim, 4);
+            d[4] = t->b.x; d[5] = t->b.y; d[6] = t->b.z; memcpy(&d[7], &obj, 4);
+            d[8] = t->c.x; d[9] = t->c.y; d[10] = t->c.z;
+            float* s = &out->props[(size_t)rank * 16];
+            memcpy(s, pr, sizeof *pr);         // 15 floats: na nb nc ta tb tc
+            out->rank_of_triangle[object_base[obj] + tri] = (uint32_t)rank;
+        }
+        memcpy(q + 12, ref, 16);
+    }
+    out->object_base = object_base;
+}

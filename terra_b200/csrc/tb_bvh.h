@@ -1,0 +1,18 @@
+// tb_bvh.h — host BVH build (reference routine restated) and flatten to the GPU layout.
+#pragma once
+
+#include <vector>
+
+#include "tb_internal.h"
+
+struct TbFlatBvh {
+    std::vector<float>    nodes;              // 16 floats per node
+    std::vector<float>    tris;               // 12 floats per rank
+    std::vector<float>    props;              // 16 floats per rank
+    std::vector<uint32_t> rank_of_triangle;   // [object_base[obj] + tri] -> rank
+    std::vector<size_t>   object_base;
+    int                   stack_bound;        // inner nodes on the deepest root->leaf path
+};
+
+void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
+void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* objects, int objects_count, TbFlatBvh* out);

@@ -315,3 +315,253 @@ extern "C" void terra_scene_destroy(HTerraScene h) {                            
     if (s->dev) tb_device_destroy(s->dev);
     delete s;
 }
+
+// =============================================================================== commit
+#include "tb_bvh.h"
+
+static float triangle_area(const TerraTriangle* t) {                                                // Terra.c:1833-1838
+    V3 ab = vsub(v3abi(&t->b), v3abi(&t->a));
+    V3 ac = vsub(v3abi(&t->c), v3abi(&t->a));
+    return vlen(vcross(ab, ac)) / 2;
+}
+
+struct TbTextureTable {
+    std::vector<const TerraTexture*> list;
+    int index_of(const TerraTexture* t) {
+        for (size_t i = 0; i < list.size(); ++i) if (list[i] == t) return (int)i;
+        list.push_back(t);
+        return (int)list.size() - 1;
+    }
+};
+
+// Function-pointer attributes cannot cross to the device: classify by pointer identity.
+static TbDevAttr classify_attribute(const TerraAttribute* a, TbTextureTable* table, const char* what) {
+    TbDevAttr d;
+    d.vx = a->value.x; d.vy = a->value.y; d.vz = a->value.z;
+    d.kind_tex = TB_ATTR_CONST;
+    if (a->state == NULL) return d;                                                                 // Terra.c:1805
+    int kind;
+    if (a->eval == terra_texture_sample) kind = TB_ATTR_TEX2D;
+    else if (a->eval == terra_texture_sample_latlong) kind = TB_ATTR_LATLONG;
+    else {
+        terra_log("terra_b200: %s attribute has an eval callback that is not one of this library's "
+                  "(terra_texture_sample / terra_texture_sample_latlong)\n", what);
+        tb_fatal("custom attribute callbacks cannot run on the GPU and there is no CPU fallback");
+    }
+    const TerraTexture* t = (const TerraTexture*)a->state;
+    if (t->pixels == NULL) tb_fatal("attribute bound to a texture without pixels");
+    d.kind_tex = kind | (table->index_of(t) << 2);
+    return d;
+}
+
+static V3 host_attr_eval(const TerraAttribute* a, V2 uv) {                                          // Terra.c:1804-1810
+    if (a->state == NULL) return v3abi(&a->value);
+    TerraFloat2 t = { uv.x, uv.y };
+    TerraFloat3 r = a->eval(a->state, &t, NULL);
+    return v3abi(&r);
+}
+
+extern "C" void terra_scene_commit(HTerraScene h) {                                                 // Terra.c:162-236
+    TbScene* s = (TbScene*)h;
+    std::lock_guard<std::mutex> guard(s->lock);
+    bool dirty_accelerator = s->dirty_objects || !s->has_bvh;
+    if (s->opts.accelerator != s->new_opts.accelerator) dirty_accelerator = true;
+    s->opts = s->new_opts;
+    if (s->opts.accelerator != kTerraAcceleratorBVH) { assert(false); return; }
+    size_t total = 0;
+    for (size_t i = 0; i < s->objects_pop; ++i) total += s->objects[i].triangles_count;
+    if (total < 2) tb_fatal("terra_scene_commit needs at least 2 triangles (the reference builder reads out of range below that)");
+    if (!s->dev) s->dev = tb_device_create(g_device_index);
+
+    if (s->dirty_lights) {                                                                          // Terra.c:194-231
+        s->lights.clear();
+        for (size_t i = 0; i < s->objects_pop; ++i) {
+            V2 mid = { 0.5f, 0.5f };
+            V3 e = host_attr_eval(&s->objects[i].material.emissive, mid);
+            if (e.x == 0 && e.y == 0 && e.z == 0) continue;
+            TbLightHost l;
+            float area = 0;
+            l.triangle_area.resize(s->objects[i].triangles_count);
+            for (size_t j = 0; j < s->objects[i].triangles_count; ++j) {
+                float a = triangle_area(&s->objects[i].triangles[j]);
+                l.triangle_area[j] = a;
+                area += a;
+            }
+            l.power = abi3(vmul(e, area * TB_PI));
+            l.area = area;
+            l.object = i;
+            s->lights_triangles_count += s->objects[i].triangles_count;   // never reset, as in the reference
+            s->lights.push_back(l);
+        }
+    }
+
+    TbTextureTable table;
+    TbDevAttr env = classify_attribute(&s->opts.environment_map, &table, "environment_map");
+    if (dirty_accelerator || s->dirty_lights) {
+        if (dirty_accelerator) tb_bvh_build(s->objects, (int)s->objects_pop, s->nodes);
+        TbFlatBvh flat;
+        tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
+        s->stack_bound = flat.stack_bound;
+        std::vector<TbDevMaterial> mats(s->objects_pop);
+        for (size_t i = 0; i < s->objects_pop; ++i) {
+            const TerraMaterial* m = &s->objects[i].material;
+            int preset = classify_bsdf(&m->bsdf);
+            if (preset < 0) {
+                terra_log("terra_b200: object %zu: material.bsdf is not one of terra_bsdf_{diffuse,phong,ggx,glass}_init\n", i);
+                tb_fatal("custom BSDF callbacks cannot run on the GPU and there is no CPU fallback");
+            }
+            if (m->attributes_count > TERRA_MATERIAL_MAX_ATTRIBUTES) tb_fatal("attributes_count > TERRA_MATERIAL_MAX_ATTRIBUTES");
+            memset(&mats[i], 0, sizeof mats[i]);
+            mats[i].preset = preset;
+            mats[i].attr_count = (int)m->attributes_count;
+            mats[i].ior = m->ior;
+            mats[i].light_index = -1;
+            mats[i].emissive = classify_attribute(&m->emissive, &table, "emissive");
+            for (size_t k = 0; k < m->attributes_count; ++k) mats[i].attr[k] = classify_attribute(&m->attributes[k], &table, "material");
+        }
+        // tag every triangle record with object | preset << 8 so the trace kernel can bin hits by
+        // material without touching the material table
+        for (size_t r = 0; r < total; ++r) {
+            uint32_t obj;
+            memcpy(&obj, &flat.tris[r * 12 + 7], 4);
+            uint32_t tag = obj | ((uint32_t)mats[obj].preset << 8);
+            memcpy(&flat.tris[r * 12 + 7], &tag, 4);
+        }
+        std::vector<TbDevLight> lights(s->lights.size());
+        std::vector<float> light_area;
+        std::vector<uint32_t> light_rank;
+        for (size_t l = 0; l < s->lights.size(); ++l) {
+            size_t obj = s->lights[l].object;
+            lights[l].object = (int32_t)obj;
+            lights[l].tri_count = (uint32_t)s->objects[obj].triangles_count;
+            lights[l].tri_base = (uint32_t)light_area.size();
+            lights[l].area = s->lights[l].area;
+            mats[obj].light_index = (int32_t)l;
+            for (size_t j = 0; j < s->objects[obj].triangles_count; ++j) {
+                light_area.push_back(s->lights[l].triangle_area[j]);
+                light_rank.push_back(flat.rank_of_triangle[flat.object_base[obj] + j]);
+            }
+        }
+        TbFlatScene up;
+        memset(&up, 0, sizeof up);
+        up.nodes = flat.nodes.data();   up.n_nodes = s->nodes.size();
+        up.tris = flat.tris.data();     up.n_tris = total;
+        up.props = flat.props.data();
+        up.materials = mats.data();     up.n_objects = s->objects_pop;
+        up.lights = lights.data();      up.n_lights = lights.size();
+        up.light_tri_area = light_area.data();
+        up.light_tri_rank = light_rank.data();
+        up.n_light_tris = light_area.size();
+        up.textures = table.list.data(); up.n_textures = table.list.size();
+        up.lights_triangles_count = s->lights_triangles_count;
+        up.env = env;
+        up.stack_bound = flat.stack_bound;
+        tb_device_upload(s->dev, &up);
+        s->has_bvh = true;
+    }
+    tb_device_set_options(s->dev, &s->opts, &env);
+    s->dirty_objects = false;
+    s->dirty_lights = false;
+}
+
+// =============================================================================== render
+static TbCameraFrame camera_frame(const TerraCamera* c) {                                           // Terra.c:1770-1781, 1794
+    V3 zaxis = vnorm(v3abi(&c->direction));
+    V3 xaxis = vnorm(vcross(v3abi(&c->up), zaxis));
+    V3 yaxis = vcross(zaxis, xaxis);
+    TbCameraFrame f;
+    f.rot[0][0] = xaxis.x; f.rot[0][1] = yaxis.x; f.rot[0][2] = zaxis.x;
+    f.rot[1][0] = xaxis.y; f.rot[1][1] = yaxis.y; f.rot[1][2] = zaxis.y;
+    f.rot[2][0] = xaxis.z; f.rot[2][1] = yaxis.z; f.rot[2][2] = zaxis.z;
+    f.pos[0] = c->position.x; f.pos[1] = c->position.y; f.pos[2] = c->position.z;
+    f.tan_half_fov = (float)tan((c->fov * 0.0174533f) / 2);
+    return f;
+}
+
+static size_t effective_spp(const TerraSceneOptions* o) {                                           // Terra.c:516-527
+    size_t spp = o->samples_per_pixel;
+    if (o->sampling_method == kTerraSamplingMethodStratified) {
+        size_t cur = o->strata * o->strata;
+        if (cur < 2) return spp > cur ? spp : cur;     // the reference loops forever on strata <= 1; do not
+        while (spp > cur) cur *= cur;
+        spp = cur;
+    }
+    return spp;
+}
+
+static uint64_t next_seed(TbScene* s) {
+    uint64_t call = s->render_calls++;
+    uint64_t base = s->seed_fixed ? s->seed : ((uint64_t)time(NULL) ^ (uint64_t)(uintptr_t)&exit);  // Terra.c:679
+    return base * 0x9E3779B97F4A7C15ull + call * 0xD1B54A32D192ED03ull + 1;
+}
+
+static TbScene* committed(HTerraScene h, const char* who) {
+    TbScene* s = (TbScene*)h;
+    if (!s || !s->dev || !s->has_bvh) {
+        terra_log("terra_b200: %s called on a scene that was never committed\n", who);
+        tb_fatal("scene not committed");
+    }
+    return s;
+}
+
+extern "C" void terra_render(const TerraCamera* camera, HTerraScene h, const TerraFramebuffer* fb,
+                             size_t x, size_t y, size_t width, size_t height) {                     // Terra.c:512-635
+    TbScene* s = committed(h, "terra_render");
+    if (width == 0 || height == 0) return;
+    if (x + width > fb->width || y + height > fb->height) tb_fatal("terra_render region outside the framebuffer");
+    std::lock_guard<std::mutex> guard(s->lock);
+    TbCameraFrame cam = camera_frame(camera);
+    tb_device_render(s->dev, &cam, fb, x, y, width, height, effective_spp(&s->opts), next_seed(s));
+}
+
+// =============================================================================== extensions
+extern "C" int  terra_b200_device_count(void) { return tb_cuda_device_count(); }
+extern "C" void terra_b200_set_device(int device) { g_device_index = device; }
+extern "C" void terra_b200_set_seed(HTerraScene h, uint64_t seed) {
+    TbScene* s = (TbScene*)h;
+    s->seed = seed; s->seed_fixed = true; s->render_calls = 0;
+}
+extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) { tb_device_get_stats(committed(h, "terra_b200_get_stats")->dev, out); }
+extern "C" void terra_b200_reset_stats(HTerraScene h) { tb_device_reset_stats(committed(h, "terra_b200_reset_stats")->dev); }
+extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
+    TbScene* s = (TbScene*)h;
+    *nodes_count = (int)s->nodes.size();
+    return s->nodes.data();
+}
+extern "C" int terra_b200_bvh_stack_bound(HTerraScene h) { return ((TbScene*)h)->stack_bound; }
+
+extern "C" void terra_b200_trace_rays(HTerraScene h, size_t n, const float* origins, const float* directions, TerraB200Hit* hits_out) {
+    TbScene* s = committed(h, "terra_b200_trace_rays");
+    std::lock_guard<std::mutex> guard(s->lock);
+    tb_device_trace_host(s->dev, n, origins, directions, hits_out);
+}
+extern "C" void terra_b200_trace_rays_device(HTerraScene h, size_t n, const void* d_o, const void* d_d, void* d_hits, void* stream) {
+    TbScene* s = committed(h, "terra_b200_trace_rays_device");
+    std::lock_guard<std::mutex> guard(s->lock);
+    tb_device_trace_resident(s->dev, n, d_o, d_d, d_hits, stream);
+}
+extern "C" void terra_b200_primary_hits(const TerraCamera* camera, HTerraScene h, size_t width, size_t height, TerraB200Hit* hits_out) {
+    TbScene* s = committed(h, "terra_b200_primary_hits");
+    std::lock_guard<std::mutex> guard(s->lock);
+    TbCameraFrame cam = camera_frame(camera);
+    tb_device_primary_hits(s->dev, &cam, width, height, hits_out);
+}
+extern "C" void terra_b200_render_device(const TerraCamera* camera, HTerraScene h, size_t fbw, size_t fbh,
+                                         size_t x, size_t y, size_t width, size_t height,
+                                         size_t sample_base, size_t spp, void* d_results, void* stream) {
+    TbScene* s = committed(h, "terra_b200_render_device");
+    std::lock_guard<std::mutex> guard(s->lock);
+    TbCameraFrame cam = camera_frame(camera);
+    uint64_t seed = s->seed_fixed ? s->seed * 0x9E3779B97F4A7C15ull + 1 : next_seed(s);
+    tb_device_render_resident(s->dev, &cam, fbw, fbh, x, y, width, height, sample_base, spp, seed, d_results, stream);
+}
+extern "C" void terra_b200_resolve_device(HTerraScene h, size_t fbw, size_t fbh, const void* d_results, void* d_pixels, void* stream) {
+    TbScene* s = committed(h, "terra_b200_resolve_device");
+    tb_device_resolve(s->dev, fbw, fbh, d_results, d_pixels, stream);
+}
+extern "C" void terra_b200_bsdf_kat(HTerraScene h, size_t object_idx, size_t n, const float* e123, const float* wo,
+                                    const float* normal, float* out) {
+    TbScene* s = committed(h, "terra_b200_bsdf_kat");
+    if (object_idx >= s->objects_pop) tb_fatal("terra_b200_bsdf_kat: object index out of range");
+    tb_device_bsdf_kat(s->dev, object_idx, n, e123, wo, normal, out);
+}
