@@ -294,6 +294,10 @@ void terra_b200_reset_stats(HTerraScene scene);
 /* The host BVH exactly as the reference lays it out (64-byte nodes, TerraBVH.h:13-17). */
 const void* terra_b200_bvh_nodes(HTerraScene scene, int* nodes_count);
 int         terra_b200_bvh_stack_bound(HTerraScene scene);   /* worst-case ordered-traversal stack */
+/* Host-only half of commit (no GPU needed): builds the BVH, optionally writes the flattened GPU
+ * arrays (16 floats per node: two boxes + two child refs; 12 floats per triangle in rank order).
+ * Returns the node count (= triangles - 1). */
+int         terra_b200_build_host_bvh(HTerraScene scene, float* flat_nodes_out, float* flat_tris_out);
 
 /* Traversal micro-benchmark / parity entry points (= terra_scene_raycast without shading).
  * Host buffers: origins/dirs are n x 3 floats; the H2D/D2H copies are part of the call. */

@@ -166,6 +166,7 @@ class TerraLib:
             sig("terra_b200_reset_stats", None, _vp)
             sig("terra_b200_bvh_nodes", _vp, _vp, C.POINTER(C.c_int))
             sig("terra_b200_bvh_stack_bound", C.c_int, _vp)
+            sig("terra_b200_build_host_bvh", C.c_int, _vp, _vp, _vp)
             sig("terra_b200_trace_rays", None, _vp, _sz, _vp, _vp, _vp)
             sig("terra_b200_trace_rays_device", None, _vp, _sz, _vp, _vp, _vp, _vp)
             sig("terra_b200_primary_hits", None, C.POINTER(Camera), _vp, _sz, _sz, _vp)
@@ -335,6 +336,13 @@ class Scene:
         s = Stats()
         self.lib.terra_b200_get_stats(self.h, C.byref(s))
         return s
+
+    def build_host_bvh(self, n_tris: int):
+        """Host-only BVH build + flatten. Returns (flat nodes (n-1,16) f32, flat tris (n,12) f32)."""
+        nodes = np.zeros((n_tris * 2, 16), np.float32)
+        tris = np.zeros((n_tris, 12), np.float32)
+        n = self.lib.terra_b200_build_host_bvh(self.h, _ptr(nodes), _ptr(tris))
+        return nodes[:n].copy(), tris
 
     def bvh_nodes(self) -> np.ndarray:
         n = C.c_int(0)

@@ -529,6 +529,19 @@ extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     return s->nodes.data();
 }
 extern "C" int terra_b200_bvh_stack_bound(HTerraScene h) { return ((TbScene*)h)->stack_bound; }
+// Host-only half of terra_scene_commit (no CUDA device needed): build the BVH and flatten it.
+// Lets the CPU test-suite check the builder and the flatten against the reference's node array.
+extern "C" int terra_b200_build_host_bvh(HTerraScene h, float* flat_nodes_out, float* flat_tris_out) {
+    TbScene* s = (TbScene*)h;
+    std::lock_guard<std::mutex> guard(s->lock);
+    tb_bvh_build(s->objects, (int)s->objects_pop, s->nodes);
+    TbFlatBvh flat;
+    tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
+    s->stack_bound = flat.stack_bound;
+    if (flat_nodes_out) memcpy(flat_nodes_out, flat.nodes.data(), flat.nodes.size() * sizeof(float));
+    if (flat_tris_out) memcpy(flat_tris_out, flat.tris.data(), flat.tris.size() * sizeof(float));
+    return (int)s->nodes.size();
+}
 
 extern "C" void terra_b200_trace_rays(HTerraScene h, size_t n, const float* origins, const float* directions, TerraB200Hit* hits_out) {
     TbScene* s = committed(h, "terra_b200_trace_rays");

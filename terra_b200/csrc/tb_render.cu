@@ -143,8 +143,10 @@ extern "C" int tb_cuda_device_count(void) {
 static void tb_wave_free(TbWave* w) {
     tb_free(w->ray_o); tb_free(w->ray_d); tb_free(w->thr); tb_free(w->lo); tb_free(w->hit);
     tb_free(w->aux_o); tb_free(w->aux_d); tb_free(w->aux_hit);
-    tb_free(w->queue[0]); tb_free(w->queue[1]); tb_free(w->matq); tb_free(w->auxq); tb_free(w->counters);
+    tb_free(w->queue[0]); tb_free(w->queue[1]); tb_free(w->matq); tb_free(w->auxq);
+    int* counters = w->counters;                 // lives as long as the device (holds the ray statistics)
     memset(w, 0, sizeof *w);
+    w->counters = counters;
 }
 static void tb_wave_reserve(TbWave* w, size_t capacity) {
     if (w->capacity >= capacity) return;
@@ -162,7 +164,6 @@ static void tb_wave_reserve(TbWave* w, size_t capacity) {
     w->queue[1] = tb_alloc<int>(capacity);
     w->matq = tb_alloc<int>(capacity * TB_PRESET_COUNT);
     w->auxq = tb_alloc<int>(capacity * 2);
-    w->counters = tb_alloc<int>(16);
 }
 
 extern "C" TbDevice* tb_device_create(int device_index) {
@@ -185,6 +186,8 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
     d->stack_bound = 0;
     memset(&d->wave, 0, sizeof d->wave);
+    d->wave.counters = tb_alloc<int>(16);
+    TB_CUDA(cudaMemset(d->wave.counters, 0, 16 * sizeof(int)));
     d->fb_capacity = 0; d->d_results = NULL; d->d_pixels = NULL; d->d_acc = NULL; d->acc_capacity = 0;
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
     memset(&d->stats, 0, sizeof d->stats);
@@ -208,6 +211,7 @@ extern "C" void tb_device_destroy(TbDevice* d) {
     TB_CUDA(cudaStreamSynchronize(d->stream));
     tb_scene_free(d);
     tb_wave_free(&d->wave);
+    tb_free(d->wave.counters);
     tb_free(d->d_results); tb_free(d->d_pixels); tb_free(d->d_acc);
     tb_free(d->d_io_o); tb_free(d->d_io_d); tb_free(d->d_io_hit);
     for (TbEventPair& e : d->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
@@ -276,4 +280,1034 @@ extern "C" void tb_device_set_options(TbDevice* d, const TerraSceneOptions* o, c
     sc.exposure = o->manual_exposure;
     sc.gamma = o->gamma;
     sc.inv_gamma = 1.f / o->gamma;                      // `1.f / scene->opts.gamma`, Terra.c:582
+}
+
+// ==================================================================================== K2: closest hit
+// Ray in the frame the reference intersects in: origin already moved 0.001 along the direction
+// (terra_scene_raycast, Terra.c:1628-1630), inverse direction (terra_ray, :1706-1708) and the
+// Wald-2013 shear/scale + axis permutation (terra_ray_triangle_intersection_init,
+// TerraGeometry.c:98-134).
+struct TbRay {
+    V3    o, inv;
+    float sx, sy, sz;
+    int   kx, ky, kz;
+};
+
+__device__ __forceinline__ float tb_sel(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+
+__device__ __forceinline__ V3 tb_offset_origin(V3 o, V3 d) { return vadd(o, vmul(d, 0.001f)); }
+
+__device__ __forceinline__ TbRay tb_ray_setup(V3 origin, V3 d) {
+    TbRay r;
+    r.o = tb_offset_origin(origin, d);
+    r.inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    int kz;                                             // terra_max_coefff3, TerraMath.inl:155-169
+    if (ax > ay) kz = ax > az ? 0 : 2;
+    else         kz = ay > az ? 1 : 2;
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
+    float dz = tb_sel(d, kz);
+    if (dz < 0.f) { int t = kx; kx = ky; ky = t; }
+    r.sz = 1.f / dz;
+    r.sx = tb_sel(d, kx) * r.sz;
+    r.sy = tb_sel(d, ky) * r.sz;
+    r.kx = kx; r.ky = ky; r.kz = kz;
+    return r;
+}
+
+// terra_ray_aabb_intersection, Terra.c:851-878. Operand order of every min/max kept (NaN behaviour).
+__device__ __forceinline__ bool tb_box(const TbRay& r, float mnx, float mny, float mnz, float mxx, float mxy, float mxz, float* tmin_out) {
+    float t1 = (mnx - r.o.x) * r.inv.x;
+    float t2 = (mxx - r.o.x) * r.inv.x;
+    float tmin = tminf(t1, t2);
+    float tmax = tmaxf(t1, t2);
+    t1 = (mny - r.o.y) * r.inv.y;
+    t2 = (mxy - r.o.y) * r.inv.y;
+    tmin = tmaxf(tmin, tminf(t1, t2));
+    tmax = tminf(tmax, tmaxf(t1, t2));
+    t1 = (mnz - r.o.z) * r.inv.z;
+    t2 = (mxz - r.o.z) * r.inv.z;
+    tmin = tmaxf(tmin, tminf(t1, t2));
+    tmax = tminf(tmax, tmaxf(t1, t2));
+    *tmin_out = tmin;
+    return tmax > tmaxf(tmin, 0.f);
+}
+
+// terra_ray_triangle_intersection_query, TerraGeometry.c:159-259: watertight, no culling, fp64 retry.
+__device__ __forceinline__ bool tb_triangle(const TbRay& r, V3 a, V3 b, V3 c, float* t_out, float* u_out, float* v_out) {
+    const V3 A = vsub(a, r.o), B = vsub(b, r.o), C = vsub(c, r.o);
+    const float Akz = tb_sel(A, r.kz), Bkz = tb_sel(B, r.kz), Ckz = tb_sel(C, r.kz);
+    const float Ax = tb_sel(A, r.kx) - r.sx * Akz;
+    const float Ay = tb_sel(A, r.ky) - r.sy * Akz;
+    const float Bx = tb_sel(B, r.kx) - r.sx * Bkz;
+    const float By = tb_sel(B, r.ky) - r.sy * Bkz;
+    const float Cx = tb_sel(C, r.kx) - r.sx * Ckz;
+    const float Cy = tb_sel(C, r.ky) - r.sy * Ckz;
+    float U = Cx * By - Cy * Bx;
+    float V = Ax * Cy - Ay * Cx;
+    float W = Bx * Ay - By * Ax;
+    if (U == 0.f || V == 0.f || W == 0.f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
+    const uint32_t sign_mask = fbits(U) & 0x80000000u;
+    if (sign_mask != (fbits(V) & 0x80000000u)) return false;
+    if (sign_mask != (fbits(W) & 0x80000000u)) return false;
+    const float det = U + V + W;
+    if (det == 0.f) return false;
+    const float Az = r.sz * Akz, Bz = r.sz * Bkz, Cz = r.sz * Ckz;
+    const float ray_depth = U * Az + V * Bz + W * Cz;
+    if (bitsf(fbits(ray_depth) ^ sign_mask) < 0.f) return false;
+    const float inv_det = 1.f / det;
+    *u_out = U * inv_det;
+    *v_out = V * inv_det;
+    *t_out = ray_depth * inv_det;
+    return true;
+}
+
+struct TbTraceArgs {
+    const float4* nodes;
+    const float4* tris;
+    const float4* ray_o;        // indexed by slot
+    const float4* ray_d;
+    const int*    queue;        // NULL: slot = ray index
+    const int*    count_ptr;    // device count (wavefront) or NULL -> count
+    int           count;
+    int*          cursor;       // global fetch cursor (zeroed before launch)
+    float4*       hit_out;      // by slot: (t, rank | prim, u, v)
+    int*          matq;         // NULL or TB_PRESET_COUNT queues of `matq_stride`
+    int*          matq_count;
+    int           matq_stride;
+    int           emit_prim;    // 1: write object|tri<<8 (API), 0: write rank (wavefront)
+};
+
+// Persistent CTAs; each warp pulls rays from a global cursor and refills idle lanes when too few
+// are busy (dynamic fetch). Near-first ordered descent of the reference tree with t culling: the
+// reference walks every box the ray passes and keeps min t with first-found-wins on ties
+// (TerraBVH.c:266-306); culling by the current closest t plus the smallest-rank tie
+// rule returns the same primitive. Stack: TB_STACK_SMEM entries per thread in shared memory
+// ([depth][thread], conflict free), the rest in local memory.
+__global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace(TbTraceArgs a) {
+    __shared__ int   s_node[TB_STACK_SMEM][TB_TRACE_THREADS];
+    __shared__ float s_tmin[TB_STACK_SMEM][TB_TRACE_THREADS];
+    int   l_node[TB_STACK_LOCAL];
+    float l_tmin[TB_STACK_LOCAL];
+    const int tid = threadIdx.x;
+    const unsigned lane = tid & 31u;
+    const int total = a.count_ptr ? *a.count_ptr : a.count;
+
+    const int DONE = -1;
+    int   slot = -1, node = DONE, sp = 0;
+    int   best_rank = -1;
+    float best_t = FLT_MAX, cull_t = FLT_MAX, best_u = 0.f, best_v = 0.f;
+    TbRay r;
+    r.o = r.inv = v3s(0.f); r.sx = r.sy = r.sz = 0.f; r.kx = r.ky = r.kz = 0;
+    bool exhausted = false;
+
+    while (true) {
+        // ---- refill idle lanes (warp converged here)
+        const bool idle = node == DONE;
+        const unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
+        if (idle_mask && !exhausted) {
+            const int want = __popc(idle_mask);
+            int base = 0;
+            if (lane == (unsigned)(__ffs(idle_mask) - 1)) base = atomicAdd(a.cursor, want);
+            base = __shfl_sync(0xffffffffu, base, __ffs(idle_mask) - 1);
+            if (base + want >= total) exhausted = true;
+            if (idle) {
+                const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
+                if (q < total) {
+                    slot = a.queue ? a.queue[q] : q;
+                    const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
+                    r = tb_ray_setup(v3(o4.x, o4.y, o4.z), v3(d4.x, d4.y, d4.z));
+                    node = 0; sp = 0;
+                    best_rank = -1; best_t = FLT_MAX; cull_t = FLT_MAX;
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, node != DONE) == 0u) break;
+
+        // ---- traverse
+        while (node != DONE) {
+            const float4* np = a.nodes + (size_t)node * 4;
+            const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+            const int ref0 = __float_as_int(q3.x), ref1 = __float_as_int(q3.y);
+            float tmin0, tmin1;
+            bool hit0 = tb_box(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
+            bool hit1 = tb_box(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, &tmin1);
+            hit0 = hit0 && !(tmin0 > cull_t);
+            hit1 = hit1 && !(tmin1 > cull_t);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const int  ref = c ? ref1 : ref0;
+                const bool h = c ? hit1 : hit0;
+                const float tm = c ? tmin1 : tmin0;
+                if (h && ref < 0 && !(tm > cull_t)) {
+                    const int rank = ~ref;
+                    const float4* tp = a.tris + (size_t)rank * 3;
+                    const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
+                    float t, u, v;
+                    if (tb_triangle(r, v3(ta.x, ta.y, ta.z), v3(tb.x, tb.y, tb.z), v3(tc.x, tc.y, tc.z), &t, &u, &v)) {
+                        if (t < best_t || (t == best_t && best_rank >= 0 && rank < best_rank)) {
+                            best_t = t; best_rank = rank; best_u = u; best_v = v;
+                            cull_t = best_t + best_t * 1e-5f;
+                        }
+                    }
+                }
+            }
+            const bool in0 = hit0 && ref0 >= 0 && !(tmin0 > cull_t);
+            const bool in1 = hit1 && ref1 >= 0 && !(tmin1 > cull_t);
+            if (in0 && in1) {
+                const bool near1 = tmin1 < tmin0;
+                const int   far_node = near1 ? ref0 : ref1;
+                const float far_tmin = near1 ? tmin0 : tmin1;
+                node = near1 ? ref1 : ref0;
+                if (sp < TB_STACK_SMEM) { s_node[sp][tid] = far_node; s_tmin[sp][tid] = far_tmin; }
+                else { l_node[sp - TB_STACK_SMEM] = far_node; l_tmin[sp - TB_STACK_SMEM] = far_tmin; }
+                ++sp;
+            } else if (in0) {
+                node = ref0;
+            } else if (in1) {
+                node = ref1;
+            } else {
+                node = DONE;
+                while (sp > 0) {
+                    --sp;
+                    int n; float tm;
+                    if (sp < TB_STACK_SMEM) { n = s_node[sp][tid]; tm = s_tmin[sp][tid]; }
+                    else { n = l_node[sp - TB_STACK_SMEM]; tm = l_tmin[sp - TB_STACK_SMEM]; }
+                    if (!(tm > cull_t)) { node = n; break; }
+                }
+            }
+            if (!exhausted && __popc(__activemask()) < TB_REFETCH_BELOW) break;
+        }
+
+        // ---- retire finished rays (warp converged again)
+        const bool finished = node == DONE && slot >= 0;
+        int preset = -1;
+        if (finished) {
+            float4 h;
+            if (best_rank >= 0) {
+                const float4 ta = __ldg(a.tris + (size_t)best_rank * 3);
+                const float4 tb = __ldg(a.tris + (size_t)best_rank * 3 + 1);
+                h.x = best_t;
+                h.y = a.emit_prim ? ta.w : __int_as_float(best_rank);
+                h.z = best_u; h.w = best_v;
+                preset = (__float_as_int(tb.w) >> 8) & 0xff;
+            } else {
+                h.x = -1.f; h.y = __int_as_float(-1); h.z = 0.f; h.w = 0.f;
+            }
+            a.hit_out[slot] = h;
+        }
+        if (a.matq) {
+#pragma unroll
+            for (int p = 0; p < TB_PRESET_COUNT; ++p) {
+                const unsigned m = __ballot_sync(0xffffffffu, finished && preset == p);
+                if (m) {
+                    int base = 0;
+                    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(a.matq_count + p, __popc(m));
+                    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+                    if (finished && preset == p) a.matq[(size_t)p * a.matq_stride + base + __popc(m & ((1u << lane) - 1u))] = slot;
+                }
+            }
+        }
+        if (finished) slot = -1;
+    }
+}
+
+// ==================================================================================== K1: ray generation
+struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot = s_local * n_pixels + p_local
+    int      x, y, w, h;       // render region inside the framebuffer
+    int      fbw, fbh;
+    int      p0, n_pixels;     // region-linear pixel range of this batch
+    int      s0, n_samples;    // sample range of this batch (relative to sample_base)
+    uint32_t sample_base;
+    uint64_t seed;
+};
+
+struct TbRaygenArgs {
+    TbBatch batch;
+    TbCameraFrame cam;
+    float   jitter;
+    float4 *ray_o, *ray_d, *thr, *lo;
+    int*    queue;
+};
+
+__device__ __forceinline__ void tb_slot_to_pixel(const TbBatch& b, int slot, int* px, int* py, uint32_t* sample) {
+    const int s_local = slot / b.n_pixels;
+    const int pr = b.p0 + (slot - s_local * b.n_pixels);
+    *py = b.y + pr / b.w;
+    *px = b.x + pr % b.w;
+    *sample = b.sample_base + (uint32_t)(b.s0 + s_local);
+}
+
+// terra_camera_perspective_sample + terra_transformf3 + terra_ray (Terra.c:555-560, 1783-1799)
+__device__ __forceinline__ V3 tb_camera_dir(const TbCameraFrame& cam, int px, int py, int fbw, int fbh, float jitter, float r1, float r2) {
+    const float dx = -jitter + 2 * r1 * jitter;
+    const float dy = -jitter + 2 * r2 * jitter;
+    const float ndc_x = ((float)px + 0.5f + dx) / (float)fbw;
+    const float ndc_y = ((float)py + 0.5f + dy) / (float)fbh;
+    const float screen_x = 2 * ndc_x - 1;
+    const float screen_y = 1 - 2 * ndc_y;
+    const float aspect_ratio = (float)fbw / (float)fbh;
+    const float frustum_x = screen_x * aspect_ratio * cam.tan_half_fov;
+    const float frustum_y = screen_y * cam.tan_half_fov;
+    V3 dir = vnorm(v3(frustum_x, frustum_y, 1.f));
+    M3 rot;
+    rot.r0 = v3(cam.rot[0][0], cam.rot[0][1], cam.rot[0][2]);
+    rot.r1 = v3(cam.rot[1][0], cam.rot[1][1], cam.rot[1][2]);
+    rot.r2 = v3(cam.rot[2][0], cam.rot[2][1], cam.rot[2][2]);
+    return mtransform(rot, dir);
+}
+
+__global__ void __launch_bounds__(256) k_raygen(TbRaygenArgs a) {
+    const int n = a.batch.n_pixels * a.batch.n_samples;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
+        int px, py; uint32_t sample;
+        tb_slot_to_pixel(a.batch, slot, &px, &py, &sample);
+        const uint64_t key = tb_path_key(a.batch.seed, (uint32_t)(py * a.batch.fbw + px), sample);
+        const float r1 = tb_randf_pcg(key, TB_DIM_JITTER_X), r2 = tb_randf_pcg(key, TB_DIM_JITTER_Y);
+        const V3 d = tb_camera_dir(a.cam, px, py, a.batch.fbw, a.batch.fbh, a.jitter, r1, r2);
+        // the path key rides in the .w lanes of the ray so later stages need no extra array
+        a.ray_o[slot] = make_float4(a.cam.pos[0], a.cam.pos[1], a.cam.pos[2], __uint_as_float((uint32_t)key));
+        a.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float((uint32_t)(key >> 32)));
+        a.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+        a.lo[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        a.queue[slot] = slot;
+    }
+}
+
+// Primary rays at jitter 0 for the parity entry point: one float4 origin/direction per pixel.
+__global__ void __launch_bounds__(256) k_primary_rays(TbCameraFrame cam, int w, int h, float4* ray_o, float4* ray_d) {
+    const int n = w * h;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const V3 d = tb_camera_dir(cam, p % w, p / w, w, h, 0.f, 0.f, 0.f);
+        ray_o[p] = make_float4(cam.pos[0], cam.pos[1], cam.pos[2], 0.f);
+        ray_d[p] = make_float4(d.x, d.y, d.z, 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pack_rays(size_t n, const float* o3, const float* d3, float4* ray_o, float4* ray_d) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        ray_o[i] = make_float4(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2], 0.f);
+        ray_d[i] = make_float4(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2], 0.f);
+    }
+}
+
+// ==================================================================================== K3: surface
+// terra_surface_init (Terra.c:1726-1764): barycentrics are re-derived from the hit point with a
+// Cramer solve (the intersector's u,v are ignored), normal/texcoord blended as
+// c*v + b*u + a*(1-u-v), attributes evaluated, skewed tangent frame built.
+struct TbHitInfo { int rank, object, preset; V3 a, b, c; V2 texcoord; };
+
+__device__ __forceinline__ TbSurface tb_surface_init(const TbDevScene& sc, int rank, V3 point, TbHitInfo* info) {
+    const float4* tp = sc.tris + (size_t)rank * 3;
+    const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
+    const float4* pp = sc.props + (size_t)rank * 4;
+    const float4 p0 = __ldg(pp), p1 = __ldg(pp + 1), p2 = __ldg(pp + 2), p3 = __ldg(pp + 3);
+    const V3 a = v3(ta.x, ta.y, ta.z), b = v3(tb.x, tb.y, tb.z), c = v3(tc.x, tc.y, tc.z);
+    const V3 na = v3(p0.x, p0.y, p0.z), nb = v3(p0.w, p1.x, p1.y), nc = v3(p1.z, p1.w, p2.x);
+    const V2 t_a = { p2.y, p2.z }, t_b = { p2.w, p3.x }, t_c = { p3.y, p3.z };
+    const int tag = __float_as_int(tb.w);
+    info->rank = rank; info->object = tag & 0xff; info->preset = (tag >> 8) & 0xff;
+    info->a = a; info->b = b; info->c = c;
+
+    const V3 e0 = vsub(b, a), e1 = vsub(c, a), p = vsub(point, a);
+    const float d00 = vdot(e0, e0), d11 = vdot(e1, e1), d01 = vdot(e0, e1);
+    const float dp0 = vdot(p, e0), dp1 = vdot(p, e1);
+    const float div = d00 * d11 - d01 * d01;
+    const float ux = (d11 * dp0 - d01 * dp1) / div;
+    const float uy = (d00 * dp1 - d01 * dp0) / div;
+    const float uw = 1 - ux - uy;
+    TbSurface s;
+    s.n = vnorm(vadd(vadd(vmul(nc, uy), vmul(nb, ux)), vmul(na, uw)));
+    V2 tex;
+    tex.x = (t_c.x * uy + t_b.x * ux) + t_a.x * uw;
+    tex.y = (t_c.y * uy + t_b.y * ux) + t_a.y * uw;
+    info->texcoord = tex;
+    const TbDevMaterial* m = sc.materials + info->object;
+    const int cnt = m->attr_count;
+    s.a0 = cnt > 0 ? tb_attr_eval(m->attr[0], sc.textures, tex, point) : v3s(0.f);
+    s.a1 = cnt > 1 ? tb_attr_eval(m->attr[1], sc.textures, tex, point) : v3s(0.f);
+    s.a2 = cnt > 2 ? tb_attr_eval(m->attr[2], sc.textures, tex, point) : v3s(0.f);
+    s.state = 0.f;
+    if (info->preset == TB_PRESET_PHONG && cnt > 3) s.state = tb_attr_eval(m->attr[3], sc.textures, tex, point).x;
+    if (info->preset == TB_PRESET_GLASS) s.state = s.a2.x;
+    s.emissive = tb_attr_eval(m->emissive, sc.textures, tex, point);
+    s.xf = basis_from_normal(s.n);
+    return s;
+}
+
+// ==================================================================================== K4: shade
+struct TbShadeArgs {
+    TbDevScene sc;
+    float4 *ray_o, *ray_d, *thr, *lo;
+    const float4* hit;
+    float4 *aux_o, *aux_d;
+    const float4* aux_hit;
+    const int* q;              // slots of this preset
+    const int* q_count;
+    int*  next_q;              // live paths for the next bounce
+    int*  next_count;
+    int*  auxq;                // visibility rays to trace between the two stages
+    int*  aux_count;
+    int   bounce;
+};
+
+// Warp-aggregated append; every lane of the warp must call it (full mask).
+__device__ __forceinline__ int tb_append(int* counter, bool pred) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (!m) return -1;
+    int base = 0;
+    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    return pred ? base + __popc(m & ((1u << lane) - 1u)) : -1;
+}
+
+// One explicit light sample: terra_scene_pick_light + terra_light_pick_triangle +
+// terra_light_sample_triangle (Terra.c:1592-1621, 1662-1697), randoms as at :1370-1388.
+struct TbLightSample { int light, tri; uint32_t rank; V3 pos, norm; float tri_area; };
+
+__device__ __forceinline__ TbLightSample tb_sample_light(const TbDevScene& sc, uint64_t key, uint32_t dim0) {
+    TbLightSample ls;
+    const float e_pick = (float)((double)tb_randf_libc(key, dim0 + TB_DIM_LIGHT_PICK) - TB_EPS_D);
+    long long li = (long long)((double)e_pick * (double)sc.n_lights);
+    if (li < 0) li = 0;
+    if (li > sc.n_lights - 1) li = sc.n_lights - 1;         // e == 1.0 would index past the table in the reference
+    const TbDevLight L = sc.lights[li];
+    const float e_tri = tb_randf_libc(key, dim0 + TB_DIM_TRI_PICK);
+    long long ti = (long long)(e_tri * (float)L.tri_count);
+    if (ti > (long long)L.tri_count - 1) ti = (long long)L.tri_count - 1;
+    ls.light = (int)li; ls.tri = (int)ti;
+    ls.rank = sc.light_tri_rank[L.tri_base + ti];
+    ls.tri_area = sc.light_tri_area[L.tri_base + ti];
+    const float e1 = tb_randf_libc(key, dim0 + TB_DIM_LIGHT_U), e2 = tb_randf_libc(key, dim0 + TB_DIM_LIGHT_V);
+    const float s = sqrtf(e1);
+    const float a = 1 - s, b = e2 * s, c = 1 - a - b;
+    const float4* tp = sc.tris + (size_t)ls.rank * 3;
+    const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
+    ls.pos = vadd(vadd(vmul(v3(ta.x, ta.y, ta.z), a), vmul(v3(tb.x, tb.y, tb.z), b)), vmul(v3(tc.x, tc.y, tc.z), c));
+    const float4* pp = sc.props + (size_t)ls.rank * 4;
+    const float4 p0 = __ldg(pp), p1 = __ldg(pp + 1), p2 = __ldg(pp + 2);
+    const V3 na = v3(p0.x, p0.y, p0.z), nb = v3(p0.w, p1.x, p1.y), nc = v3(p1.z, p1.w, p2.x);
+    ls.norm = vnorm(vadd(vadd(vmul(na, a), vmul(nb, b)), vmul(nc, c)));
+    return ls;
+}
+
+// terra_surface_ray, Terra.c:1715-1724 (sign = +1)
+__device__ __forceinline__ V3 tb_surface_ray_origin(const TbSurface& s, V3 point) { return vadd(point, vmul(s.n, 0.0001f * 1.f)); }
+
+template <int PRESET, int STAGE>
+__global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
+    const int count = *a.q_count;
+    const int stride = gridDim.x * blockDim.x;
+    const int rounds = (count + stride - 1) / stride;
+    const TbDevScene& sc = a.sc;
+    for (int it = 0; it < rounds; ++it) {
+        const int i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const bool valid = i < count;
+        bool alive = false, want_aux0 = false, want_aux1 = false;
+        int slot = 0;
+        V3 next_o = v3s(0.f), next_d = v3s(0.f), aux0_d = v3s(0.f), aux1_d = v3s(0.f), aux_o = v3s(0.f);
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4;
+        if (valid) {
+            slot = a.q[i];
+            o4 = a.ray_o[slot]; d4 = a.ray_d[slot];
+            const float4 h4 = a.hit[slot];
+            const uint64_t key = ((uint64_t)__float_as_uint(d4.w) << 32) | __float_as_uint(o4.w);
+            const uint32_t dim0 = 2u + (uint32_t)a.bounce * TB_DIMS_PER_BOUNCE;
+            const V3 d = v3(d4.x, d4.y, d4.z);
+            const V3 ro = tb_offset_origin(v3(o4.x, o4.y, o4.z), d);
+            const V3 point = vadd(ro, vmul(d, h4.x));                        // terra_ray_pos, TerraGeometry.c:9-12
+            TbHitInfo info;
+            TbSurface s = tb_surface_init(sc, __float_as_int(h4.y), point, &info);
+            const V3 wo = vneg(d);
+            const int integ = sc.integrator;
+            const bool direct = integ == kTerraIntegratorDirect || integ == kTerraIntegratorDirectMis;
+            const bool mis = integ == kTerraIntegratorDirectMis;
+
+            if (STAGE == 0) {
+                // ---- emit the visibility rays of terra_integrate_direct / _direct_mis
+                if (direct && sc.n_lights > 0) {
+                    aux_o = tb_surface_ray_origin(s, point);
+                    if (mis) {
+                        aux1_d = tb_bsdf_sample(PRESET, s, tb_randf_libc(key, dim0 + TB_DIM_MIS0), tb_randf_libc(key, dim0 + TB_DIM_MIS1),
+                                                tb_randf_libc(key, dim0 + TB_DIM_MIS2), wo);
+                        want_aux1 = true;
+                    }
+                    const TbLightSample ls = tb_sample_light(sc, key, dim0);
+                    aux0_d = vnorm(vsub(ls.pos, point));
+                    want_aux0 = true;
+                }
+            } else {
+                // ---- terra_integrate (Terra.c:1099-1138)
+                const float4 t4 = a.thr[slot];
+                V3 thr = v3(t4.x, t4.y, t4.z);
+                V3 Lo = v3s(0.f);
+                if (!direct) {                                                 // simple, :1339-1347
+                    if (vdot(wo, s.n) > 0) Lo = vpoint(s.emissive, thr);
+                } else {
+                    if (a.bounce == 0 && vdot(wo, s.n) > 0) Lo = vadd(Lo, s.emissive);
+                    if (sc.n_lights > 0) {
+                        V3 bsdf_sample = v3s(0.f);
+                        if (mis) bsdf_sample = tb_bsdf_sample(PRESET, s, tb_randf_libc(key, dim0 + TB_DIM_MIS0), tb_randf_libc(key, dim0 + TB_DIM_MIS1),
+                                                              tb_randf_libc(key, dim0 + TB_DIM_MIS2), wo);
+                        const TbLightSample ls = tb_sample_light(sc, key, dim0);
+                        const float light_pick_pdf = 1.f / (float)sc.lights_triangles_count;
+                        const V3 p_to_light = vsub(ls.pos, point);
+                        const V3 wi = vnorm(p_to_light);
+                        const float4 ah = a.aux_hit[(size_t)slot * 2];
+                        if (ah.x >= 0.f && (uint32_t)__float_as_int(ah.y) == ls.rank) {      // same object AND triangle, :1403
+                            const float cosl = vdot(vneg(wi), ls.norm);
+                            if (cosl > 0) {
+                                const V3 lo_ = tb_offset_origin(tb_surface_ray_origin(s, point), wi);
+                                const V3 lpoint = vadd(lo_, vmul(wi, ah.x));
+                                TbHitInfo linfo;
+                                const TbSurface lsurf = tb_surface_init(sc, (int)ls.rank, lpoint, &linfo);
+                                const float light_pdf = vsqlen(p_to_light) / fabsf(cosl * ls.tri_area);
+                                if (!mis) {                                    // :1417-1422
+                                    const V3 f = tb_bsdf_eval(PRESET, s, wi, wo);
+                                    V3 Ld = vpoint(lsurf.emissive, f);
+                                    Ld = vmul(Ld, vdot(wi, s.n) / (light_pdf * light_pick_pdf));
+                                    Lo = vadd(Lo, Ld);
+                                } else {                                       // :1505-1514
+                                    const float bsdf_pdf = tb_bsdf_pdf(PRESET, s, wi, wo);
+                                    const float weight = (light_pdf * light_pdf) / (light_pdf * light_pdf + bsdf_pdf * bsdf_pdf);
+                                    if (light_pdf != 0) {
+                                        const V3 f = tb_bsdf_eval(PRESET, s, wi, wo);
+                                        V3 L = vpoint(lsurf.emissive, f);
+                                        L = vmul(L, vdot(wi, s.n) * weight / (light_pdf * light_pick_pdf));
+                                        Lo = vadd(Lo, L);
+                                    }
+                                }
+                            }
+                        }
+                        if (mis) {                                             // :1517-1583
+                            const V3 wi2 = bsdf_sample;
+                            const V3 f = tb_bsdf_eval(PRESET, s, wi2, wo);
+                            const float bsdf_pdf = tb_bsdf_pdf(PRESET, s, wi2, wo);
+                            const float4 bh = a.aux_hit[(size_t)slot * 2 + 1];
+                            if (bh.x >= 0.f) {
+                                const V3 bo = tb_offset_origin(tb_surface_ray_origin(s, point), wi2);
+                                const V3 bpoint = vadd(bo, vmul(wi2, bh.x));
+                                TbHitInfo binfo;
+                                const TbSurface bsurf = tb_surface_init(sc, __float_as_int(bh.y), bpoint, &binfo);
+                                if (binfo.object == sc.lights[ls.light].object) {
+                                    const float NoW = vdot(bsurf.n, vneg(wi2));
+                                    if (NoW > 0) {
+                                        const float dist = vsqdist(bpoint, point);
+                                        const V3 ab = vsub(binfo.b, binfo.a), ac = vsub(binfo.c, binfo.a);
+                                        const float area = vlen(vcross(ab, ac)) / 2;            // terra_triangle_area, :1833-1838
+                                        const float light_pdf = dist / (NoW * area);
+                                        const float weight = (bsdf_pdf * bsdf_pdf) / (light_pdf * light_pdf + bsdf_pdf * bsdf_pdf);
+                                        if (bsdf_pdf != 0) {
+                                            V3 L = vpoint(bsurf.emissive, f);
+                                            L = vmul(L, vdot(wi2, s.n) * weight / bsdf_pdf);
+                                            Lo = vadd(Lo, L);
+                                        }
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    Lo = vpoint(Lo, thr);
+                }
+                if (Lo.x != 0.f || Lo.y != 0.f || Lo.z != 0.f) {
+                    const float4 l4 = a.lo[slot];
+                    a.lo[slot] = make_float4(l4.x + Lo.x, l4.y + Lo.y, l4.z + Lo.z, 0.f);   // Lo = Lo + radiance, :1063
+                }
+                // ---- continue the path (terra_trace, Terra.c:1065-1093)
+                if (a.bounce < sc.bounces) {
+                    const float e0 = tb_randf_libc(key, dim0 + TB_DIM_BSDF0), e1 = tb_randf_libc(key, dim0 + TB_DIM_BSDF1);
+                    const float e2 = tb_randf_libc(key, dim0 + TB_DIM_BSDF2);
+                    const V3 wi = tb_bsdf_sample(PRESET, s, e0, e1, e2, wo);
+                    const float pdf = tmaxf(tb_bsdf_pdf(PRESET, s, wi, wo), TB_EPS_F);
+                    V3 f = tb_bsdf_eval(PRESET, s, wi, wo);
+                    f = vmul(f, 1.f / pdf);
+                    thr = vpoint(thr, f);
+                    thr = vmul(thr, vdot(s.n, wi));
+                    const float p = tmaxf(thr.x, tmaxf(thr.y, thr.z));
+                    const float e3 = tb_randf_libc(key, dim0 + TB_DIM_RR);
+                    if (!(e3 > p)) {
+                        thr = vmul(thr, (float)(1.f / ((double)p + TB_EPS_D)));
+                        a.thr[slot] = make_float4(thr.x, thr.y, thr.z, 0.f);
+                        next_o = tb_surface_ray_origin(s, point);
+                        next_d = wi;
+                        alive = true;
+                    }
+                }
+            }
+        }
+        if (STAGE == 0) {
+            const int i0 = tb_append(a.aux_count, want_aux0);
+            if (want_aux0) {
+                a.aux_o[(size_t)slot * 2] = make_float4(aux_o.x, aux_o.y, aux_o.z, 0.f);
+                a.aux_d[(size_t)slot * 2] = make_float4(aux0_d.x, aux0_d.y, aux0_d.z, 0.f);
+                a.auxq[i0] = slot * 2;
+            }
+            const int i1 = tb_append(a.aux_count, want_aux1);
+            if (want_aux1) {
+                a.aux_o[(size_t)slot * 2 + 1] = make_float4(aux_o.x, aux_o.y, aux_o.z, 0.f);
+                a.aux_d[(size_t)slot * 2 + 1] = make_float4(aux1_d.x, aux1_d.y, aux1_d.z, 0.f);
+                a.auxq[i1] = slot * 2 + 1;
+            }
+        } else {
+            const int at = tb_append(a.next_count, alive);
+            if (alive) {
+                a.ray_o[slot] = make_float4(next_o.x, next_o.y, next_o.z, o4.w);
+                a.ray_d[slot] = make_float4(next_d.x, next_d.y, next_d.z, d4.w);
+                a.next_q[at] = slot;
+            }
+        }
+    }
+}
+
+// ==================================================================================== K6: accumulate + tonemap
+// Terra.c:551-567: acc = sum over the pixel's samples in sample order (one thread per pixel, so
+// the float sum order is the reference's and the result is deterministic — no atomics).
+__global__ void __launch_bounds__(256) k_accumulate(TbBatch b, const float4* lo, float4* acc) {
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < b.n_pixels; p += gridDim.x * blockDim.x) {
+        float4 s = acc[b.p0 + p];
+        for (int k = 0; k < b.n_samples; ++k) {
+            const float4 l = lo[(size_t)k * b.n_pixels + p];
+            s.x = s.x + l.x; s.y = s.y + l.y; s.z = s.z + l.z;
+        }
+        acc[b.p0 + p] = s;
+    }
+}
+
+__device__ __forceinline__ V3 tb_uncharted2(V3 x) {                          // Terra.c:1815-1828
+    const float A = 0.15f, B = 0.5f, C = 0.1f, D = 0.2f, E = 0.02f, F = 0.3f;
+    V3 r;
+    r.x = ((x.x * (A * x.x + C * B) + D * E) / (x.x * (A * x.x + B) + D * F)) - E / F;
+    r.y = ((x.y * (A * x.y + C * B) + D * E) / (x.y * (A * x.y + B) + D * F)) - E / F;
+    r.z = ((x.z * (A * x.z + C * B) + D * E) / (x.z * (A * x.z + B) + D * F)) - E / F;
+    return r;
+}
+
+__device__ __forceinline__ V3 tb_tonemap(V3 color, int op, float inv_gamma) {    // Terra.c:578-627
+    switch (op) {
+        case kTerraTonemappingOperatorLinear:
+            return v3(powf(color.x, inv_gamma), powf(color.y, inv_gamma), powf(color.z, inv_gamma));
+        case kTerraTonemappingOperatorReinhard:
+            color.x = color.x / (1.f + color.x);
+            color.y = color.y / (1.f + color.y);
+            color.z = color.z / (1.f + color.z);
+            return v3(powf(color.x, inv_gamma), powf(color.y, inv_gamma), powf(color.z, inv_gamma));
+        case kTerraTonemappingOperatorFilmic: {
+            V3 x = v3(tmaxf(0.f, color.x - 0.004f), tmaxf(0.f, color.y - 0.004f), tmaxf(0.f, color.z - 0.004f));
+            color.x = (x.x * (6.2f * x.x + 0.5f)) / (x.x * (6.2f * x.x + 1.7f) + 0.06f);
+            color.y = (x.y * (6.2f * x.y + 0.5f)) / (x.y * (6.2f * x.y + 1.7f) + 0.06f);
+            color.x = (x.z * (6.2f * x.z + 0.5f)) / (x.z * (6.2f * x.z + 1.7f) + 0.06f);   // sic: .x twice, .z untouched
+            return color;
+        }
+        case kTerraTonemappingOperatorUncharted2: {
+            V3 white_scale = tb_uncharted2(v3s(11.2f));
+            white_scale = v3(1.f / white_scale.x, 1.f / white_scale.y, 1.f / white_scale.z);
+            V3 t = tb_uncharted2(vmul(color, 2.f));
+            color = vpoint(t, white_scale);
+            return v3(powf(color.x, inv_gamma), powf(color.y, inv_gamma), powf(color.z, inv_gamma));
+        }
+        default:
+            return color;
+    }
+}
+
+// Terra.c:569-630 for a w x h region: results += (acc, spp); pixels = tonemap(acc / samples * exposure).
+struct TbFinalizeArgs {
+    const float4* acc;         // region-linear
+    TerraRawIntegrationResult* results; size_t results_pitch;   // element pitch; points at the region's first pixel
+    float* pixels; size_t pixels_pitch;                         // may be NULL
+    int w, h, spp, tonemap;
+    float exposure, inv_gamma;
+};
+__global__ void __launch_bounds__(256) k_finalize(TbFinalizeArgs a) {
+    const int n = a.w * a.h;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const int i = p / a.w, j = p - i * a.w;
+        TerraRawIntegrationResult* r = a.results + (size_t)i * a.results_pitch + j;
+        const float4 s = a.acc[p];
+        const V3 acc = v3(s.x + r->acc.x, s.y + r->acc.y, s.z + r->acc.z);
+        const int samples = r->samples + a.spp;
+        r->acc.x = acc.x; r->acc.y = acc.y; r->acc.z = acc.z;
+        r->samples = samples;
+        if (a.pixels) {
+            V3 color = vmul(vdiv(acc, (float)samples), a.exposure);
+            color = tb_tonemap(color, a.tonemap, a.inv_gamma);
+            float* px = a.pixels + ((size_t)i * a.pixels_pitch + j) * 3;
+            px[0] = color.x; px[1] = color.y; px[2] = color.z;
+        }
+    }
+}
+__global__ void __launch_bounds__(256) k_resolve(const TerraRawIntegrationResult* results, float* pixels, size_t n,
+                                                 int tonemap, float exposure, float inv_gamma) {
+    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (size_t)gridDim.x * blockDim.x) {
+        const TerraRawIntegrationResult r = results[p];
+        V3 color = vmul(vdiv(v3(r.acc.x, r.acc.y, r.acc.z), (float)r.samples), exposure);
+        color = tb_tonemap(color, tonemap, inv_gamma);
+        pixels[3 * p] = color.x; pixels[3 * p + 1] = color.y; pixels[3 * p + 2] = color.z;
+    }
+}
+
+// ==================================================================================== BSDF known-answer kernel
+__global__ void k_bsdf_kat(TbDevScene sc, int object, size_t n, const float* e123, const float* wo3, const float* n3, float* out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const TbDevMaterial* m = sc.materials + object;
+        TbSurface s;
+        s.n = v3(n3[3 * i], n3[3 * i + 1], n3[3 * i + 2]);
+        s.xf = basis_from_normal(s.n);
+        V2 uv = { 0.f, 0.f };
+        s.a0 = tb_attr_eval(m->attr[0], sc.textures, uv, s.n);
+        s.a1 = tb_attr_eval(m->attr[1], sc.textures, uv, s.n);
+        s.a2 = tb_attr_eval(m->attr[2], sc.textures, uv, s.n);
+        s.emissive = v3s(0.f);
+        s.state = 0.f;
+        if (m->preset == TB_PRESET_PHONG) s.state = tb_attr_eval(m->attr[3], sc.textures, uv, s.n).x;
+        if (m->preset == TB_PRESET_GLASS) s.state = s.a2.x;
+        const V3 wo = v3(wo3[3 * i], wo3[3 * i + 1], wo3[3 * i + 2]);
+        const V3 wi = tb_bsdf_sample(m->preset, s, e123[3 * i], e123[3 * i + 1], e123[3 * i + 2], wo);
+        const float pdf = tb_bsdf_pdf(m->preset, s, wi, wo);
+        const V3 f = tb_bsdf_eval(m->preset, s, wi, wo);
+        float* o = out + 8 * i;
+        o[0] = wi.x; o[1] = wi.y; o[2] = wi.z; o[3] = pdf; o[4] = f.x; o[5] = f.y; o[6] = f.z; o[7] = s.state;
+    }
+}
+
+// ==================================================================================== host-side launchers
+// counters layout (ints): [0] trace fetch cursor  [1] live paths this bounce  [2] live paths next bounce
+// [3] visibility rays  [4..7] per-preset hit counts  [8..9] u64 rays traced (statistics)
+__global__ void k_counters(int* c, int mode, int value) {
+    unsigned long long* rays = (unsigned long long*)(c + 8);
+    switch (mode) {
+        case 0: c[0] = 0; c[1] = value; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; break;   // new wave
+        case 1: c[0] = 0; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)c[1]; break;   // bounce begins
+        case 2: c[0] = 0; *rays += (unsigned long long)c[3]; break;                                  // before the visibility trace
+        case 3: c[1] = c[2]; break;                                                                  // bounce ends
+        case 4: *rays += (unsigned long long)value; c[0] = 0; break;                                 // stand-alone trace of `value` rays
+        default: *rays = 0; break;
+    }
+}
+
+static size_t tb_batch_capacity() {
+    const char* e = getenv("TERRA_B200_BATCH");
+    size_t cap = e ? (size_t)strtoull(e, NULL, 10) : ((size_t)1 << 22);
+    if (cap < 1024) cap = 1024;
+    if (cap > ((size_t)1 << 28)) cap = (size_t)1 << 28;
+    return cap;
+}
+
+static TbEventPair* tb_event_pair(TbDevice* d) {
+    if (d->ev_used == d->ev_pool.size()) {
+        TbEventPair e;
+        TB_CUDA(cudaEventCreate(&e.a));
+        TB_CUDA(cudaEventCreate(&e.b));
+        d->ev_pool.push_back(e);
+    }
+    return &d->ev_pool[d->ev_used++];
+}
+
+// Sum the device times of the trace launches recorded since the last drain. Stream must be idle.
+static void tb_drain_events(TbDevice* d) {
+    for (size_t i = 0; i < d->ev_used; ++i) {
+        float ms = 0.f;
+        TB_CUDA(cudaEventElapsedTime(&ms, d->ev_pool[i].a, d->ev_pool[i].b));
+        d->stats.trace_kernel_ms += ms;
+        d->stats.trace_kernel_launches += 1;
+    }
+    d->ev_used = 0;
+}
+
+static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a) {
+    TbEventPair* e = tb_event_pair(d);
+    TB_CUDA(cudaEventRecord(e->a, st));
+    k_trace<<<d->sm_count * TB_TRACE_CTAS_PER_SM, TB_TRACE_THREADS, 0, st>>>(a);
+    TB_CUDA(cudaEventRecord(e->b, st));
+    d->stats.kernel_launches += 1;
+}
+
+typedef void (*TbShadeKernel)(TbShadeArgs);
+static TbShadeKernel tb_shade_kernel(int preset, int stage) {
+    static const TbShadeKernel table[TB_PRESET_COUNT][2] = {
+        { k_shade<0, 0>, k_shade<0, 1> }, { k_shade<1, 0>, k_shade<1, 1> },
+        { k_shade<2, 0>, k_shade<2, 1> }, { k_shade<3, 0>, k_shade<3, 1> } };
+    return table[preset][stage];
+}
+
+// All waves of one region: adds `spp` samples per pixel into d_acc (region-linear float4, zeroed by the caller).
+static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* cam, size_t fbw, size_t fbh,
+                             size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
+                             uint64_t seed, float4* d_acc) {
+    const size_t npx = w * h;
+    const size_t cap = tb_batch_capacity();
+    const size_t px_per_wave = npx < cap ? npx : cap;
+    size_t s_per_wave = npx < cap ? cap / npx : 1;
+    if (s_per_wave > spp) s_per_wave = spp;
+    if (s_per_wave < 1) s_per_wave = 1;
+    tb_wave_reserve(&d->wave, px_per_wave * s_per_wave);
+    TbWave& wv = d->wave;
+    const TbDevScene& sc = d->sc;
+    const bool direct = sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis;
+    if (sc.integrator > kTerraIntegratorDirectMis) {
+        terra_log("terra_b200: integrator %d (debug views) is not implemented on the GPU path\n", sc.integrator);
+        abort();
+    }
+    const int shade_grid = d->sm_count * 4;
+    for (size_t p0 = 0; p0 < npx; p0 += px_per_wave) {
+        const size_t np = npx - p0 < px_per_wave ? npx - p0 : px_per_wave;
+        for (size_t s0 = 0; s0 < spp; s0 += s_per_wave) {
+            const size_t ns = spp - s0 < s_per_wave ? spp - s0 : s_per_wave;
+            TbBatch b;
+            b.x = (int)x; b.y = (int)y; b.w = (int)w; b.h = (int)h; b.fbw = (int)fbw; b.fbh = (int)fbh;
+            b.p0 = (int)p0; b.n_pixels = (int)np; b.s0 = (int)s0; b.n_samples = (int)ns;
+            b.sample_base = (uint32_t)sample_base; b.seed = seed;
+            const int n_paths = (int)(np * ns);
+            TbRaygenArgs rg;
+            rg.batch = b; rg.cam = *cam; rg.jitter = sc.jitter;
+            rg.ray_o = wv.ray_o; rg.ray_d = wv.ray_d; rg.thr = wv.thr; rg.lo = wv.lo; rg.queue = wv.queue[0];
+            k_counters<<<1, 1, 0, st>>>(wv.counters, 0, n_paths);
+            k_raygen<<<d->sm_count * 8, 256, 0, st>>>(rg);
+            d->stats.kernel_launches += 2;
+            int cur = 0;
+            for (int bounce = 0; bounce <= sc.bounces; ++bounce) {
+                k_counters<<<1, 1, 0, st>>>(wv.counters, 1, 0);
+                TbTraceArgs ta;
+                memset(&ta, 0, sizeof ta);
+                ta.nodes = sc.nodes; ta.tris = sc.tris;
+                ta.ray_o = wv.ray_o; ta.ray_d = wv.ray_d;
+                ta.queue = wv.queue[cur]; ta.count_ptr = wv.counters + 1; ta.cursor = wv.counters;
+                ta.hit_out = wv.hit;
+                ta.matq = wv.matq; ta.matq_count = wv.counters + 4; ta.matq_stride = (int)wv.capacity;
+                ta.emit_prim = 0;
+                tb_launch_trace(d, st, ta);
+                d->stats.kernel_launches += 1;
+                TbShadeArgs sa;
+                sa.sc = sc;
+                sa.ray_o = wv.ray_o; sa.ray_d = wv.ray_d; sa.thr = wv.thr; sa.lo = wv.lo; sa.hit = wv.hit;
+                sa.aux_o = wv.aux_o; sa.aux_d = wv.aux_d; sa.aux_hit = wv.aux_hit;
+                sa.next_q = wv.queue[cur ^ 1]; sa.next_count = wv.counters + 2;
+                sa.auxq = wv.auxq; sa.aux_count = wv.counters + 3;
+                sa.bounce = bounce;
+                if (direct && sc.n_lights > 0) {
+                    for (int p = 0; p < TB_PRESET_COUNT; ++p) {
+                        if (!(sc.preset_mask & (1 << p))) continue;
+                        sa.q = wv.matq + (size_t)p * wv.capacity; sa.q_count = wv.counters + 4 + p;
+                        tb_shade_kernel(p, 0)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
+                        d->stats.kernel_launches += 1;
+                    }
+                    k_counters<<<1, 1, 0, st>>>(wv.counters, 2, 0);
+                    TbTraceArgs xa;
+                    memset(&xa, 0, sizeof xa);
+                    xa.nodes = sc.nodes; xa.tris = sc.tris;
+                    xa.ray_o = wv.aux_o; xa.ray_d = wv.aux_d;
+                    xa.queue = wv.auxq; xa.count_ptr = wv.counters + 3; xa.cursor = wv.counters;
+                    xa.hit_out = wv.aux_hit;
+                    xa.emit_prim = 0;
+                    tb_launch_trace(d, st, xa);
+                    d->stats.kernel_launches += 1;
+                }
+                for (int p = 0; p < TB_PRESET_COUNT; ++p) {
+                    if (!(sc.preset_mask & (1 << p))) continue;
+                    sa.q = wv.matq + (size_t)p * wv.capacity; sa.q_count = wv.counters + 4 + p;
+                    tb_shade_kernel(p, 1)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
+                    d->stats.kernel_launches += 1;
+                }
+                k_counters<<<1, 1, 0, st>>>(wv.counters, 3, 0);
+                d->stats.kernel_launches += 1;
+                cur ^= 1;
+            }
+            k_accumulate<<<d->sm_count * 4, 256, 0, st>>>(b, wv.lo, d_acc);
+            d->stats.kernel_launches += 1;
+            d->stats.paths_traced += (uint64_t)n_paths;
+        }
+    }
+    TB_CUDA(cudaGetLastError());
+}
+
+// ==================================================================================== entry points
+static void tb_finish_call(TbDevice* d, cudaStream_t st, bool whole_render) {
+    if (whole_render) TB_CUDA(cudaEventRecord(d->ev_call_b, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    TB_CUDA(cudaGetLastError());
+    if (whole_render) {
+        float ms = 0.f;
+        TB_CUDA(cudaEventElapsedTime(&ms, d->ev_call_a, d->ev_call_b));
+        d->stats.render_ms += ms;
+    }
+    tb_drain_events(d);
+}
+
+extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const TerraFramebuffer* fb,
+                                 size_t x, size_t y, size_t w, size_t h, size_t spp, uint64_t seed) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    const size_t npx = w * h;
+    if (npx > d->fb_capacity) {
+        tb_free(d->d_results); tb_free(d->d_pixels); tb_free(d->d_acc);
+        d->d_results = tb_alloc<TerraRawIntegrationResult>(npx);
+        d->d_pixels = tb_alloc<float>(npx * 3);
+        d->d_acc = tb_alloc<float4>(npx);
+        d->fb_capacity = npx;
+    }
+    TB_CUDA(cudaEventRecord(d->ev_call_a, st));
+    // progressive accumulation: the caller's results[] are the state (Terra.c:570-572), so they go up first
+    TB_CUDA(cudaMemcpy2DAsync(d->d_results, w * sizeof(TerraRawIntegrationResult),
+                              fb->results + y * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
+                              w * sizeof(TerraRawIntegrationResult), h, cudaMemcpyHostToDevice, st));
+    d->stats.h2d_bytes += npx * sizeof(TerraRawIntegrationResult);
+    TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
+    tb_render_region(d, st, cam, fb->width, fb->height, x, y, w, h, 0, spp, seed, d->d_acc);
+    TbFinalizeArgs fa;
+    fa.acc = d->d_acc;
+    fa.results = d->d_results; fa.results_pitch = w;
+    fa.pixels = d->d_pixels; fa.pixels_pitch = w;
+    fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = d->sc.tonemap;
+    fa.exposure = d->sc.exposure; fa.inv_gamma = d->sc.inv_gamma;
+    k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
+    d->stats.kernel_launches += 1;
+    TB_CUDA(cudaMemcpy2DAsync(fb->results + y * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
+                              d->d_results, w * sizeof(TerraRawIntegrationResult),
+                              w * sizeof(TerraRawIntegrationResult), h, cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaMemcpy2DAsync(fb->pixels + y * fb->width + x, fb->width * sizeof(TerraFloat3),
+                              d->d_pixels, w * sizeof(TerraFloat3), w * sizeof(TerraFloat3), h, cudaMemcpyDeviceToHost, st));
+    d->stats.d2h_bytes += npx * (sizeof(TerraRawIntegrationResult) + sizeof(TerraFloat3));
+    tb_finish_call(d, st, true);
+}
+
+extern "C" void tb_device_render_resident(TbDevice* d, const TbCameraFrame* cam, size_t fbw, size_t fbh,
+                                          size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
+                                          uint64_t seed, void* d_results, void* stream) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    const size_t npx = w * h;
+    if (npx > d->acc_capacity) {
+        tb_free(d->d_acc);
+        d->d_acc = tb_alloc<float4>(npx > d->fb_capacity ? npx : d->fb_capacity);
+        d->acc_capacity = npx > d->fb_capacity ? npx : d->fb_capacity;
+        if (d->fb_capacity < npx) { tb_free(d->d_results); tb_free(d->d_pixels); d->d_results = NULL; d->d_pixels = NULL; d->fb_capacity = 0; }
+    }
+    TB_CUDA(cudaEventRecord(d->ev_call_a, st));
+    TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
+    tb_render_region(d, st, cam, fbw, fbh, x, y, w, h, sample_base, spp, seed, d->d_acc);
+    TbFinalizeArgs fa;
+    fa.acc = d->d_acc;
+    fa.results = (TerraRawIntegrationResult*)d_results + y * fbw + x; fa.results_pitch = fbw;
+    fa.pixels = NULL; fa.pixels_pitch = 0;
+    fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = 0; fa.exposure = 1.f; fa.inv_gamma = 1.f;
+    k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
+    d->stats.kernel_launches += 1;
+    tb_finish_call(d, st, true);
+}
+
+extern "C" void tb_device_resolve(TbDevice* d, size_t fbw, size_t fbh, const void* d_results, void* d_pixels, void* stream) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    k_resolve<<<d->sm_count * 4, 256, 0, st>>>((const TerraRawIntegrationResult*)d_results, (float*)d_pixels, fbw * fbh,
+                                               d->sc.tonemap, d->sc.exposure, d->sc.inv_gamma);
+    d->stats.kernel_launches += 1;
+    TB_CUDA(cudaStreamSynchronize(st));
+}
+
+static void tb_trace_generic(TbDevice* d, cudaStream_t st, size_t n, const float4* d_o, const float4* d_d, float4* d_hit) {
+    k_counters<<<1, 1, 0, st>>>(d->wave.counters, 4, (int)n);
+    TbTraceArgs ta;
+    memset(&ta, 0, sizeof ta);
+    ta.nodes = d->sc.nodes; ta.tris = d->sc.tris;
+    ta.ray_o = d_o; ta.ray_d = d_d;
+    ta.count = (int)n; ta.cursor = d->wave.counters;
+    ta.hit_out = d_hit;
+    ta.emit_prim = 1;
+    tb_launch_trace(d, st, ta);
+    d->stats.kernel_launches += 1;
+}
+
+static void tb_io_reserve(TbDevice* d, size_t n) {
+    if (n <= d->io_capacity) return;
+    tb_free(d->d_io_o); tb_free(d->d_io_d); tb_free(d->d_io_hit);
+    d->d_io_o = tb_alloc<float4>(n);
+    d->d_io_d = tb_alloc<float4>(n);
+    d->d_io_hit = tb_alloc<TerraB200Hit>(n);
+    d->io_capacity = n;
+}
+
+extern "C" void tb_device_trace_resident(TbDevice* d, size_t n, const void* d_o, const void* d_d, void* d_hits, void* stream) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    const size_t chunk = (size_t)1 << 30;
+    for (size_t at = 0; at < n; at += chunk) {
+        const size_t m = n - at < chunk ? n - at : chunk;
+        tb_trace_generic(d, st, m, (const float4*)d_o + at, (const float4*)d_d + at, (float4*)d_hits + at);
+    }
+    tb_finish_call(d, st, false);
+}
+
+extern "C" void tb_device_trace_host(TbDevice* d, size_t n, const float* origins, const float* dirs, TerraB200Hit* out) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    const size_t chunk = (size_t)1 << 24;
+    tb_io_reserve(d, n < chunk ? n : chunk);
+    // the xyz staging reuses the tail of the hit buffer: 16 B/ray >= 12 B/ray
+    float* d_o3 = NULL; float* d_d3 = NULL;
+    TB_CUDA(cudaMalloc((void**)&d_o3, (n < chunk ? n : chunk) * 12));
+    TB_CUDA(cudaMalloc((void**)&d_d3, (n < chunk ? n : chunk) * 12));
+    for (size_t at = 0; at < n; at += chunk) {
+        const size_t m = n - at < chunk ? n - at : chunk;
+        TB_CUDA(cudaMemcpyAsync(d_o3, origins + 3 * at, m * 12, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(d_d3, dirs + 3 * at, m * 12, cudaMemcpyHostToDevice, st));
+        k_pack_rays<<<d->sm_count * 8, 256, 0, st>>>(m, d_o3, d_d3, d->d_io_o, d->d_io_d);
+        d->stats.kernel_launches += 1;
+        tb_trace_generic(d, st, m, d->d_io_o, d->d_io_d, (float4*)d->d_io_hit);
+        TB_CUDA(cudaMemcpyAsync(out + at, d->d_io_hit, m * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, st));
+        d->stats.h2d_bytes += m * 24;
+        d->stats.d2h_bytes += m * sizeof(TerraB200Hit);
+    }
+    tb_finish_call(d, st, false);
+    TB_CUDA(cudaFree(d_o3));
+    TB_CUDA(cudaFree(d_d3));
+}
+
+extern "C" void tb_device_primary_hits(TbDevice* d, const TbCameraFrame* cam, size_t w, size_t h, TerraB200Hit* out) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    const size_t n = w * h;
+    tb_io_reserve(d, n);
+    k_primary_rays<<<d->sm_count * 8, 256, 0, st>>>(*cam, (int)w, (int)h, d->d_io_o, d->d_io_d);
+    d->stats.kernel_launches += 1;
+    tb_trace_generic(d, st, n, d->d_io_o, d->d_io_d, (float4*)d->d_io_hit);
+    TB_CUDA(cudaMemcpyAsync(out, d->d_io_hit, n * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, st));
+    d->stats.d2h_bytes += n * sizeof(TerraB200Hit);
+    tb_finish_call(d, st, false);
+}
+
+extern "C" void tb_device_bsdf_kat(TbDevice* d, size_t object_idx, size_t n, const float* e123, const float* wo,
+                                   const float* normal, float* out) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    float* d_e = tb_alloc<float>(n * 3); float* d_w = tb_alloc<float>(n * 3); float* d_n = tb_alloc<float>(n * 3);
+    float* d_out = tb_alloc<float>(n * 8);
+    TB_CUDA(cudaMemcpyAsync(d_e, e123, n * 12, cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaMemcpyAsync(d_w, wo, n * 12, cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaMemcpyAsync(d_n, normal, n * 12, cudaMemcpyHostToDevice, st));
+    k_bsdf_kat<<<d->sm_count, 256, 0, st>>>(d->sc, (int)object_idx, n, d_e, d_w, d_n, d_out);
+    d->stats.kernel_launches += 1;
+    TB_CUDA(cudaMemcpyAsync(out, d_out, n * 32, cudaMemcpyDeviceToHost, st));
+    tb_finish_call(d, st, false);
+    tb_free(d_e); tb_free(d_w); tb_free(d_n); tb_free(d_out);
+}
+
+extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
+    TB_CUDA(cudaSetDevice(d->index));
+    unsigned long long rays = 0;
+    TB_CUDA(cudaMemcpy(&rays, d->wave.counters + 8, sizeof rays, cudaMemcpyDeviceToHost));
+    d->stats.rays_traced = rays;
+    *out = d->stats;
+}
+
+extern "C" void tb_device_reset_stats(TbDevice* d) {
+    TB_CUDA(cudaSetDevice(d->index));
+    k_counters<<<1, 1, 0, d->stream>>>(d->wave.counters, 99, 0);
+    TB_CUDA(cudaStreamSynchronize(d->stream));
+    memset(&d->stats, 0, sizeof d->stats);
 }
