@@ -283,6 +283,8 @@ typedef struct {
     uint64_t trace_kernel_launches;
     double   render_ms;          /* device time of whole terra_render calls */
     uint64_t h2d_bytes, d2h_bytes;
+    uint64_t nodes_visited;      /* only while counting is on (terra_b200_set_counting): 64-byte nodes fetched */
+    uint64_t tris_tested;        /*   and triangles tested by the traversal kernel */
 } TerraB200Stats;
 
 int  terra_b200_device_count(void);
@@ -290,6 +292,8 @@ void terra_b200_set_device(int device);              /* before terra_scene_commi
 void terra_b200_set_seed(HTerraScene scene, uint64_t seed);   /* default: time based, like the reference */
 void terra_b200_get_stats(HTerraScene scene, TerraB200Stats* out);
 void terra_b200_reset_stats(HTerraScene scene);
+/* Switch the traversal kernel to its counting variant (slower; never on in timed runs). */
+void terra_b200_set_counting(HTerraScene scene, int on);
 
 /* The host BVH exactly as the reference lays it out (64-byte nodes, TerraBVH.h:13-17). */
 const void* terra_b200_bvh_nodes(HTerraScene scene, int* nodes_count);
@@ -297,7 +301,15 @@ int         terra_b200_bvh_stack_bound(HTerraScene scene);   /* worst-case order
 /* Host-only half of commit (no GPU needed): builds the BVH, optionally writes the flattened GPU
  * arrays (16 floats per node: two boxes + two child refs; 12 floats per triangle in rank order).
  * Returns the node count (= triangles - 1). */
-int         terra_b200_build_host_bvh(HTerraScene scene, float* flat_nodes_out, float* flat_tris_out);
+int         terra_b200_build_host_bvh(HTerraScene scene, int mode, float* flat_nodes_out, float* flat_tris_out);
+/* Acceleration structure built by the next terra_scene_commit, process-wide:
+ *   TERRA_B200_BVH_REFERENCE  the reference's tree (x-only SAH, src/TerraBVH.c:79-244), byte-identical nodes;
+ *   TERRA_B200_BVH_SAH3       binned SAH over x,y,z in the same 64-byte node format (default).
+ * Closest hits do not depend on the choice (same triangles, same intersection arithmetic);
+ * traversal work does. Also settable with the environment variable TERRA_B200_BVH=reference|sah3. */
+#define TERRA_B200_BVH_REFERENCE 0
+#define TERRA_B200_BVH_SAH3      1
+void        terra_b200_set_bvh_mode(int mode);
 
 /* Traversal micro-benchmark / parity entry points (= terra_scene_raycast without shading).
  * Host buffers: origins/dirs are n x 3 floats; the H2D/D2H copies are part of the call. */

@@ -94,7 +94,8 @@ class Framebuffer(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64), ("paths_traced", C.c_uint64),
                 ("trace_kernel_ms", C.c_double), ("trace_kernel_launches", C.c_uint64),
-                ("render_ms", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("render_ms", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64)]
 
 
 HIT_DTYPE = np.dtype([("t", "<f4"), ("prim", "<u4"), ("u", "<f4"), ("v", "<f4")])
@@ -113,6 +114,7 @@ FILTER_POINT, FILTER_BILINEAR, FILTER_TRILINEAR, FILTER_ANISOTROPIC = range(4)
 ADDRESS_WRAP, ADDRESS_MIRROR, ADDRESS_CLAMP = range(3)
 
 _vp, _sz = C.c_void_p, C.c_size_t
+BVH_REFERENCE, BVH_SAH3 = 0, 1
 
 
 class TerraLib:
@@ -164,9 +166,11 @@ class TerraLib:
             sig("terra_b200_set_seed", None, _vp, C.c_uint64)
             sig("terra_b200_get_stats", None, _vp, C.POINTER(Stats))
             sig("terra_b200_reset_stats", None, _vp)
+            sig("terra_b200_set_counting", None, _vp, C.c_int)
             sig("terra_b200_bvh_nodes", _vp, _vp, C.POINTER(C.c_int))
             sig("terra_b200_bvh_stack_bound", C.c_int, _vp)
-            sig("terra_b200_build_host_bvh", C.c_int, _vp, _vp, _vp)
+            sig("terra_b200_build_host_bvh", C.c_int, _vp, C.c_int, _vp, _vp)
+            sig("terra_b200_set_bvh_mode", None, C.c_int)
             sig("terra_b200_trace_rays", None, _vp, _sz, _vp, _vp, _vp)
             sig("terra_b200_trace_rays_device", None, _vp, _sz, _vp, _vp, _vp, _vp)
             sig("terra_b200_primary_hits", None, C.POINTER(Camera), _vp, _sz, _sz, _vp)
@@ -337,11 +341,12 @@ class Scene:
         self.lib.terra_b200_get_stats(self.h, C.byref(s))
         return s
 
-    def build_host_bvh(self, n_tris: int):
-        """Host-only BVH build + flatten. Returns (flat nodes (n-1,16) f32, flat tris (n,12) f32)."""
+    def build_host_bvh(self, n_tris: int, mode: int = 0):
+        """Host-only BVH build (mode 0 = reference tree, 1 = sah3) + flatten.
+        Returns (flat nodes (n-1,16) f32, flat tris (n,12) f32)."""
         nodes = np.zeros((n_tris * 2, 16), np.float32)
         tris = np.zeros((n_tris, 12), np.float32)
-        n = self.lib.terra_b200_build_host_bvh(self.h, _ptr(nodes), _ptr(tris))
+        n = self.lib.terra_b200_build_host_bvh(self.h, mode, _ptr(nodes), _ptr(tris))
         return nodes[:n].copy(), tris
 
     def bvh_nodes(self) -> np.ndarray:

@@ -15,4 +15,6 @@ struct TbFlatBvh {
 };
 
 void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
+// Conventional binned-SAH tree over x, y and z in the same node format (see tb_bvh.cpp).
+void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
 void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* objects, int objects_count, TbFlatBvh* out);

@@ -244,6 +244,7 @@ struct TbScene {
     bool              dirty_objects, dirty_lights, has_bvh;
     std::vector<TbHostNode> nodes;   // the reference-layout BVH
     int               stack_bound;
+    int               bvh_mode;
     TbDevice*         dev;
     uint64_t          seed;
     bool              seed_fixed;
@@ -252,6 +253,17 @@ struct TbScene {
 };
 
 static int g_device_index = 0;
+// Acceleration structure the next commit builds: 0 = the reference's tree (x-only SAH, TerraBVH.c),
+// 1 = binned SAH over three axes in the same node format (default; see tb_bvh.cpp).
+enum { TB_BVH_REFERENCE = 0, TB_BVH_SAH3 = 1 };
+static int g_bvh_mode = -1;
+static int bvh_mode() {
+    if (g_bvh_mode >= 0) return g_bvh_mode;
+    const char* e = getenv("TERRA_B200_BVH");
+    if (e && strcmp(e, "reference") == 0) return TB_BVH_REFERENCE;
+    return TB_BVH_SAH3;
+}
+static void build_bvh(TbScene* s, int mode);
 enum { TB_PREALLOCATED_OBJECTS = 64 };
 
 extern "C" HTerraScene terra_scene_create(void) {                                                   // Terra.c:130-138
@@ -264,6 +276,7 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     s->lights_triangles_count = 0;
     s->dirty_objects = s->dirty_lights = s->has_bvh = false;
     s->stack_bound = 0;
+    s->bvh_mode = -1;
     s->dev = NULL;
     s->seed = 0;
     s->seed_fixed = false;
@@ -361,10 +374,16 @@ static V3 host_attr_eval(const TerraAttribute* a, V2 uv) {                      
     return v3abi(&r);
 }
 
+static void build_bvh(TbScene* s, int mode) {
+    if (mode == TB_BVH_REFERENCE) tb_bvh_build(s->objects, (int)s->objects_pop, s->nodes);
+    else tb_bvh_build_sah3(s->objects, (int)s->objects_pop, s->nodes);
+    s->bvh_mode = mode;
+}
+
 extern "C" void terra_scene_commit(HTerraScene h) {                                                 // Terra.c:162-236
     TbScene* s = (TbScene*)h;
     std::lock_guard<std::mutex> guard(s->lock);
-    bool dirty_accelerator = s->dirty_objects || !s->has_bvh;
+    bool dirty_accelerator = s->dirty_objects || !s->has_bvh || s->bvh_mode != bvh_mode();
     if (s->opts.accelerator != s->new_opts.accelerator) dirty_accelerator = true;
     s->opts = s->new_opts;
     if (s->opts.accelerator != kTerraAcceleratorBVH) { assert(false); return; }
@@ -398,7 +417,7 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
     TbTextureTable table;
     TbDevAttr env = classify_attribute(&s->opts.environment_map, &table, "environment_map");
     if (dirty_accelerator || s->dirty_lights) {
-        if (dirty_accelerator) tb_bvh_build(s->objects, (int)s->objects_pop, s->nodes);
+        if (dirty_accelerator) build_bvh(s, bvh_mode());
         TbFlatBvh flat;
         tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
         s->stack_bound = flat.stack_bound;
@@ -523,6 +542,7 @@ extern "C" void terra_b200_set_seed(HTerraScene h, uint64_t seed) {
 }
 extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) { tb_device_get_stats(committed(h, "terra_b200_get_stats")->dev, out); }
 extern "C" void terra_b200_reset_stats(HTerraScene h) { tb_device_reset_stats(committed(h, "terra_b200_reset_stats")->dev); }
+extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;
     *nodes_count = (int)s->nodes.size();
@@ -531,10 +551,12 @@ extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
 extern "C" int terra_b200_bvh_stack_bound(HTerraScene h) { return ((TbScene*)h)->stack_bound; }
 // Host-only half of terra_scene_commit (no CUDA device needed): build the BVH and flatten it.
 // Lets the CPU test-suite check the builder and the flatten against the reference's node array.
-extern "C" int terra_b200_build_host_bvh(HTerraScene h, float* flat_nodes_out, float* flat_tris_out) {
+extern "C" void terra_b200_set_bvh_mode(int mode) { g_bvh_mode = mode; }
+extern "C" int terra_b200_build_host_bvh(HTerraScene h, int mode, float* flat_nodes_out, float* flat_tris_out) {
     TbScene* s = (TbScene*)h;
     std::lock_guard<std::mutex> guard(s->lock);
-    tb_bvh_build(s->objects, (int)s->objects_pop, s->nodes);
+    build_bvh(s, mode);
+    s->has_bvh = false;             // a later commit rebuilds for the device
     TbFlatBvh flat;
     tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
     s->stack_bound = flat.stack_bound;

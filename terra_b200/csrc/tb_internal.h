@@ -124,6 +124,7 @@ void      tb_device_bsdf_kat(TbDevice* dev, size_t object_idx, size_t n, const f
                              const float* normal, float* out);
 void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_reset_stats(TbDevice* dev);
+void      tb_device_set_counting(TbDevice* dev, int on);
 int       tb_cuda_device_count(void);
 #ifdef __cplusplus
 }

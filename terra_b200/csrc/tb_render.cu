@@ -125,6 +125,7 @@ struct TbDevice {
     std::vector<TbEventPair> ev_pool;
     size_t       ev_used;
     cudaEvent_t  ev_call_a, ev_call_b;
+    int          counting;     // use the counting variant of k_trace (work counters for the roofline)
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -192,6 +193,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
     memset(&d->stats, 0, sizeof d->stats);
     d->ev_used = 0;
+    d->counting = 0;
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
     return d;
@@ -381,6 +383,7 @@ struct TbTraceArgs {
     int*          matq_count;
     int           matq_stride;
     int           emit_prim;    // 1: write object|tri<<8 (API), 0: write rank (wavefront)
+    unsigned long long* visit_counters;   // COUNT variant only: [0] nodes fetched, [1] triangles tested
 };
 
 // Persistent CTAs; each warp pulls rays from a global cursor and refills idle lanes when too few
@@ -389,6 +392,7 @@ struct TbTraceArgs {
 // (TerraBVH.c:266-306); culling by the current closest t plus the smallest-rank tie
 // rule returns the same primitive. Stack: TB_STACK_SMEM entries per thread in shared memory
 // ([depth][thread], conflict free), the rest in local memory.
+template <bool COUNT>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace(TbTraceArgs a) {
     __shared__ int   s_node[TB_STACK_SMEM][TB_TRACE_THREADS];
     __shared__ float s_tmin[TB_STACK_SMEM][TB_TRACE_THREADS];
@@ -405,6 +409,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
     TbRay r;
     r.o = r.inv = v3s(0.f); r.sx = r.sy = r.sz = 0.f; r.kx = r.ky = r.kz = 0;
     bool exhausted = false;
+    unsigned n_nodes = 0, n_tris = 0;        // COUNT variant: the canonical work counters of SURVEY §8(d)
 
     while (true) {
         // ---- refill idle lanes (warp converged here)
@@ -433,6 +438,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
         while (node != DONE) {
             const float4* np = a.nodes + (size_t)node * 4;
             const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+            if (COUNT) ++n_nodes;
             const int ref0 = __float_as_int(q3.x), ref1 = __float_as_int(q3.y);
             float tmin0, tmin1;
             bool hit0 = tb_box(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
@@ -449,6 +455,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                     const float4* tp = a.tris + (size_t)rank * 3;
                     const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
                     float t, u, v;
+                    if (COUNT) ++n_tris;
                     if (tb_triangle(r, v3(ta.x, ta.y, ta.z), v3(tb.x, tb.y, tb.z), v3(tc.x, tc.y, tc.z), &t, &u, &v)) {
                         if (t < best_t || (t == best_t && best_rank >= 0 && rank < best_rank)) {
                             best_t = t; best_rank = rank; best_u = u; best_v = v;
@@ -514,6 +521,10 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
             }
         }
         if (finished) slot = -1;
+    }
+    if (COUNT) {
+        atomicAdd(a.visit_counters, (unsigned long long)n_nodes);
+        atomicAdd(a.visit_counters + 1, (unsigned long long)n_tris);
     }
 }
 
@@ -987,7 +998,7 @@ __global__ void k_counters(int* c, int mode, int value) {
         case 2: c[0] = 0; *rays += (unsigned long long)c[3]; break;                                  // before the visibility trace
         case 3: c[1] = c[2]; break;                                                                  // bounce ends
         case 4: *rays += (unsigned long long)value; c[0] = 0; break;                                 // stand-alone trace of `value` rays
-        default: *rays = 0; break;
+        default: *rays = 0; c[10] = c[11] = c[12] = c[13] = 0; break;
     }
 }
 
@@ -1023,7 +1034,13 @@ static void tb_drain_events(TbDevice* d) {
 static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a) {
     TbEventPair* e = tb_event_pair(d);
     TB_CUDA(cudaEventRecord(e->a, st));
-    k_trace<<<d->sm_count * TB_TRACE_CTAS_PER_SM, TB_TRACE_THREADS, 0, st>>>(a);
+    if (d->counting) {
+        TbTraceArgs c = a;
+        c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
+        k_trace<true><<<d->sm_count * TB_TRACE_CTAS_PER_SM, TB_TRACE_THREADS, 0, st>>>(c);
+    } else {
+        k_trace<false><<<d->sm_count * TB_TRACE_CTAS_PER_SM, TB_TRACE_THREADS, 0, st>>>(a);
+    }
     TB_CUDA(cudaEventRecord(e->b, st));
     d->stats.kernel_launches += 1;
 }
@@ -1299,11 +1316,15 @@ extern "C" void tb_device_bsdf_kat(TbDevice* d, size_t object_idx, size_t n, con
 
 extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
     TB_CUDA(cudaSetDevice(d->index));
-    unsigned long long rays = 0;
-    TB_CUDA(cudaMemcpy(&rays, d->wave.counters + 8, sizeof rays, cudaMemcpyDeviceToHost));
-    d->stats.rays_traced = rays;
+    unsigned long long c[3] = { 0, 0, 0 };
+    TB_CUDA(cudaMemcpy(c, d->wave.counters + 8, sizeof c, cudaMemcpyDeviceToHost));
+    d->stats.rays_traced = c[0];
+    d->stats.nodes_visited = c[1];
+    d->stats.tris_tested = c[2];
     *out = d->stats;
 }
+
+extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; }
 
 extern "C" void tb_device_reset_stats(TbDevice* d) {
     TB_CUDA(cudaSetDevice(d->index));
