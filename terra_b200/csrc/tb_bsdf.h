@@ -104,6 +104,7 @@ TB_HD float tb_ggx_G1(V3 v, V3 n, V3 h, float alpha2) {                       //
     float VoN = vdot(v, n);
     float chi = tb_ggx_chi(VoH / VoN);
     float VoH2 = VoH * VoH;
+    if (VoH2 == 0.f || VoN == 0.f) return 0.f;      // restatement guard: 0/0 and 0*inf would be NaN
     float tan2 = (1.f - VoH2) / VoH2;
     return (chi * 2) / (sqrtf(1 + alpha2 * tan2) + 1);
 }
@@ -126,8 +127,18 @@ TB_HD V3 tb_ggx_sample(const TbSurface& s, float e1, float e2, float e3, V3 wo) 
     V3 r = vmul(h, 2 * HoV);
     return vsub(r, wo);
 }
+// Guard added by the restatement: sample() returns wi = -wo when the sampled half vector faces away
+// from wo (HoV clamps to 0, :341-343); wi + wo is then the zero vector and normalising it would
+// poison the path with NaN. Such a direction carries no energy: pdf and eval return 0.
+TB_HD bool tb_ggx_half(V3 wi, V3 wo, V3* h) {
+    V3 hs = vadd(wi, wo);
+    if (!(vsqlen(hs) > 0.f)) return false;
+    *h = vnorm(hs);
+    return true;
+}
 TB_HD float tb_ggx_pdf(const TbSurface& s, V3 wi, V3 wo) {                    // :347-356
-    V3 h = vnorm(vadd(wi, wo));
+    V3 h;
+    if (!tb_ggx_half(wi, wo, &h)) return 0.f;
     float alpha = s.a1.x;
     float alpha2 = alpha * alpha;
     float NoH = vdot(s.n, h);
@@ -138,7 +149,8 @@ TB_HD float tb_ggx_pdf(const TbSurface& s, V3 wi, V3 wo) {                    //
     return weight_diffuse * pd + weight_specular * ps;
 }
 TB_HD V3 tb_ggx_eval(const TbSurface& s, V3 wi, V3 wo) {                      // :358-388 (minus the final *NoL)
-    V3 h = vnorm(vadd(wi, wo));
+    V3 h;
+    if (!tb_ggx_half(wi, wo, &h)) return v3s(0.f);
     float metal = s.a1.y;
     float f0 = (1.f - s.a1.z) / (1.f + s.a1.z);                               // :21-27 terra_bsdf_R0
     f0 *= f0;
