@@ -197,8 +197,12 @@ def _ptr(a: np.ndarray) -> int:
     return a.ctypes.data
 
 
+_oracle_for_presets = None
+
+
 class Scene:
     """Scene built through the public API only (reference call sequence)."""
+    default_preset_overrides: dict = {}
 
     def __init__(self, lib: TerraLib):
         self.lib = lib
@@ -206,6 +210,7 @@ class Scene:
         self.objects_base = None          # &objects[0]; stable while <= 64 objects
         self.n_objects = 0
         self._keep = []                   # textures etc. referenced by raw pointer from attributes
+        self.preset_overrides = dict(Scene.default_preset_overrides)   # name -> init function (tests plug the oracle's in)
 
     # -- construction -------------------------------------------------------------------
     def add_object(self, tris: np.ndarray, normals: np.ndarray | None = None,
@@ -238,7 +243,7 @@ class Scene:
         self.lib.terra_attribute_init_constant(C.byref(attr), C.byref(v))
 
     def set_diffuse(self, obj: Object, albedo, emissive=(0, 0, 0)):
-        self.lib.terra_bsdf_diffuse_init(C.byref(obj.material.bsdf))
+        self._preset_init("diffuse", self.preset_overrides.get("diffuse"))(C.byref(obj.material.bsdf))
         self.const_attr(obj.material.attributes[0], albedo)
         obj.material.attributes_count = 1
         self.const_attr(obj.material.emissive, emissive)
@@ -246,7 +251,7 @@ class Scene:
 
     def set_phong(self, obj: Object, albedo, specular, exponent, emissive=(0, 0, 0)):
         # slot order: reference include/TerraPresets.h:20-24, satellite/src/Scene.cpp:196-213
-        self.lib.terra_bsdf_phong_init(C.byref(obj.material.bsdf))
+        self._preset_init("phong", self.preset_overrides.get("phong"))(C.byref(obj.material.bsdf))
         self.const_attr(obj.material.attributes[0], specular)
         self.const_attr(obj.material.attributes[1], albedo)
         self.const_attr(obj.material.attributes[2], (exponent, exponent, exponent))
@@ -255,8 +260,19 @@ class Scene:
         self.const_attr(obj.material.emissive, emissive)
         obj.material.ior = 1.5
 
+    def _preset_init(self, name, override):
+        if override is not None:
+            return override
+        if self.lib.is_product or name in ("diffuse", "phong"):
+            return getattr(self.lib, f"terra_bsdf_{name}_init")
+        # the reference carries GGX/glass only as dead code: its scenes get the oracle's callbacks
+        global _oracle_for_presets
+        if _oracle_for_presets is None:
+            _oracle_for_presets = OracleLib()
+        return getattr(_oracle_for_presets, f"terra_oracle_bsdf_{name}_init")
+
     def set_ggx(self, obj: Object, albedo, roughness, metalness, ior=1.5, emissive=(0, 0, 0), bsdf_init=None):
-        (bsdf_init or self.lib.terra_bsdf_ggx_init)(C.byref(obj.material.bsdf))
+        self._preset_init("ggx", bsdf_init)(C.byref(obj.material.bsdf))
         self.const_attr(obj.material.attributes[0], albedo)
         self.const_attr(obj.material.attributes[1], (roughness, metalness, ior))
         obj.material.attributes_count = 2
@@ -264,7 +280,7 @@ class Scene:
         obj.material.ior = ior
 
     def set_glass(self, obj: Object, albedo, ior=1.5, bsdf_init=None):
-        (bsdf_init or self.lib.terra_bsdf_glass_init)(C.byref(obj.material.bsdf))
+        self._preset_init("glass", bsdf_init)(C.byref(obj.material.bsdf))
         self.const_attr(obj.material.attributes[0], albedo)
         self.const_attr(obj.material.attributes[1], (ior, 0, 0))
         self.const_attr(obj.material.attributes[2], (0, 0, 0))
@@ -393,3 +409,94 @@ class Scene:
 
 def make_camera(position, direction, up=(0, 1, 0), fov=45.0) -> Camera:
     return Camera(Float3(*position), Float3(*direction), Float3(*up), float(fov))
+
+
+# ---------------------------------------------------------------------------------------------
+# TEST INFRASTRUCTURE binding: oracle/libterra_oracle.so (CPU restatement). Only tests/,
+# __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may use this.
+class OracleLib:
+    def __init__(self, path: os.PathLike | str | None = None):
+        path = Path(path) if path is not None else ORACLE_LIB
+        if not path.exists():
+            raise FileNotFoundError(f"{path} is missing — run `make -C oracle`")
+        self.lib = L = C.CDLL(str(path))
+
+        def sig(name, res, *args):
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, list(args)
+
+        sig("oracle_scene_create", _vp, _vp, C.c_int, C.POINTER(SceneOptions))
+        sig("oracle_scene_destroy", None, _vp)
+        sig("oracle_bvh_nodes", _vp, _vp, C.POINTER(C.c_int))
+        sig("oracle_trace_rays", None, _vp, _sz, _vp, _vp, _vp)
+        sig("oracle_trace_counted", None, _vp, _vp, _sz, _vp, _vp, _vp, _vp)
+        sig("oracle_primary_hits", None, _vp, C.POINTER(Camera), _sz, _sz, _vp, _vp)
+        sig("oracle_render", None, _vp, C.POINTER(Camera), C.POINTER(Framebuffer), _sz, _sz, _sz, _sz, C.c_uint32)
+        sig("oracle_raycast_surface", C.c_int, _vp, _vp, _vp, C.POINTER(ShadingSurface), _vp, C.POINTER(C.c_int))
+        for p in ("diffuse", "phong", "ggx", "glass"):
+            sig(f"terra_oracle_bsdf_{p}_init", None, C.POINTER(BSDF))
+
+    def __getattr__(self, name):
+        return getattr(self.lib, name)
+
+
+class OracleScene:
+    """The oracle's view of a scene built through either Terra-ABI library (it reads the
+    caller-owned TerraObject array in place)."""
+
+    def __init__(self, oracle: OracleLib, scene: Scene):
+        self.o, self.scene = oracle, scene
+        self.h = oracle.oracle_scene_create(scene.objects_base, scene.n_objects, C.byref(scene.options()))
+
+    def destroy(self):
+        if self.h:
+            self.o.oracle_scene_destroy(self.h)
+            self.h = None
+
+    def bvh_nodes(self) -> np.ndarray:
+        n = C.c_int(0)
+        p = self.o.oracle_bvh_nodes(self.h, C.byref(n))
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), (n.value * 64,)).copy()
+
+    def trace_rays(self, origins, dirs) -> np.ndarray:
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(dirs, np.float32)
+        hits = np.empty(o.shape[0], HIT_DTYPE)
+        self.o.oracle_trace_rays(self.h, o.shape[0], _ptr(o), _ptr(d), _ptr(hits))
+        return hits
+
+    def trace_counted(self, origins, dirs, nodes: np.ndarray | None = None):
+        """Canonical near-first culled walk; `nodes` = raw 64-byte node array (default: reference tree).
+        Returns (hits, nodes_fetched, triangles_tested)."""
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(dirs, np.float32)
+        hits = np.empty(o.shape[0], HIT_DTYPE)
+        cnt = np.zeros(2, np.uint64)
+        self.o.oracle_trace_counted(self.h, _ptr(nodes) if nodes is not None else None, o.shape[0], _ptr(o), _ptr(d),
+                                    _ptr(hits), _ptr(cnt))
+        return hits, int(cnt[0]), int(cnt[1])
+
+    def primary_hits(self, cam: Camera, width: int, height: int):
+        hits = np.empty(width * height, HIT_DTYPE)
+        dirs = np.empty((width * height, 3), np.float32)
+        self.o.oracle_primary_hits(self.h, C.byref(cam), width, height, _ptr(hits), _ptr(dirs))
+        return hits.reshape(height, width), dirs.reshape(height, width, 3)
+
+    def render(self, cam: Camera, width: int, height: int, pcg_seed: int = 1, region=None):
+        res = np.zeros(width * height, RESULT_DTYPE)
+        pix = np.zeros((height, width, 3), np.float32)
+        fb = Framebuffer(_ptr(pix), _ptr(res), width, height)
+        x, y, w, h = region or (0, 0, width, height)
+        self.o.oracle_render(self.h, C.byref(cam), C.byref(fb), x, y, w, h, pcg_seed)
+        return res.reshape(height, width), pix
+
+
+_libc = None
+
+
+def srand(seed: int):
+    """libc srand(): the reference (and the oracle) draw BSDF/roulette numbers from rand()."""
+    global _libc
+    if _libc is None:
+        _libc = C.CDLL(None)
+    _libc.srand(C.c_uint(seed))
