@@ -425,6 +425,16 @@ int oracle_raycast_surface(const OracleScene* s, const float* origin, const floa
     return obj;
 }
 
+/* KAT helper: the surface record a BSDF callback sees for a given shading normal and attribute
+ * values (frame = terra_f4x4_basis(normal), TerraMath.inl:251-272). */
+void oracle_surface_from_normal(const float* normal, const float* attributes24, TerraShadingSurface* sf) {
+    memset(sf, 0, sizeof *sf);
+    sf->normal = mk(normal[0], normal[1], normal[2]);
+    sf->transform = frame_from_normal(sf->normal);
+    for (int i = 0; i < TERRA_MATERIAL_MAX_ATTRIBUTES; ++i)
+        sf->attributes[i] = mk(attributes24[3 * i], attributes24[3 * i + 1], attributes24[3 * i + 2]);
+}
+
 /* ------------------------------------------------------------------ presets
  * Diffuse (TerraPresets.c:34-60) and Phong (:66-146): live reference code restated.
  * Slots: diffuse [0]=albedo; phong [0]=specular colour [1]=albedo [2].x=exponent [3].x=lobe pick. */

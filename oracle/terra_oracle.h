@@ -49,6 +49,9 @@ void oracle_render(const OracleScene* s, const TerraCamera* cam, const TerraFram
 int  oracle_raycast_surface(const OracleScene* s, const float* origin, const float* dir,
                             TerraShadingSurface* surf, float* point, int* tri);
 
+/* KAT helper: surface record (frame from `normal`, 8 x float3 attribute values) for BSDF callbacks. */
+void oracle_surface_from_normal(const float* normal, const float* attributes24, TerraShadingSurface* sf);
+
 /* Presets as TerraBSDF callbacks (usable inside the reference's terra_render). */
 void terra_oracle_bsdf_diffuse_init(TerraBSDF* b);
 void terra_oracle_bsdf_phong_init(TerraBSDF* b);

@@ -433,6 +433,7 @@ class OracleLib:
         sig("oracle_primary_hits", None, _vp, C.POINTER(Camera), _sz, _sz, _vp, _vp)
         sig("oracle_render", None, _vp, C.POINTER(Camera), C.POINTER(Framebuffer), _sz, _sz, _sz, _sz, C.c_uint32)
         sig("oracle_raycast_surface", C.c_int, _vp, _vp, _vp, C.POINTER(ShadingSurface), _vp, C.POINTER(C.c_int))
+        sig("oracle_surface_from_normal", None, _vp, _vp, C.POINTER(ShadingSurface))
         for p in ("diffuse", "phong", "ggx", "glass"):
             sig(f"terra_oracle_bsdf_{p}_init", None, C.POINTER(BSDF))
 
@@ -489,6 +490,36 @@ class OracleScene:
         x, y, w, h = region or (0, 0, width, height)
         self.o.oracle_render(self.h, C.byref(cam), C.byref(fb), x, y, w, h, pcg_seed)
         return res.reshape(height, width), pix
+
+
+# TerraBSDF callback prototypes (include/terra_b200.h; reference include/Terra.h:40-54)
+BSDF_SAMPLE = C.CFUNCTYPE(Float3, C.POINTER(ShadingSurface), C.c_float, C.c_float, C.c_float, C.POINTER(Float3))
+BSDF_PDF = C.CFUNCTYPE(C.c_float, C.POINTER(ShadingSurface), C.POINTER(Float3), C.POINTER(Float3))
+BSDF_EVAL = C.CFUNCTYPE(Float3, C.POINTER(ShadingSurface), C.POINTER(Float3), C.POINTER(Float3))
+
+
+def run_bsdf_callbacks(oracle: "OracleLib", init_fn, attributes, e123, wo, normal) -> np.ndarray:
+    """Calls the host {sample, pdf, eval} callbacks that `init_fn` installs, in terra_trace's order
+    (sample -> pdf -> eval on one surface record, Terra.c:1068-1075), for n input tuples.
+    attributes: up to 8 rgb triples. Returns (n,8) float32 = wi.xyz, pdf, f.xyz, attributes[3].x."""
+    b = BSDF()
+    init_fn(C.byref(b))
+    sample, pdf, ev = BSDF_SAMPLE(b.sample), BSDF_PDF(b.pdf), BSDF_EVAL(b.eval)
+    attrs = np.zeros((8, 3), np.float32)
+    a = np.asarray(attributes, np.float32).reshape(-1, 3)
+    attrs[:a.shape[0]] = a
+    n = len(e123)
+    out = np.zeros((n, 8), np.float32)
+    for i in range(n):
+        sf = ShadingSurface()
+        nrm = np.ascontiguousarray(normal[i], np.float32)
+        oracle.oracle_surface_from_normal(_ptr(nrm), _ptr(attrs), C.byref(sf))
+        w = Float3(*[float(x) for x in wo[i]])
+        wi = sample(C.byref(sf), float(e123[i][0]), float(e123[i][1]), float(e123[i][2]), C.byref(w))
+        p = pdf(C.byref(sf), C.byref(wi), C.byref(w))
+        f = ev(C.byref(sf), C.byref(wi), C.byref(w))
+        out[i] = (wi.x, wi.y, wi.z, p, f.x, f.y, f.z, sf.attributes[3].x)
+    return out
 
 
 _libc = None
