@@ -1,0 +1,471 @@
+#!/usr/bin/env python
+"""bench.py — the driver's measurement contract for the Terra hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload at N=1 (and, split by sample ranges, at N>1): BASELINE.json configs[1] — the procedural
+~100k-triangle sphere field, mixed Lambert / GGX presets, 1920x1080, 256 spp, bounces 4. One STEP =
+one full frame = 1920*1080*256 paths through the hot path (raygen -> closest hit -> shade -> ... ->
+accumulate -> tonemap). Metric = Mpaths/s (1 path = 1 (pixel, sample) = one terra_trace call).
+
+  value   device-resident: terra_b200_render_device + terra_b200_resolve_device, framebuffer in HBM
+  e2e     the reference-facing call: terra_render() on a HOST TerraFramebuffer (H2D of the running
+          results[], D2H of results[] + pixels[] inside the timed region)
+  roofline  the dominant kernel k_trace: algorithmic bytes (32 + 16 + 64*nodes + 36*tris per ray, visit
+          counts from the kernel's counting variant, validated against the oracle's canonical walk in
+          tests/) / its mean launch time (CUDA events on the launching stream, recorded by the library)
+  cpu_baseline  the UNMODIFIED reference (oracle/_ref, multi-process tile farm, all host cores) on a
+          bounded sample of the same frame (a tile subset at 1 spp), as a rate.
+
+Other workloads (--workload c1|c3_1m|c3_10m|c5) are for the profiles/ notes; the default is the contract.
+Nothing here reads /root/reference. The oracle / reference .so are only ever the CPU baseline."""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+REPO = Path(__file__).resolve().parent
+sys.path.insert(0, str(REPO))
+
+WORKLOADS = {
+    "c1": dict(name="C1 Cornell 36 tris Lambert+emissive 256x256 16spp bounces 8", w=256, h=256, spp=16),
+    "c2": dict(name="C2 100k-tri sphere field, mixed Lambert/GGX, 1920x1080, 256 spp, bounces 4", w=1920, h=1080, spp=256),
+    "c5": dict(name="C5 glass+metal divergence stress, 1920x1080, 512 spp, bounces 32 + RR", w=1920, h=1080, spp=512),
+    "c3_1m": dict(name="C3 traversal: 64M incoherent rays vs 1M-triangle terrain", rays=64_000_000, tris=1_000_000),
+    "c3_10m": dict(name="C3 traversal: 64M incoherent rays vs 10M-triangle terrain", rays=64_000_000, tris=10_000_000),
+}
+
+
+def build_scene(lib, scenes, workload, spp):
+    if workload == "c1":
+        return scenes.cornell(lib, spp=spp, bounces=8)
+    if workload == "c2":
+        return scenes.sphere_field(lib, spp=spp, bounces=4, ggx=True)
+    if workload == "c5":
+        return scenes.glass_metal(lib, spp=spp, bounces=32)
+    raise ValueError(workload)
+
+
+# --------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu_index = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu_index)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------- CPU arm
+def cpu_reference_rate(workload, budget_s, seed=1, steps=1, warmup=0):
+    """Times the reference's own CPU renderer on a bounded sample of `workload`.
+
+    kind "reference": oracle/_ref/libterra_ref.so = the unmodified reference sources, driven the way
+    its only caller does (one terra_render per tile from every host core, satellite/src/Renderer.cpp:
+    316-349) — as processes, because glibc rand() serialises threads. GGX spheres get the oracle's
+    callbacks through the function-pointer table (the reference has no live GGX preset).
+    kind "port": the oracle's renderer, single core, when the reference .so is absent.
+    Sample = every S-th 128x128 tile of the frame at `spp_cpu` spp, S chosen from a one-tile probe so
+    a step costs about `budget_s`. Returns (list of per-step Mpaths/s, info dict)."""
+    from terra_b200 import api, scenes
+    wl = WORKLOADS[workload]
+    w, h = wl["w"], wl["h"]
+    cores = os.cpu_count() or 1
+    tile = 128
+    tx, ty = (w + tile - 1) // tile, (h + tile - 1) // tile
+    spp_cpu = 1
+    if api.REFERENCE_LIB.exists():
+        ref = api.TerraLib(api.REFERENCE_LIB)
+        t0 = time.time()
+        s, cam = build_scene(ref, scenes, workload, spp_cpu)
+        build_s = time.time() - t0
+        # probe: every 17th tile (8 tiles spread over the frame) on all cores -> CPU-seconds per tile
+        all_tiles = tx * ty
+        n_probe = len(range(0, all_tiles, 17))
+        secs, _, _, _, _ = s.ref_render_farm(cam, w, h, spp_cpu, tile=tile, nproc=min(cores, n_probe), seed=seed, tile_stride=17)
+        per_tile = max(secs, 1e-3) * min(cores, n_probe) / n_probe
+        want_tiles = budget_s * cores / per_tile
+        if want_tiles >= all_tiles:
+            stride = 1
+            spp_cpu = int(max(1, min(64, want_tiles // all_tiles)))
+            if spp_cpu > 1:
+                s.options().samples_per_pixel = spp_cpu
+                s.commit()
+        else:
+            stride = max(1, int(all_tiles // max(want_tiles, 1.0)))
+        rates, rays_total, paths_total, secs_total = [], 0, 0, 0.0
+        for it in range(warmup + steps):
+            secs, rays, paths, _, _ = s.ref_render_farm(cam, w, h, spp_cpu, tile=tile, nproc=cores, seed=seed + it, tile_stride=stride)
+            if it >= warmup:
+                rates.append(paths / secs / 1e6)
+                rays_total += rays; paths_total += paths; secs_total += secs
+        s.destroy()
+        info = {"kind": "reference", "cores": cores,
+                "sample": f"every {stride}th 128x128 tile of the {w}x{h} frame ({len(range(0, tx * ty, stride))} tiles) at {spp_cpu} spp, "
+                          f"{cores}-process tile farm over libterra_ref.so; {paths_total} paths, {rays_total} rays, {secs_total:.2f} s; "
+                          f"reference BVH build {build_s:.2f} s excluded",
+                "mrays_per_s": rays_total / secs_total / 1e6 if secs_total else None}
+        return rates, info
+    # port: oracle renderer on one core, a centred crop
+    prod, ora = api.TerraLib(), api.OracleLib()
+    orig = api.Scene.commit
+    api.Scene.commit = lambda self: None
+    try:
+        s, cam = build_scene(prod, scenes, workload, spp_cpu)
+    finally:
+        api.Scene.commit = orig
+    osc = api.OracleScene(ora, s)
+    cw = ch = 32
+    rates = []
+    for it in range(warmup + steps):
+        api.srand(seed + it)
+        t0 = time.time()
+        osc.render(cam, w, h, region=((w - cw) // 2, (h - ch) // 2, cw, ch))
+        if it >= warmup:
+            rates.append(cw * ch * spp_cpu / (time.time() - t0) / 1e6)
+    osc.destroy(); s.destroy()
+    return rates, {"kind": "port", "cores": 1, "sample": f"centre {cw}x{ch} crop of the {w}x{h} frame at {spp_cpu} spp, oracle renderer, 1 core"}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation on this box's host cores, same metric/config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = WORKLOADS[args.workload]
+    total = max(1, args.steps + args.warmup)
+    budget = min(10.0, 150.0 / total)
+    t0 = time.time()
+    rates, info = cpu_reference_rate(args.workload, budget, steps=args.steps, warmup=args.warmup)
+    value = float(np.mean(rates))
+    paths_per_step = wl["w"] * wl["h"] * wl["spp"]
+    line = {
+        "impl": "reference", "metric": "mpaths_per_s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": paths_per_step / (value * 1e6) * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "width": wl["w"], "height": wl["h"], "spp": wl["spp"],
+                   "note": "rate measured on a bounded sample; ms_per_step is the full frame extrapolated from it"},
+        "cpu_baseline": dict(info, value=value, unit="Mpaths/s"),
+        "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.time() - t0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------- GPU arm
+def measured_peaks():
+    p = REPO / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def profile_traffic(kernel):
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture, if any."""
+    p = REPO / "profiles" / "traffic.json"
+    if p.exists():
+        return json.loads(p.read_text()).get(kernel)
+    return None
+
+
+def run_render_arm(args):
+    import torch
+    import torch.distributed as dist
+    from terra_b200 import api, scenes
+    from terra_b200.multigpu import DistRenderer
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = WORKLOADS[args.workload]
+    w, h = args.width or wl["w"], args.height or wl["h"]
+    spp = args.spp or wl["spp"]
+    paths_per_step = w * h * spp
+
+    cpu_rates, cpu_info = None, None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:      # before CUDA is initialised: the farm fork()s
+        cpu_rates, cpu_info = cpu_reference_rate(args.workload, args.cpu_budget)
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = api.TerraLib()
+    if lib.terra_b200_device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU fallback")
+    lib.terra_b200_set_device(local)
+    t0 = time.time()
+    s, cam = build_scene(lib, scenes, args.workload, spp)           # replicated on every GPU
+    commit_s = time.time() - t0
+    lib.terra_b200_set_seed(s.h, 2024)
+    r = DistRenderer(lib, s, cam, w, h, mode=args.split)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        lib.terra_b200_reset_stats(s.h)
+        evs = []
+        for _ in range(steps):
+            flush.zero_()                                             # L2 flush between timed iterations
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            evs.append((a, b))
+        barrier()
+        ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)                 # max over ranks
+        return float(ms.item()) / steps, s.stats()
+
+    # ---- value: device-resident frame (render on every rank -> one reduce -> resolve on rank 0)
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms_dev, st = timed(lambda: r.render(spp), args.steps, args.warmup)
+    clk = clocks.stop() if rank == 0 else None
+    launches = st.kernel_launches
+    trace_ms, trace_launches, rays = st.trace_kernel_ms, st.trace_kernel_launches, st.rays_traced
+    rays_all = torch.tensor([rays], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(rays_all)                                     # statistics only, outside every timed region
+    rays_all = float(rays_all.item())
+
+    # ---- e2e: host framebuffer in, host framebuffer out
+    if world == 1:
+        fb = api.Framebuffer()
+        assert lib.terra_framebuffer_create(C.byref(fb), w, h)
+        ms_e2e, _ = timed(lambda: lib.terra_render(C.byref(cam), s.h, C.byref(fb), 0, 0, w, h), max(1, args.steps // 2), 1)
+        h2d, d2h = w * h * 16 + 40, w * h * 28
+    else:
+        def e2e_step():
+            if rank == 0:
+                r.results.copy_(r.host_results, non_blocking=True)    # the running accumulators go up (then are reset: one frame)
+            r.render(spp)
+            if rank == 0:
+                r.to_host()
+        ms_e2e, _ = timed(e2e_step, max(1, args.steps // 2), 1)
+        h2d, d2h = w * h * 16 + 40, w * h * 28
+
+    # ---- work counters for the roofline: one small counted frame (never inside a timed region)
+    lib.terra_b200_set_counting(s.h, 1)
+    lib.terra_b200_reset_stats(s.h)
+    r.render(min(spp, 4 * world))
+    torch.cuda.synchronize()
+    stc = s.stats()
+    lib.terra_b200_set_counting(s.h, 0)
+    nodes_per_ray = stc.nodes_visited / max(1, stc.rays_traced)
+    tris_per_ray = stc.tris_tested / max(1, stc.rays_traced)
+    bytes_per_ray = 32 + 16 + 64 * nodes_per_ray + 36 * tris_per_ray
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peaks()
+    rays_per_launch = rays / max(1, trace_launches)
+    trace_ms_per_launch = trace_ms / max(1, trace_launches)
+    achieved = bytes_per_ray * rays_per_launch / (trace_ms_per_launch * 1e-3) / 1e9 if trace_ms_per_launch else 0.0
+    value = paths_per_step / (ms_dev * 1e-3) / 1e6
+    e2e = paths_per_step / (ms_e2e * 1e-3) / 1e6
+    line = {
+        "metric": "mpaths_per_s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": wl["name"], "width": w, "height": h, "spp": spp, "bounces": int(s.options().bounces),
+                   "integrator": "simple", "split": args.split if world > 1 else "none", "bvh": os.environ.get("TERRA_B200_BVH", "sah3"),
+                   "l2": "flushed between timed iterations (256 MiB write); path-state waves (4M slots x 144 B) exceed L2"},
+        "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": profile_traffic("k_trace"), "peak_source": peak_src,
+                     "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
+                     "rays_per_launch": rays_per_launch, "ms_per_launch": trace_ms_per_launch,
+                     "note": "working set (nodes+tris ~11 MB) is L2-resident: the HBM figure is the contract's denominator, "
+                             "the L2 fraction is in profiles/"},
+        "extra": {"mrays_per_s": rays_all / args.steps / (ms_dev * 1e-3) / 1e6,
+                  "rays_per_path": rays_all / args.steps / paths_per_step,
+                  "trace_share_of_step": trace_ms / args.steps / ms_dev if ms_dev else None,
+                  "scene_commit_s": commit_s},
+    }
+    if cpu_info is not None:
+        v = float(np.mean(cpu_rates))
+        line["cpu_baseline"] = dict(cpu_info, value=v, unit="Mpaths/s")
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_traversal_arm(args):
+    """Config C3: incoherent closest-hit Mrays/s, no shading (terra_scene_raycast minus terra_surface_init)."""
+    import torch
+    from terra_b200 import api, scenes
+    wl = WORKLOADS[args.workload]
+    n_rays = args.rays or wl["rays"]
+    lib = api.TerraLib()
+    if lib.terra_b200_device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU fallback")
+    torch.cuda.set_device(0)
+    extent = 1000.0 if wl["tris"] <= 2_000_000 else 10000.0
+    t0 = time.time()
+    s, cam = scenes.terrain(lib, n_tris=wl["tris"], extent=extent, lights=False)
+    commit_s = time.time() - t0
+    lo = np.array([0, -0.09 * extent, 0], np.float32)
+    hi = np.array([extent, 0.09 * extent, extent], np.float32)
+    chunk = 1 << 24
+    g = torch.Generator(device="cuda").manual_seed(7)
+    o4 = torch.empty(n_rays, 4, device="cuda")
+    d4 = torch.empty(n_rays, 4, device="cuda")
+    ext = torch.tensor(hi - lo, device="cuda")
+    lo_t = torch.tensor(lo, device="cuda")
+    for a in range(0, n_rays, chunk):                                  # origin ~U(bbox inflated 10%), direction uniform on the sphere
+        m = min(chunk, n_rays - a)
+        o4[a:a + m, :3] = lo_t - 0.05 * ext + torch.rand(m, 3, device="cuda", generator=g) * (1.1 * ext)
+        z = torch.rand(m, device="cuda", generator=g) * 2 - 1
+        ph = torch.rand(m, device="cuda", generator=g) * (2 * np.pi)
+        rr = torch.sqrt(torch.clamp(1 - z * z, min=0))
+        d = torch.stack([rr * torch.cos(ph), z, rr * torch.sin(ph)], 1)
+        d4[a:a + m, :3] = d / d.norm(dim=1, keepdim=True)
+    o4[:, 3] = 0
+    d4[:, 3] = 0
+    hits = torch.empty(n_rays, 4, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def step():
+        lib.terra_b200_trace_rays_device(s.h, n_rays, C.c_void_p(o4.data_ptr()), C.c_void_p(d4.data_ptr()), C.c_void_p(hits.data_ptr()), stream)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    lib.terra_b200_reset_stats(s.h)
+    clocks = ClockSampler(0)
+    clocks.start()
+    tot = 0.0
+    for _ in range(args.steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); step(); b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    clk = clocks.stop()
+    st = s.stats()
+    ms = tot / args.steps
+    # e2e through host buffers on a 16M-ray slice
+    n_e2e = min(n_rays, 1 << 24)
+    oh = o4[:n_e2e, :3].contiguous().cpu().numpy()
+    dh = d4[:n_e2e, :3].contiguous().cpu().numpy()
+    s.trace_rays(oh[:1000], dh[:1000])
+    t0 = time.time()
+    hh = s.trace_rays(oh, dh)
+    e2e_s = time.time() - t0
+    # canonical work counters: oracle walk of the SAME tree over a 200k-ray sample (CPU, untimed)
+    ora = api.OracleLib()
+    osc = api.OracleScene(ora, s) if wl["tris"] <= 2_000_000 and not args.no_cpu_baseline else None
+    n_s = 200_000
+    if osc is not None:
+        want, n_nodes, n_tris = osc.trace_counted(oh[:n_s], dh[:n_s], s.bvh_nodes())
+        agree = float((want["t"].view(np.uint32) == hh["t"][:n_s].view(np.uint32)).mean())
+        nodes_per_ray, tris_per_ray, src = n_nodes / n_s, n_tris / n_s, "oracle canonical walk, 200k-ray sample"
+    else:
+        lib.terra_b200_set_counting(s.h, 1); lib.terra_b200_reset_stats(s.h)
+        s.trace_rays(oh[:1_000_000], dh[:1_000_000])
+        stc = s.stats(); lib.terra_b200_set_counting(s.h, 0)
+        nodes_per_ray, tris_per_ray, agree, src = stc.nodes_visited / 1e6, stc.tris_tested / 1e6, None, "k_trace<COUNT>, 1M-ray sample"
+    bytes_per_ray = 32 + 16 + 64 * nodes_per_ray + 36 * tris_per_ray
+    peak, peak_src = measured_peaks()
+    k_ms = st.trace_kernel_ms / max(1, st.trace_kernel_launches)
+    achieved = bytes_per_ray * (n_rays / max(1, st.trace_kernel_launches / args.steps)) / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": "incoherent_mrays_per_s", "value": n_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "rays": n_rays, "triangles": wl["tris"], "bvh": os.environ.get("TERRA_B200_BVH", "sah3"),
+                   "l2": "flushed between timed iterations; rays+hits (3 GB) exceed L2"},
+        "e2e": {"value": n_e2e / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": n_e2e * 24, "d2h_bytes_per_step": n_e2e * 16,
+                "rays": n_e2e},
+        "gpu_launches": int(st.kernel_launches), "clocks": clk,
+        "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": profile_traffic("k_trace_" + args.workload), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
+                     "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "counter": src, "ms_per_launch": k_ms},
+        "extra": {"scene_commit_s": commit_s, "hit_t_agreement_with_oracle": agree},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=list(WORKLOADS))
+    ap.add_argument("--split", default="samples", choices=["samples", "rows"])
+    ap.add_argument("--spp", type=int, default=0)
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--rays", type=int, default=0)
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        if args.workload.startswith("c3"):
+            raise SystemExit("--impl reference supports the render workloads")
+        return run_reference_arm(args)
+    if args.workload.startswith("c3"):
+        return run_traversal_arm(args)
+    return run_render_arm(args)
+
+
+if __name__ == "__main__":
+    main()
