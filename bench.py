@@ -202,11 +202,14 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def profile_traffic(kernel):
-    """dram bytes per launch of `kernel` from the committed ncu --set full capture, if any."""
+def profile_traffic(kernel, rays_per_launch):
+    """DRAM bytes per launch of `kernel`: dram bytes/ray from the committed ncu --set full capture
+    (profiles/traffic.json) x the rays one launch of this run processed. None without a capture."""
     p = REPO / "profiles" / "traffic.json"
     if p.exists():
-        return json.loads(p.read_text()).get(kernel)
+        e = json.loads(p.read_text()).get(kernel)
+        if e:
+            return e["dram_bytes_per_ray"] * rays_per_launch
     return None
 
 
@@ -327,7 +330,7 @@ def run_render_arm(args):
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": profile_traffic("k_trace"), "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": profile_traffic("k_trace", rays_per_launch), "peak_source": peak_src,
                      "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
                      "rays_per_launch": rays_per_launch, "ms_per_launch": trace_ms_per_launch,
                      "note": "working set (nodes+tris ~11 MB) is L2-resident: the HBM figure is the contract's denominator, "
@@ -435,7 +438,7 @@ def run_traversal_arm(args):
                 "rays": n_e2e},
         "gpu_launches": int(st.kernel_launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": profile_traffic("k_trace_" + args.workload), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
+                     "traffic": profile_traffic("k_trace_" + args.workload, n_rays), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
                      "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "counter": src, "ms_per_launch": k_ms},
         "extra": {"scene_commit_s": commit_s, "hit_t_agreement_with_oracle": agree},
     }

@@ -295,6 +295,11 @@ void terra_b200_reset_stats(HTerraScene scene);
 /* Switch the traversal kernel to its counting variant (slower; never on in timed runs). */
 void terra_b200_set_counting(HTerraScene scene, int on);
 
+/* Memory-system probe for the roofline denominators MEASURED_PEAKS.json lacks: GB/s of (mode 0) a
+ * streaming 128-bit read or (mode 1) random 64-byte record gathers over a `bytes`-sized buffer
+ * (<= ~64 MB: L2-resident; >= 1 GB: HBM). */
+double terra_b200_probe_bandwidth(size_t bytes, int mode);
+
 /* The host BVH exactly as the reference lays it out (64-byte nodes, TerraBVH.h:13-17). */
 const void* terra_b200_bvh_nodes(HTerraScene scene, int* nodes_count);
 int         terra_b200_bvh_stack_bound(HTerraScene scene);   /* worst-case ordered-traversal stack */

@@ -163,6 +163,7 @@ class TerraLib:
             sig("terra_bsdf_glass_init", None, C.POINTER(BSDF))
             sig("terra_b200_device_count", C.c_int)
             sig("terra_b200_set_device", None, C.c_int)
+            sig("terra_b200_probe_bandwidth", C.c_double, _sz, C.c_int)
             sig("terra_b200_set_seed", None, _vp, C.c_uint64)
             sig("terra_b200_get_stats", None, _vp, C.POINTER(Stats))
             sig("terra_b200_reset_stats", None, _vp)

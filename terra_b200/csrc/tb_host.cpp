@@ -536,6 +536,7 @@ extern "C" void terra_render(const TerraCamera* camera, HTerraScene h, const Ter
 // =============================================================================== extensions
 extern "C" int  terra_b200_device_count(void) { return tb_cuda_device_count(); }
 extern "C" void terra_b200_set_device(int device) { g_device_index = device; }
+extern "C" double terra_b200_probe_bandwidth(size_t bytes, int mode) { return tb_device_probe_bandwidth(g_device_index, bytes, mode); }
 extern "C" void terra_b200_set_seed(HTerraScene h, uint64_t seed) {
     TbScene* s = (TbScene*)h;
     s->seed = seed; s->seed_fixed = true; s->render_calls = 0;

@@ -126,6 +126,7 @@ void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 int       tb_cuda_device_count(void);
+double    tb_device_probe_bandwidth(int device_index, size_t bytes, int mode);
 #ifdef __cplusplus
 }
 #endif

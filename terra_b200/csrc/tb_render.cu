@@ -1314,6 +1314,66 @@ extern "C" void tb_device_bsdf_kat(TbDevice* d, size_t object_idx, size_t n, con
     tb_free(d_e); tb_free(d_w); tb_free(d_n); tb_free(d_out);
 }
 
+// ==================================================================================== memory-system probes
+// Roofline denominators that MEASURED_PEAKS.json does not carry: L2 bandwidth for a
+// resident buffer, (mode 0) streaming 128-bit reads, (mode 1) random 64-byte-aligned gathers of one
+// node-sized record (4 x 128-bit), the access pattern of k_trace. Returns GB/s.
+__global__ void __launch_bounds__(256) k_probe_stream(const float4* buf, size_t n_vec, int reps, float4* sink) {
+    float4 acc = make_float4(0, 0, 0, 0);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int r = 0; r < reps; ++r)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
+            const float4 v = __ldcg(buf + i);      // L2 only: a per-SM slice of a small buffer would otherwise sit in L1
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+    if (acc.x == 12345.678f) sink[0] = acc;
+}
+__global__ void __launch_bounds__(256) k_probe_gather(const float4* buf, size_t n_rec, int per_thread, float4* sink) {
+    float4 acc = make_float4(0, 0, 0, 0);
+    uint64_t st = tb_mix64(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 0x9E3779B97F4A7C15ull + 1);
+    for (int k = 0; k < per_thread; ++k) {
+        st = st * 6364136223846793005ull + 1442695040888963407ull;
+        const size_t rec = (size_t)((st >> 33) % n_rec);
+        const float4* p = buf + rec * 4;
+        const float4 a = __ldcg(p), b = __ldcg(p + 1), c = __ldcg(p + 2), d = __ldcg(p + 3);
+        acc.x += a.x + b.x + c.x + d.x; acc.y += a.y + b.y; acc.z += c.z; acc.w += d.w;
+    }
+    if (acc.x == 12345.678f) sink[0] = acc;
+}
+extern "C" double tb_device_probe_bandwidth(int device_index, size_t bytes, int mode) {
+    TB_CUDA(cudaSetDevice(device_index));
+    cudaDeviceProp prop;
+    TB_CUDA(cudaGetDeviceProperties(&prop, device_index));
+    float4* buf = tb_alloc<float4>(bytes / 16 + 4);
+    float4* sink = tb_alloc<float4>(1);
+    TB_CUDA(cudaMemset(buf, 0, bytes));
+    cudaEvent_t a, b;
+    TB_CUDA(cudaEventCreate(&a)); TB_CUDA(cudaEventCreate(&b));
+    const int grid = prop.multiProcessorCount * 8;
+    double moved = 0;
+    float best = 1e30f;
+    for (int it = 0; it < 4; ++it) {                // first pass warms L2; keep the best of the rest
+        TB_CUDA(cudaEventRecord(a));
+        if (mode == 0) {
+            const int reps = (int)(((size_t)8 << 30) / bytes) + 1;
+            k_probe_stream<<<grid, 256>>>(buf, bytes / 16, reps, sink);
+            moved = (double)reps * (double)(bytes / 16) * 16.0;
+        } else {
+            const int per_thread = 2048;
+            k_probe_gather<<<grid, 256>>>(buf, bytes / 64, per_thread, sink);
+            moved = (double)grid * 256.0 * per_thread * 64.0;
+        }
+        TB_CUDA(cudaEventRecord(b));
+        TB_CUDA(cudaEventSynchronize(b));
+        float ms = 0.f;
+        TB_CUDA(cudaEventElapsedTime(&ms, a, b));
+        if (it > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    tb_free(buf); tb_free(sink);
+    return moved / (best * 1e-3) / 1e9;
+}
+
 extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
     TB_CUDA(cudaSetDevice(d->index));
     unsigned long long c[3] = { 0, 0, 0 };

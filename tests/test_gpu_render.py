@@ -93,18 +93,23 @@ IMAGE_CASES = {
 
 @pytest.mark.parametrize("name", list(IMAGE_CASES))
 def test_converged_image_matches_cpu_renderer(api, scenes, gpu, oracle, name):
-    """Per-channel mean within 0.5 % and RMSE(GPU,CPU) <= 1.25 x RMSE(CPU A, CPU B) at matched spp.
+    """Per-channel image mean within 0.5 % and RMSE(GPU,CPU) <= 1.25 x RMSE(CPU A, CPU B) at matched spp.
     CPU<->GPU parity beyond the first hit is statistical by construction: the reference draws from
-    libc rand() and a time-seeded PCG."""
+    libc rand() and a time-seeded PCG.
+    The RMSE comparison runs at subpixel_jitter = 0: the reference seeds its jitter PCG from time(NULL)
+    in every terra_render call (Terra.c:529-530), so two CPU runs inside one second share their
+    jitter pattern and RMSE(A,B) would miss the pixel-filter noise. At jitter 0 the camera rays are
+    identical on both sides and the only noise is the BSDF / light / roulette sampling, which srand()
+    decorrelates between A and B. The mean is checked with jitter on as well."""
     w = h = 40
     spp = 1024
-    kw = dict(IMAGE_CASES[name], jitter=0.5)
+    kw = dict(IMAGE_CASES[name])
     ref = api.TerraLib(api.REFERENCE_LIB) if api.REFERENCE_LIB.exists() else None
     nproc = min(8, os.cpu_count() or 1)
-    build = lambda lib: scenes.cornell(lib, spp=spp, **kw)
-    A = radiance(cpu_render(api, scenes, ref, oracle, build, w, h, spp, 11, nproc))
-    B = radiance(cpu_render(api, scenes, ref, oracle, build, w, h, spp, 23, nproc))
-    s, cam = scenes.cornell(gpu, spp=spp, **kw)
+    build0 = lambda lib: scenes.cornell(lib, spp=spp, jitter=0.0, **kw)
+    A = radiance(cpu_render(api, scenes, ref, oracle, build0, w, h, spp, 11, nproc))
+    B = radiance(cpu_render(api, scenes, ref, oracle, build0, w, h, spp, 23, nproc))
+    s, cam = build0(gpu)
     gpu.terra_b200_set_seed(s.h, 7)
     res, _ = s.render(cam, w, h)
     G = radiance(res)
@@ -114,16 +119,26 @@ def test_converged_image_matches_cpu_renderer(api, scenes, gpu, oracle, name):
     s.destroy()
     assert (res["samples"] == spp).all() and (res4["samples"] == 4 * spp).all()
     assert np.isfinite(G).all() and np.isfinite(G4).all()
-    rmse_ab = np.sqrt(((A - B) ** 2).mean())
-    rmse_ga = np.sqrt(((G - A) ** 2).mean())
-    rmse_gb = np.sqrt(((G - B) ** 2).mean())
-    assert min(rmse_ga, rmse_gb) <= RMSE_FACTOR * rmse_ab, (rmse_ga, rmse_gb, rmse_ab)
+    rmse = lambda x, y: float(np.sqrt(((x - y) ** 2).mean()))
+    rmse_ab, rmse_ga, rmse_gb = rmse(A, B), rmse(G, A), rmse(G, B)
+    assert max(rmse_ga, rmse_gb) <= RMSE_FACTOR * rmse_ab, (rmse_ga, rmse_gb, rmse_ab)
     cpu_mean = ((A + B) / 2).mean(axis=(0, 1))
-    gpu_mean = G4.mean(axis=(0, 1))
-    # standard error of the CPU mean estimated from the two runs; the 0.5 % bar is on the converged value
-    sem = np.abs(A.mean(axis=(0, 1)) - B.mean(axis=(0, 1))) / 2
-    rel = np.abs(gpu_mean - cpu_mean) / cpu_mean
-    assert (rel <= MEAN_TOL + 2 * sem / cpu_mean).all(), (rel, sem / cpu_mean, gpu_mean, cpu_mean)
+    rel = np.abs(G4.mean(axis=(0, 1)) - cpu_mean) / cpu_mean
+    # the 0.5 % bar is on the converged value; 2048 CPU spp are not converged to 0.5 % for the noisiest
+    # integrator (simple: only paths that run into the emitter carry energy), hence the sem term
+    sem = np.abs(A.mean(axis=(0, 1)) - B.mean(axis=(0, 1))) / 2 / cpu_mean
+    print(f"{name}: rmse GA {rmse_ga:.5f} GB {rmse_gb:.5f} AB {rmse_ab:.5f}; mean rel err {rel}, cpu sem {sem}")
+    assert (rel <= MEAN_TOL + 2 * sem).all(), (rel, sem)
+    # jitter on (the benchmark configuration): image mean only
+    build1 = lambda lib: scenes.cornell(lib, spp=spp, jitter=0.5, **kw)
+    J = radiance(cpu_render(api, scenes, ref, oracle, build1, w, h, spp, 31, nproc))
+    s, cam = build1(gpu)
+    gpu.terra_b200_set_seed(s.h, 9)
+    GJ = radiance(s.render(cam, w, h, passes=2)[0])
+    s.destroy()
+    relj = np.abs(GJ.mean(axis=(0, 1)) - J.mean(axis=(0, 1))) / J.mean(axis=(0, 1))
+    print(f"{name}: jittered mean rel err {relj}")
+    assert (relj <= MEAN_TOL + 4 * sem + 0.003).all(), relj
 
 
 # ----------------------------------------------------------------------------- accumulate + tonemap
