@@ -475,6 +475,7 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         up.lights_triangles_count = s->lights_triangles_count;
         up.env = env;
         up.stack_bound = flat.stack_bound;
+        up.exact_boxes = s->bvh_mode == TB_BVH_REFERENCE ? 1 : 0;
         tb_device_upload(s->dev, &up);
         s->has_bvh = true;
     }

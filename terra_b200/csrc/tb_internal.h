@@ -102,6 +102,7 @@ struct TbFlatScene {          // host staging of everything the device needs
     uint64_t             lights_triangles_count;
     TbDevAttr            env;
     int                  stack_bound;
+    int                  exact_boxes;     // 1: reference tree -> reference box arithmetic in k_trace (tb_trace.cuh)
 };
 
 #ifdef __cplusplus
