@@ -128,6 +128,8 @@ struct TbDevice {
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_v1;     // TERRA_B200_TRACE=v1: the first (if-if) kernel, for A/B runs
+    int          trace_v3;     // TERRA_B200_TRACE=v3: rounds with postponed leaves (tb_trace_v3.cuh)
+    int          ld128;        // TERRA_B200_TRACE=ld128: node fetch as 4 x 128-bit instead of 2 x 256-bit, for A/B runs
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -197,7 +199,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->ev_used = 0;
     d->counting = 0;
     d->exact_boxes = 0;
-    { const char* e = getenv("TERRA_B200_TRACE"); d->trace_v1 = e && strcmp(e, "v1") == 0; }
+    { const char* e = getenv("TERRA_B200_TRACE"); d->trace_v1 = e && strcmp(e, "v1") == 0; d->ld128 = e && strcmp(e, "ld128") == 0; d->trace_v3 = e && strcmp(e, "v3") == 0; }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
     return d;
@@ -393,6 +395,7 @@ struct TbTraceArgs {
 
 #include "tb_trace_v1.cuh"
 #include "tb_trace.cuh"
+#include "tb_trace_v3.cuh"
 
 // ==================================================================================== K1: ray generation
 struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot = s_local * n_pixels + p_local
@@ -870,7 +873,7 @@ __global__ void k_counters(int* c, int mode, int value) {
 
 static size_t tb_batch_capacity() {
     const char* e = getenv("TERRA_B200_BATCH");
-    size_t cap = e ? (size_t)strtoull(e, NULL, 10) : ((size_t)1 << 22);
+    size_t cap = e ? (size_t)strtoull(e, NULL, 10) : ((size_t)1 << 26);
     if (cap < 1024) cap = 1024;
     if (cap > ((size_t)1 << 28)) cap = (size_t)1 << 28;
     return cap;
@@ -906,12 +909,22 @@ static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a) 
     if (d->trace_v1) {
         if (d->counting) k_trace_v1<true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
         else             k_trace_v1<false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+    } else if (d->trace_v3) {
+        if (d->exact_boxes) {
+            if (d->counting) k_trace_v3<true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+            else             k_trace_v3<false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        } else {
+            if (d->counting) k_trace_v3<true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+            else             k_trace_v3<false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        }
     } else if (d->exact_boxes) {
-        if (d->counting) k_trace<true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        if (d->counting) k_trace<true, true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else             k_trace<false, true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+    } else if (d->ld128) {
+        k_trace<false, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     } else {
-        if (d->counting) k_trace<true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        if (d->counting) k_trace<true, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else             k_trace<false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     }
     TB_CUDA(cudaEventRecord(e->b, st));
     d->stats.kernel_launches += 1;

@@ -101,11 +101,12 @@ def test_converged_image_matches_cpu_renderer(api, scenes, gpu, oracle, name):
     jitter pattern and RMSE(A,B) would miss the pixel-filter noise. At jitter 0 the camera rays are
     identical on both sides and the only noise is the BSDF / light / roulette sampling, which srand()
     decorrelates between A and B. The mean is checked with jitter on as well.
-    The frame is 48x40, not square: with a square frame and the centred Cornell camera the jitter-free
-    rays of both image diagonals run exactly along the wall/floor intersection lines (dir.x == +-dir.y),
-    an exact-t tie between two differently coloured objects that the reference resolves by its tree's
-    visiting order — a "numerical tie" outside the parity bar (measured: 0.17 radiance on 8 pixels)."""
-    w, h = 48, 40
+    The frame is 47x40: with the centred Cornell camera a jitter-free ray runs exactly along a
+    wall/floor intersection line when |dir.x| == |dir.y|, i.e. (2j+1-W) == +-(2i+1-H) — whole diagonals
+    of pixels whenever W-H is even. That is an exact-t tie between two differently coloured objects,
+    which the reference resolves by its tree's visiting order: a "numerical tie" outside the parity
+    bar (measured: 0.17 radiance on those pixels). W-H odd has no such pixel."""
+    w, h = 47, 40
     spp = 1024
     kw = dict(IMAGE_CASES[name])
     ref = api.TerraLib(api.REFERENCE_LIB) if api.REFERENCE_LIB.exists() else None
