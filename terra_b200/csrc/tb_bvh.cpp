@@ -10,6 +10,7 @@
 // 32-byte elements), the float SAH cost expression, and the LIFO task order that numbers nodes.
 // tests/test_bvh.py checks the node array byte-for-byte against terra_bvh_create.
 #include <float.h>
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -359,4 +360,51 @@ void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vecto
         }
     }
     nodes.resize((size_t)nodes_count);
+}
+
+// ------------------------------------------------------------------------------------ quantised nodes
+// 32-byte nodes for the traversal kernel (layout and rationale: tb_trace.cuh). Child boxes go on a 16-bit
+// grid over the scene box padded by 0.1 %; mins round down, maxes round up (checked in double against
+// the decode expression lo + q * cell), then both move one more cell outwards to cover the half-cell
+// rounding of the kernel's folded decode constant. The decoded box therefore contains the float box.
+void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out) {
+    const size_t n = flat.nodes.size() / 16;
+    double lo[3] = { DBL_MAX, DBL_MAX, DBL_MAX }, hi[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
+    for (size_t i = 0; i < n; ++i) {
+        const float* q = &flat.nodes[i * 16];
+        for (int c = 0; c < 2; ++c)
+            for (int k = 0; k < 3; ++k) {
+                if (q[6 * c + k] < lo[k]) lo[k] = q[6 * c + k];
+                if (q[6 * c + 3 + k] > hi[k]) hi[k] = q[6 * c + 3 + k];
+            }
+    }
+    for (int k = 0; k < 3; ++k) {
+        double ext = hi[k] - lo[k];
+        if (!(ext > 0)) ext = 1.0;
+        const double pad = ext * 1e-3;
+        out->grid_lo[k] = (float)(lo[k] - pad);
+        out->grid_cell[k] = (float)((ext + 2 * pad) / 65535.0);
+    }
+    out->nodes.assign(n * 8, 0u);
+    for (size_t i = 0; i < n; ++i) {
+        const float* q = &flat.nodes[i * 16];
+        uint16_t g[12];
+        for (int c = 0; c < 2; ++c)
+            for (int k = 0; k < 3; ++k) {
+                const double l = out->grid_lo[k], cell = out->grid_cell[k];
+                long a = (long)floor((q[6 * c + k] - l) / cell);
+                while (a > 0 && l + a * cell > q[6 * c + k]) --a;
+                a -= 1;
+                long b = (long)ceil((q[6 * c + 3 + k] - l) / cell);
+                while (b < 65535 && l + b * cell < q[6 * c + 3 + k]) ++b;
+                b += 1;
+                if (a < 0) a = 0;
+                if (b > 65535) b = 65535;
+                g[6 * c + k] = (uint16_t)a;
+                g[6 * c + 3 + k] = (uint16_t)b;
+            }
+        uint32_t* w = &out->nodes[i * 8];
+        for (int j = 0; j < 6; ++j) w[j] = (uint32_t)g[2 * j] | ((uint32_t)g[2 * j + 1] << 16);
+        memcpy(&w[6], &q[12], 8);              // the two child references, as in the float node
+    }
 }

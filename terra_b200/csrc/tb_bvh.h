@@ -14,6 +14,12 @@ struct TbFlatBvh {
     int                   stack_bound;        // inner nodes on the deepest root->leaf path
 };
 
+struct TbQuantBvh {
+    std::vector<uint32_t> nodes;              // 8 words per node (tb_trace.cuh)
+    float grid_lo[3], grid_cell[3];
+};
+void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out);
+
 void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
 // Conventional binned-SAH tree over x, y and z in the same node format (see tb_bvh.cpp).
 void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);

@@ -476,6 +476,13 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         up.env = env;
         up.stack_bound = flat.stack_bound;
         up.exact_boxes = s->bvh_mode == TB_BVH_REFERENCE ? 1 : 0;
+        TbQuantBvh quant;
+        if (!up.exact_boxes) {
+            tb_bvh_quantize(flat, &quant);
+            up.qnodes = quant.nodes.data();
+            memcpy(up.grid_lo, quant.grid_lo, sizeof up.grid_lo);
+            memcpy(up.grid_cell, quant.grid_cell, sizeof up.grid_cell);
+        }
         tb_device_upload(s->dev, &up);
         s->has_bvh = true;
     }

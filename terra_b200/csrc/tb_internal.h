@@ -102,6 +102,8 @@ struct TbFlatScene {          // host staging of everything the device needs
     uint64_t             lights_triangles_count;
     TbDevAttr            env;
     int                  stack_bound;
+    const uint32_t*      qnodes;          // 8 words per node, or NULL (reference tree: float boxes only)
+    float                grid_lo[3], grid_cell[3];
     int                  exact_boxes;     // 1: reference tree -> reference box arithmetic in k_trace (tb_trace.cuh)
 };
 

@@ -102,6 +102,9 @@ struct TbDevice {
     TbDevScene   sc;
     // owned device memory
     float4 *d_nodes, *d_tris, *d_props;
+    uint4*  d_qnodes;
+    float   grid_lo[3], grid_cell[3];
+    int     use_quant_nodes;   // TERRA_B200_TRACE=quant: 32-byte quantised nodes (experiment, tb_trace.cuh)
     TbDevMaterial* d_mats;
     TbDevTexture*  d_texs;
     TbDevLight*    d_lights;
@@ -188,6 +191,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     memset(&d->sc, 0, sizeof d->sc);
     d->d_nodes = d->d_tris = d->d_props = NULL;
+    d->d_qnodes = NULL;
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
     d->stack_bound = 0;
     memset(&d->wave, 0, sizeof d->wave);
@@ -199,7 +203,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->ev_used = 0;
     d->counting = 0;
     d->exact_boxes = 0;
-    { const char* e = getenv("TERRA_B200_TRACE"); d->trace_v1 = e && strcmp(e, "v1") == 0; d->ld128 = e && strcmp(e, "ld128") == 0; d->trace_v3 = e && strcmp(e, "v3") == 0; }
+    { const char* e = getenv("TERRA_B200_TRACE"); d->trace_v1 = e && strcmp(e, "v1") == 0; d->ld128 = e && strcmp(e, "ld128") == 0; d->trace_v3 = e && strcmp(e, "v3") == 0; d->use_quant_nodes = e && strcmp(e, "quant") == 0; }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
     return d;
@@ -207,6 +211,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
 
 static void tb_scene_free(TbDevice* d) {
     tb_free(d->d_nodes); tb_free(d->d_tris); tb_free(d->d_props); tb_free(d->d_mats); tb_free(d->d_texs);
+    tb_free(d->d_qnodes); d->d_qnodes = NULL;
     tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
     for (void* p : d->tex_pixels) tb_free(p);
     d->tex_pixels.clear();
@@ -246,6 +251,11 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
     tb_scene_free(d);
     d->d_nodes = (float4*)tb_upload(f->nodes, f->n_nodes * 16, d);
     d->d_tris = (float4*)tb_upload(f->tris, f->n_tris * 12, d);
+    if (f->qnodes) {
+        d->d_qnodes = (uint4*)tb_upload(f->qnodes, f->n_nodes * 8, d);
+        memcpy(d->grid_lo, f->grid_lo, sizeof d->grid_lo);
+        memcpy(d->grid_cell, f->grid_cell, sizeof d->grid_cell);
+    }
     d->d_props = (float4*)tb_upload(f->props, f->n_tris * 16, d);
     std::vector<TbDevMaterial> mats(f->materials, f->materials + f->n_objects);
     d->d_mats = tb_upload(mats.data(), mats.size(), d);
@@ -391,6 +401,8 @@ struct TbTraceArgs {
     int           matq_stride;
     int           emit_prim;    // 1: write object|tri<<8 (API), 0: write rank (wavefront)
     unsigned long long* visit_counters;   // COUNT variant only: [0] nodes fetched, [1] triangles tested
+    const uint4*  qnodes;       // quantised 32-byte nodes (tb_trace.cuh), or NULL
+    float         grid_lo[3], grid_cell[3];
 };
 
 #include "tb_trace_v1.cuh"
@@ -918,13 +930,19 @@ static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a) 
             else             k_trace_v3<false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
         }
     } else if (d->exact_boxes) {
-        if (d->counting) k_trace<true, true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        if (d->counting) k_trace<true, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else             k_trace<false, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     } else if (d->ld128) {
-        k_trace<false, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        k_trace<false, false, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+    } else if (d->d_qnodes && d->use_quant_nodes) {
+        c.qnodes = d->d_qnodes;
+        memcpy(c.grid_lo, d->grid_lo, sizeof c.grid_lo);
+        memcpy(c.grid_cell, d->grid_cell, sizeof c.grid_cell);
+        if (d->counting) k_trace<true, false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else             k_trace<false, false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     } else {
-        if (d->counting) k_trace<true, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        if (d->counting) k_trace<true, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else             k_trace<false, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     }
     TB_CUDA(cudaEventRecord(e->b, st));
     d->stats.kernel_launches += 1;
