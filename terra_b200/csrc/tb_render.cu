@@ -104,7 +104,6 @@ struct TbDevice {
     float4 *d_nodes, *d_tris, *d_props;
     uint4*  d_qnodes;
     float   grid_lo[3], grid_cell[3];
-    int     use_quant_nodes;   // TERRA_B200_TRACE=quant: 32-byte quantised nodes (experiment, tb_trace.cuh)
     TbDevMaterial* d_mats;
     TbDevTexture*  d_texs;
     TbDevLight*    d_lights;
@@ -130,9 +129,7 @@ struct TbDevice {
     cudaEvent_t  ev_call_a, ev_call_b;
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
-    int          trace_v1;     // TERRA_B200_TRACE=v1: the first (if-if) kernel, for A/B runs
-    int          trace_v3;     // TERRA_B200_TRACE=v3: rounds with postponed leaves (tb_trace_v3.cuh)
-    int          ld128;        // TERRA_B200_TRACE=ld128: node fetch as 4 x 128-bit instead of 2 x 256-bit, for A/B runs
+    int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -203,7 +200,12 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->ev_used = 0;
     d->counting = 0;
     d->exact_boxes = 0;
-    { const char* e = getenv("TERRA_B200_TRACE"); d->trace_v1 = e && strcmp(e, "v1") == 0; d->ld128 = e && strcmp(e, "ld128") == 0; d->trace_v3 = e && strcmp(e, "v3") == 0; d->use_quant_nodes = e && strcmp(e, "quant") == 0; }
+    {
+        const char* e = getenv("TERRA_B200_TRACE");
+        static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128" };
+        d->trace_kind = 0;
+        for (int k = 0; e && k < 7; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
+    }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
     return d;
@@ -912,38 +914,48 @@ static void tb_drain_events(TbDevice* d) {
     d->ev_used = 0;
 }
 
-static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a) {
-    TbEventPair* e = tb_event_pair(d);
-    TB_CUDA(cudaEventRecord(e->a, st));
+// Which closest-hit kernel a launch uses. Measured on B200 (profiles/): camera rays are coherent and
+// instruction-bound, where the while-while kernel over 64-byte float nodes is fastest (10.5 Grays/s on C2);
+// bounce / visibility / API rays are incoherent and bound by L1 wavefronts AND by issue slots at 7 of 32
+// lanes, where the rounds kernel over 32-byte quantised nodes is fastest (3.9 vs 2.8 Grays/s on C3).
+// TERRA_B200_TRACE=v1|v2|v3|v3q|quant|ld128 forces one kernel for every launch (A/B runs).
+enum { TB_K_AUTO = 0, TB_K_V1, TB_K_V2, TB_K_V3, TB_K_V3Q, TB_K_QUANT, TB_K_LD128 };
+
+template <bool COUNT>
+static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind) {
     const int grid = d->sm_count * TB_TRACE_CTAS_PER_SM;
-    TbTraceArgs c = a;
-    c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
-    if (d->trace_v1) {
-        if (d->counting) k_trace_v1<true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace_v1<false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-    } else if (d->trace_v3) {
-        if (d->exact_boxes) {
-            if (d->counting) k_trace_v3<true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-            else             k_trace_v3<false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        } else {
-            if (d->counting) k_trace_v3<true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-            else             k_trace_v3<false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        }
-    } else if (d->exact_boxes) {
-        if (d->counting) k_trace<true, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-    } else if (d->ld128) {
-        k_trace<false, false, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-    } else if (d->d_qnodes && d->use_quant_nodes) {
+    const bool have_q = d->d_qnodes != NULL;
+    if (have_q) {
         c.qnodes = d->d_qnodes;
         memcpy(c.grid_lo, d->grid_lo, sizeof c.grid_lo);
         memcpy(c.grid_cell, d->grid_cell, sizeof c.grid_cell);
-        if (d->counting) k_trace<true, false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-    } else {
-        if (d->counting) k_trace<true, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else             k_trace<false, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     }
+    if (kind == TB_K_V1) { k_trace_v1<COUNT><<<grid, TB_TRACE_THREADS, 0, st>>>(c); return; }
+    if (d->exact_boxes) {           // reference tree: the reference's own box arithmetic, float nodes
+        if (kind == TB_K_V3 || kind == TB_K_V3Q) k_trace_v3<COUNT, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else k_trace<COUNT, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        return;
+    }
+    switch (kind) {
+        case TB_K_V3:    k_trace_v3<COUNT, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+        case TB_K_V3Q:   if (have_q) { k_trace_v3<COUNT, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break; }
+                         k_trace_v3<COUNT, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+        case TB_K_QUANT: if (have_q) { k_trace<COUNT, false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break; }
+                         k_trace<COUNT, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+        case TB_K_LD128: k_trace<COUNT, false, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+        default:         k_trace<COUNT, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+    }
+}
+
+static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, bool coherent) {
+    TbEventPair* e = tb_event_pair(d);
+    TB_CUDA(cudaEventRecord(e->a, st));
+    TbTraceArgs c = a;
+    c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
+    int kind = d->trace_kind;
+    if (kind == TB_K_AUTO) kind = coherent ? TB_K_V2 : TB_K_V3Q;
+    if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind);
+    else             tb_launch_trace_kernel<false>(d, st, c, kind);
     TB_CUDA(cudaEventRecord(e->b, st));
     d->stats.kernel_launches += 1;
 }
@@ -1001,7 +1013,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 ta.hit_out = wv.hit;
                 ta.matq = wv.matq; ta.matq_count = wv.counters + 4; ta.matq_stride = (int)wv.capacity;
                 ta.emit_prim = 0;
-                tb_launch_trace(d, st, ta);
+                tb_launch_trace(d, st, ta, bounce == 0);
                 d->stats.kernel_launches += 1;
                 TbShadeArgs sa;
                 sa.sc = sc;
@@ -1025,7 +1037,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                     xa.queue = wv.auxq; xa.count_ptr = wv.counters + 3; xa.cursor = wv.counters;
                     xa.hit_out = wv.aux_hit;
                     xa.emit_prim = 0;
-                    tb_launch_trace(d, st, xa);
+                    tb_launch_trace(d, st, xa, false);
                     d->stats.kernel_launches += 1;
                 }
                 for (int p = 0; p < TB_PRESET_COUNT; ++p) {
@@ -1130,7 +1142,7 @@ extern "C" void tb_device_resolve(TbDevice* d, size_t fbw, size_t fbh, const voi
     TB_CUDA(cudaStreamSynchronize(st));
 }
 
-static void tb_trace_generic(TbDevice* d, cudaStream_t st, size_t n, const float4* d_o, const float4* d_d, float4* d_hit) {
+static void tb_trace_generic(TbDevice* d, cudaStream_t st, size_t n, const float4* d_o, const float4* d_d, float4* d_hit, bool coherent = false) {
     k_counters<<<1, 1, 0, st>>>(d->wave.counters, 4, (int)n);
     TbTraceArgs ta;
     memset(&ta, 0, sizeof ta);
@@ -1139,7 +1151,7 @@ static void tb_trace_generic(TbDevice* d, cudaStream_t st, size_t n, const float
     ta.count = (int)n; ta.cursor = d->wave.counters;
     ta.hit_out = d_hit;
     ta.emit_prim = 1;
-    tb_launch_trace(d, st, ta);
+    tb_launch_trace(d, st, ta, coherent);
     d->stats.kernel_launches += 1;
 }
 
@@ -1195,7 +1207,7 @@ extern "C" void tb_device_primary_hits(TbDevice* d, const TbCameraFrame* cam, si
     tb_io_reserve(d, n);
     k_primary_rays<<<d->sm_count * 8, 256, 0, st>>>(*cam, (int)w, (int)h, d->d_io_o, d->d_io_d);
     d->stats.kernel_launches += 1;
-    tb_trace_generic(d, st, n, d->d_io_o, d->d_io_d, (float4*)d->d_io_hit);
+    tb_trace_generic(d, st, n, d->d_io_o, d->d_io_d, (float4*)d->d_io_hit, true);      // camera rays
     TB_CUDA(cudaMemcpyAsync(out, d->d_io_hit, n * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, st));
     d->stats.d2h_bytes += n * sizeof(TerraB200Hit);
     tb_finish_call(d, st, false);

@@ -19,7 +19,7 @@
 #define TB_REF_POP  ((int)0x80000001)             /* lane must pop its stack next round */
 #define TB_TRI_MIN  8
 
-template <bool COUNT, bool EXACT>
+template <bool COUNT, bool EXACT, bool QUANT>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace_v3(TbTraceArgs a) {
     __shared__ int   s_ref[TB_STACK_SMEM][TB_TRACE_THREADS];
     __shared__ float s_tmin[TB_STACK_SMEM][TB_TRACE_THREADS];
@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                     const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
                     const V3 d = v3(d4.x, d4.y, d4.z);
                     r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
-                    if (!EXACT) fr = tb_fast_ray(r, d);
+                    if (QUANT) fr = tb_quant_ray(r, d, a.grid_lo, a.grid_cell);
+                    else if (!EXACT) fr = tb_fast_ray(r, d);
                     cur = 0; sp = 0;
                     best_rank = -1; best_t = FLT_MAX; cull_t = FLT_MAX;
                 }
@@ -89,9 +90,15 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
             const bool do_tri = tri_round && pend != TB_REF_DONE;
             // 4. all loads of the round first, so node and triangle latencies overlap
             float4 q0, q1, q2, q3, ta, tb, tc;
+            uint4 qa, qb;
             if (is_node) {
-                const float4* np = a.nodes + (size_t)cur * 4;
-                q0 = __ldg(np); q1 = __ldg(np + 1); q2 = __ldg(np + 2); q3 = __ldg(np + 3);
+                if (QUANT) {
+                    const uint4* np = a.qnodes + (size_t)cur * 2;
+                    qa = __ldg(np); qb = __ldg(np + 1);
+                } else {
+                    const float4* np = a.nodes + (size_t)cur * 4;
+                    q0 = __ldg(np); q1 = __ldg(np + 1); q2 = __ldg(np + 2); q3 = __ldg(np + 3);
+                }
             }
             if (do_tri) {
                 const float4* tp = a.tris + (size_t)(~pend) * 3;
@@ -100,13 +107,19 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
             // 5. node step
             if (is_node) {
                 if (COUNT) ++n_nodes;
-                const int ref0 = __float_as_int(q3.x), ref1 = __float_as_int(q3.y);
+                int ref0, ref1;
                 float tmin0, tmin1;
                 bool hit0, hit1;
-                if (EXACT) {
+                if (QUANT) {
+                    ref0 = (int)qb.z; ref1 = (int)qb.w;
+                    hit0 = tb_box_fast(fr, tb_qlo(qa.x), tb_qhi(qa.x), tb_qlo(qa.y), tb_qhi(qa.y), tb_qlo(qa.z), tb_qhi(qa.z), &tmin0);
+                    hit1 = tb_box_fast(fr, tb_qlo(qa.w), tb_qhi(qa.w), tb_qlo(qb.x), tb_qhi(qb.x), tb_qlo(qb.y), tb_qhi(qb.y), &tmin1);
+                } else if (EXACT) {
+                    ref0 = __float_as_int(q3.x); ref1 = __float_as_int(q3.y);
                     hit0 = tb_box(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
                     hit1 = tb_box(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, &tmin1);
                 } else {
+                    ref0 = __float_as_int(q3.x); ref1 = __float_as_int(q3.y);
                     hit0 = tb_box_fast(fr, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
                     hit1 = tb_box_fast(fr, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, &tmin1);
                 }
