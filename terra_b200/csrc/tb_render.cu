@@ -42,6 +42,8 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_TRACE_CTAS_PER_SM  8            // persistent grid = SMs x this
 #define TB_STACK_SMEM         16           // traversal stack entries held in shared memory ...
 #define TB_STACK_LOCAL        112          // ... deeper entries spill to local memory
+#define TB_TRI_MIN            8            // rounds kernel: parked leaves needed before a triangle round
+#define TB_REFETCH_ROUNDS     26           // rounds kernel: refill the warp when fewer lanes own a ray (swept on B200: 16/20/26/30)
 #define TB_REFETCH_BELOW      20           // dynamic fetch: refill the warp when fewer lanes are busy
 #define TB_SHADE_THREADS      256
 #define TB_QUEUE_SENTINEL     0x7fffffff
@@ -130,6 +132,7 @@ struct TbDevice {
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
+    int          tri_min, refetch_below;
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -204,6 +207,8 @@ extern "C" TbDevice* tb_device_create(int device_index) {
         const char* e = getenv("TERRA_B200_TRACE");
         static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128" };
         d->trace_kind = 0;
+        const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
+        const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
         for (int k = 0; e && k < 7; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
     }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
@@ -405,6 +410,7 @@ struct TbTraceArgs {
     unsigned long long* visit_counters;   // COUNT variant only: [0] nodes fetched, [1] triangles tested
     const uint4*  qnodes;       // quantised 32-byte nodes (tb_trace.cuh), or NULL
     float         grid_lo[3], grid_cell[3];
+    int           tri_min, refetch_below;   // rounds kernel tunables (tb_trace_v3.cuh)
 };
 
 #include "tb_trace_v1.cuh"
@@ -952,6 +958,7 @@ static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, 
     TB_CUDA(cudaEventRecord(e->a, st));
     TbTraceArgs c = a;
     c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
+    c.tri_min = d->tri_min; c.refetch_below = d->refetch_below;
     int kind = d->trace_kind;
     if (kind == TB_K_AUTO) kind = coherent ? TB_K_V2 : TB_K_V3Q;
     if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind);

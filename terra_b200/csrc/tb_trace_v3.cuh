@@ -17,7 +17,6 @@
 #pragma once
 
 #define TB_REF_POP  ((int)0x80000001)             /* lane must pop its stack next round */
-#define TB_TRI_MIN  8
 
 template <bool COUNT, bool EXACT, bool QUANT>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace_v3(TbTraceArgs a) {
@@ -86,7 +85,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
             const bool is_node = cur >= 0;
             const unsigned node_mask = __ballot_sync(FULL, is_node);
             const unsigned pend_mask = __ballot_sync(FULL, pend != TB_REF_DONE);
-            const bool tri_round = pend_mask != 0u && (__popc(pend_mask) >= TB_TRI_MIN || node_mask == 0u);
+            const bool tri_round = pend_mask != 0u && (__popc(pend_mask) >= a.tri_min || node_mask == 0u);
             const bool do_tri = tri_round && pend != TB_REF_DONE;
             // 4. all loads of the round first, so node and triangle latencies overlap
             float4 q0, q1, q2, q3, ta, tb, tc;
@@ -150,7 +149,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
             }
             // 7. leave the rounds when the warp is done or has too few rays left to be worth a round
             const unsigned live = __ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE);
-            if (live == 0u || (!exhausted && __popc(live) < TB_REFETCH_BELOW)) break;
+            if (live == 0u || (!exhausted && __popc(live) < a.refetch_below)) break;
         }
 
         // ---- retire finished rays (warp converged)
