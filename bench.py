@@ -202,6 +202,16 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def l2_roofline(lib, achieved):
+    """The north-star's second denominator: L2 bandwidth measured on this box by the
+    library's own probes over a 40 MB L2-resident buffer — (i) streaming 128-bit reads, the
+    denominator, (ii) random 64-byte record gathers, k_trace's access pattern, for information."""
+    stream = float(lib.terra_b200_probe_bandwidth(40 << 20, 0))
+    gather = float(lib.terra_b200_probe_bandwidth(40 << 20, 1))
+    return {"stream_gbs": stream, "gather_gbs": gather, "frac_of_stream": achieved / stream if stream else None,
+            "frac_of_gather": achieved / gather if gather else None}
+
+
 def profile_traffic(kernel, rays_per_launch):
     """DRAM bytes per launch of `kernel`: dram bytes/ray from the committed ncu --set full capture
     (profiles/traffic.json) x the rays one launch of this run processed. None without a capture."""
@@ -325,7 +335,7 @@ def run_render_arm(args):
         "data": "synthetic",
         "config": {"workload": wl["name"], "width": w, "height": h, "spp": spp, "bounces": int(s.options().bounces),
                    "integrator": "simple", "split": args.split if world > 1 else "none", "bvh": os.environ.get("TERRA_B200_BVH", "sah3"),
-                   "l2": "flushed between timed iterations (256 MiB write); path-state waves (4M slots x 144 B) exceed L2"},
+                   "l2": "flushed between timed iterations (256 MiB write); path-state waves (up to 64M slots x 80 B) exceed L2"},
         "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
         "gpu_launches": int(launches),
         "clocks": clk,
@@ -333,6 +343,7 @@ def run_render_arm(args):
                      "frac": achieved / peak, "traffic": profile_traffic("k_trace", rays_per_launch), "peak_source": peak_src,
                      "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
                      "rays_per_launch": rays_per_launch, "ms_per_launch": trace_ms_per_launch,
+                     "l2": l2_roofline(lib, achieved),
                      "note": "working set (nodes+tris ~11 MB) is L2-resident: the HBM figure is the contract's denominator, "
                              "the L2 fraction is in profiles/"},
         "extra": {"mrays_per_s": rays_all / args.steps / (ms_dev * 1e-3) / 1e6,
@@ -439,7 +450,8 @@ def run_traversal_arm(args):
         "gpu_launches": int(st.kernel_launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": profile_traffic("k_trace_" + args.workload, n_rays), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
-                     "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "counter": src, "ms_per_launch": k_ms},
+                     "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "counter": src, "ms_per_launch": k_ms,
+                     "l2": l2_roofline(lib, achieved)},
         "extra": {"scene_commit_s": commit_s, "hit_t_agreement_with_oracle": agree},
     }
     print(json.dumps(line), flush=True)

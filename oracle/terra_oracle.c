@@ -694,14 +694,81 @@ static f3 integrate_direct_mis(const OracleScene* s, const TerraObject* ob, cons
     return had(Lo, *thr);
 }
 
-static f3 integrate(const OracleScene* s, const TerraObject* ob, const TerraShadingSurface* sf,
+/* Debug views, Terra.c:1140-1337. All return zero past bounce 0. */
+static f3 integrate_debug_depth(const f3* ray_origin, const f3* p) {                    /* :1148-1157 */
+    const float far_plane = 500.f;
+    f3 ba = sub(*ray_origin, *p);
+    float d = sqrtf(dot(ba, ba)) / far_plane;
+    return mk(d, d, d);
+}
+static f3 integrate_debug_normals(const TerraShadingSurface* sf) {                       /* :1159-1198, terra_clampf3 TerraMath.inl:290-299 */
+    f3 nn = sf->normal, p, n, c = mk(0, 0, 0);
+    p.x = nn.x > 0.f ? nn.x : 0.f; p.y = nn.y > 0.f ? nn.y : 0.f; p.z = nn.z > 0.f ? nn.z : 0.f;
+    p.x = p.x < 1.f ? p.x : 1.f;   p.y = p.y < 1.f ? p.y : 1.f;   p.z = p.z < 1.f ? p.z : 1.f;
+    n.x = nn.x > -1.f ? nn.x : -1.f; n.y = nn.y > -1.f ? nn.y : -1.f; n.z = nn.z > -1.f ? nn.z : -1.f;
+    n.x = n.x < 0.f ? n.x : 0.f;   n.y = n.y < 0.f ? n.y : 0.f;   n.z = n.z < 0.f ? n.z : 0.f;
+    n = scl(n, -1.f);
+    c = add(c, scl(mk(1, 0, 0), p.x)); c = add(c, scl(mk(0, 1, 0), p.y)); c = add(c, scl(mk(0, 0, 1), p.z));
+    c = add(c, scl(mk(0, 1, 1), n.x)); c = add(c, scl(mk(1, 0, 1), n.y)); c = add(c, scl(mk(1, 1, 0), n.z));
+    return c;
+}
+static f3 integrate_debug_mis_weight(const OracleScene* s, const TerraObject* ob, const TerraShadingSurface* sf,
+                                     const f3* p, const f3* wo, const f3* thr) {          /* :1200-1337 */
+    f3 Lo = mk(0, 0, 0);
+    f3 bs;
+    { float e1 = randf(); float e2 = randf(); float e3 = randf(); bs = ob->material.bsdf.sample(sf, e1, e2, e3, wo); }
+    float pick_pdf;
+    float e = randf() - OEPS;
+    const OLight* l = pick_light(s, e, &pick_pdf);
+    size_t ti = (size_t)(randf() * s->objects[l->object].triangles_count);
+    f3 lp, ln;
+    { float e1 = randf(); float e2 = randf(); sample_light_triangle(s, l, ti, e1, e2, &lp, &ln); }
+    {
+        f3 to_light = sub(lp, *p), wi = unit(to_light);
+        TerraShadingSurface lsf;
+        f3 hp; size_t htri = 0;
+        int hobj = raycast(s, surface_ray_origin(sf, p), wi, &lsf, &hp, &htri);
+        if (hobj == l->object && htri == ti) {
+            float cs = dot(ln, neg(wi));
+            if (cs > 0) {
+                float bpdf = ob->material.bsdf.pdf(sf, &wi, wo);
+                float lpdf = sqlen(to_light) / fabsf(cs * l->tri_area[htri]);
+                Lo = add(Lo, mk(0, 0, (bpdf * bpdf) / (lpdf * lpdf + bpdf * bpdf)));
+            }
+        }
+    }
+    {
+        f3 wi = bs;
+        (void)ob->material.bsdf.eval(sf, &wi, wo);
+        float bpdf = ob->material.bsdf.pdf(sf, &wi, wo);
+        TerraShadingSurface lsf;
+        f3 hp; size_t htri = 0;
+        int hobj = raycast(s, surface_ray_origin(sf, p), wi, &lsf, &hp, &htri);
+        if (hobj == l->object) {
+            float NoW = dot(lsf.normal, neg(wi));
+            if (NoW > 0) {
+                f3 dl = sub(*p, hp);
+                float dist = dot(dl, dl);
+                float lpdf = dist / (NoW * tri_area(&s->objects[hobj].triangles[htri]));
+                Lo = add(Lo, mk((bpdf * bpdf) / (lpdf * lpdf + bpdf * bpdf), 0, 0));
+            }
+        }
+    }
+    return had(Lo, *thr);
+}
+
+static f3 integrate(const OracleScene* s, const f3* ray_origin, const TerraObject* ob, const TerraShadingSurface* sf,
                     const f3* p, const f3* wo, const f3* thr, size_t bounce) {           /* Terra.c:1099-1138 */
     switch (s->opts.integrator) {
         case kTerraIntegratorSimple:                                                     /* :1339-1347 */
             return dot(*wo, sf->normal) > 0 ? had(sf->emissive, *thr) : mk(0, 0, 0);
         case kTerraIntegratorDirect:    return integrate_direct(s, ob, sf, p, wo, thr, bounce);
         case kTerraIntegratorDirectMis: return integrate_direct_mis(s, ob, sf, p, wo, thr, bounce);
-        default:                        return mk(0, 0, 0);    /* debug views: not restated */
+        case kTerraIntegratorDebugMono:       return bounce != 0 ? mk(0, 0, 0) : mk(1, 1, 1);   /* :1140-1146 */
+        case kTerraIntegratorDebugDepth:      return bounce != 0 ? mk(0, 0, 0) : integrate_debug_depth(ray_origin, p);
+        case kTerraIntegratorDebugNormals:    return bounce != 0 ? mk(0, 0, 0) : integrate_debug_normals(sf);
+        case kTerraIntegratorDebugMisWeights: return bounce != 0 ? mk(0, 0, 0) : integrate_debug_mis_weight(s, ob, sf, p, wo, thr);
+        default:                        return mk(0, 0, 0);
     }
 }
 
@@ -715,7 +782,7 @@ static f3 trace_path(const OracleScene* s, f3 o, f3 d) {
         if (obj < 0) break;       /* the environment lookup's result is discarded by the reference (:1054-1057) */
         const TerraObject* ob = &s->objects[obj];
         f3 wo = neg(d);
-        Lo = add(Lo, integrate(s, ob, &sf, &p, &wo, &thr, bounce));
+        Lo = add(Lo, integrate(s, &o, ob, &sf, &p, &wo, &thr, bounce));
         float e0 = randf(); float e1 = randf(); float e2 = randf();
         f3 wi = ob->material.bsdf.sample(&sf, e0, e1, e2, &wo);
         float pdf = fmx(ob->material.bsdf.pdf(&sf, &wi, &wo), OEPS);

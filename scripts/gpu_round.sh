@@ -14,7 +14,7 @@ echo "== bench c3_1m"; timeout 900 python bench.py --workload c3_1m --steps 3 > 
 NCU_CMD="python bench.py --steps 1 --warmup 3 --spp 8 --no-cpu-baseline"
 echo "== ncu launch list"
 $NCU_CMD > $OUT/${TAG}_ncu_plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 300 --csv --log-file $OUT/${TAG}_launches.csv $NCU_CMD > $OUT/${TAG}_ncu_launches.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_launches.csv $NCU_CMD > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
 echo "== ncu full capture of k_trace"
 ncu --set full --clock-control none --import-source on -k regex:k_trace -s 8 -c 3 -f -o $OUT/${TAG}_k_trace $NCU_CMD > $OUT/${TAG}_ncu_full.log 2>&1

@@ -600,6 +600,75 @@ __device__ __forceinline__ TbLightSample tb_sample_light(const TbDevScene& sc, u
 // terra_surface_ray, Terra.c:1715-1724 (sign = +1)
 __device__ __forceinline__ V3 tb_surface_ray_origin(const TbSurface& s, V3 point) { return vadd(point, vmul(s.n, 0.0001f * 1.f)); }
 
+// Debug views, terra_integrate_debug_{mono,depth,normals,mis_weight} (Terra.c:1140-1337). All of them
+// return zero past bounce 0, so the host loop runs one bounce only. `ray_origin` is the caller's ray
+// origin (what terra_integrate_debug_depth sees), not the one terra_scene_raycast moved by 1e-3 * dir.
+__device__ __forceinline__ V3 tb_integrate_debug(const TbDevScene& sc, int integ, TbSurface& s, const TbHitInfo& info,
+                                                 V3 point, V3 ray_origin, V3 wo, V3 thr, uint64_t key, uint32_t dim0,
+                                                 const float4* aux_hit, int preset) {
+    if (integ == kTerraIntegratorDebugMono) return v3s(1.f);
+    if (integ == kTerraIntegratorDebugDepth) {                                 // :1148-1157
+        const float far_plane = 500.f;
+        return v3s(vlen(vsub(ray_origin, point)) / far_plane);
+    }
+    if (integ == kTerraIntegratorDebugNormals) {                               // :1159-1198
+        // terra_clampf3 (TerraMath.inl:290-299): max first, then min, `>` / `<` as written
+        V3 p, n;
+        p.x = s.n.x > 0.f ? s.n.x : 0.f; p.y = s.n.y > 0.f ? s.n.y : 0.f; p.z = s.n.z > 0.f ? s.n.z : 0.f;
+        p.x = p.x < 1.f ? p.x : 1.f;     p.y = p.y < 1.f ? p.y : 1.f;     p.z = p.z < 1.f ? p.z : 1.f;
+        n.x = s.n.x > -1.f ? s.n.x : -1.f; n.y = s.n.y > -1.f ? s.n.y : -1.f; n.z = s.n.z > -1.f ? s.n.z : -1.f;
+        n.x = n.x < 0.f ? n.x : 0.f;     n.y = n.y < 0.f ? n.y : 0.f;     n.z = n.z < 0.f ? n.z : 0.f;
+        n = vmul(n, -1.f);
+        V3 c = v3s(0.f);
+        c = vadd(c, vmul(v3(1, 0, 0), p.x)); c = vadd(c, vmul(v3(0, 1, 0), p.y)); c = vadd(c, vmul(v3(0, 0, 1), p.z));
+        c = vadd(c, vmul(v3(0, 1, 1), n.x)); c = vadd(c, vmul(v3(1, 0, 1), n.y)); c = vadd(c, vmul(v3(1, 1, 0), n.z));
+        return c;
+    }
+    // ---- kTerraIntegratorDebugMisWeights, :1200-1337: blue = weight of the light sample, red = of the BSDF sample
+    V3 Lo = v3s(0.f);
+    if (sc.n_lights <= 0) return Lo;
+    const V3 bsdf_sample = tb_bsdf_sample(preset, s, tb_randf_libc(key, dim0 + TB_DIM_MIS0), tb_randf_libc(key, dim0 + TB_DIM_MIS1),
+                                          tb_randf_libc(key, dim0 + TB_DIM_MIS2), wo);
+    const TbLightSample ls = tb_sample_light(sc, key, dim0);
+    {
+        const V3 p_to_light = vsub(ls.pos, point);
+        const V3 wi = vnorm(p_to_light);
+        const float4 ah = aux_hit[0];
+        if (ah.x >= 0.f && (uint32_t)__float_as_int(ah.y) == ls.rank) {
+            const float cosl = vdot(ls.norm, vneg(wi));
+            if (cosl > 0) {
+                const float bsdf_pdf = tb_bsdf_pdf(preset, s, wi, wo);
+                const float light_pdf = vsqlen(p_to_light) / fabsf(cosl * ls.tri_area);
+                const float weight = (bsdf_pdf * bsdf_pdf) / (light_pdf * light_pdf + bsdf_pdf * bsdf_pdf);
+                Lo = vadd(Lo, v3(0.f, 0.f, weight));
+            }
+        }
+    }
+    {
+        const V3 wi = bsdf_sample;
+        const float bsdf_pdf = tb_bsdf_pdf(preset, s, wi, wo);
+        const float4 bh = aux_hit[1];
+        if (bh.x >= 0.f) {
+            const V3 bo = tb_offset_origin(tb_surface_ray_origin(s, point), wi);
+            const V3 bpoint = vadd(bo, vmul(wi, bh.x));
+            TbHitInfo binfo;
+            const TbSurface bsurf = tb_surface_init(sc, __float_as_int(bh.y), bpoint, &binfo);
+            if (binfo.object == sc.lights[ls.light].object) {
+                const float NoW = vdot(bsurf.n, vneg(wi));
+                if (NoW > 0) {
+                    const float dist = vsqdist(bpoint, point);
+                    const V3 ab = vsub(binfo.b, binfo.a), ac = vsub(binfo.c, binfo.a);
+                    const float area = vlen(vcross(ab, ac)) / 2;
+                    const float light_pdf = dist / (NoW * area);
+                    const float weight = (bsdf_pdf * bsdf_pdf) / (light_pdf * light_pdf + bsdf_pdf * bsdf_pdf);
+                    Lo = vadd(Lo, v3(weight, 0.f, 0.f));
+                }
+            }
+        }
+    }
+    return vpoint(Lo, thr);
+}
+
 template <int PRESET, int STAGE>
 __global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
     const int count = *a.q_count;
@@ -626,8 +695,10 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
             TbSurface s = tb_surface_init(sc, __float_as_int(h4.y), point, &info);
             const V3 wo = vneg(d);
             const int integ = sc.integrator;
-            const bool direct = integ == kTerraIntegratorDirect || integ == kTerraIntegratorDirectMis;
-            const bool mis = integ == kTerraIntegratorDirectMis;
+            const bool dbg_mis = integ == kTerraIntegratorDebugMisWeights;            // bounce 0 only (host loop)
+            const bool direct = integ == kTerraIntegratorDirect || integ == kTerraIntegratorDirectMis || dbg_mis;
+            const bool mis = integ == kTerraIntegratorDirectMis || dbg_mis;
+            const bool debug = integ > kTerraIntegratorDirectMis;
 
             if (STAGE == 0) {
                 // ---- emit the visibility rays of terra_integrate_direct / _direct_mis
@@ -647,7 +718,9 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
                 const float4 t4 = a.thr[slot];
                 V3 thr = v3(t4.x, t4.y, t4.z);
                 V3 Lo = v3s(0.f);
-                if (!direct) {                                                 // simple, :1339-1347
+                if (debug) {
+                    Lo = tb_integrate_debug(sc, integ, s, info, point, v3(o4.x, o4.y, o4.z), wo, thr, key, dim0, a.aux_hit + (size_t)slot * 2, PRESET);
+                } else if (!direct) {                                          // simple, :1339-1347
                     if (vdot(wo, s.n) > 0) Lo = vpoint(s.emissive, thr);
                 } else {
                     if (a.bounce == 0 && vdot(wo, s.n) > 0) Lo = vadd(Lo, s.emissive);
@@ -720,7 +793,8 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
                     a.lo[slot] = make_float4(l4.x + Lo.x, l4.y + Lo.y, l4.z + Lo.z, 0.f);   // Lo = Lo + radiance, :1063
                 }
                 // ---- continue the path (terra_trace, Terra.c:1065-1093)
-                if (a.bounce < sc.bounces) {
+                // (debug views add nothing after bounce 0, :1140-1337: their paths end here)
+                if (a.bounce < sc.bounces && !debug) {
                     const float e0 = tb_randf_libc(key, dim0 + TB_DIM_BSDF0), e1 = tb_randf_libc(key, dim0 + TB_DIM_BSDF1);
                     const float e2 = tb_randf_libc(key, dim0 + TB_DIM_BSDF2);
                     const V3 wi = tb_bsdf_sample(PRESET, s, e0, e1, e2, wo);
@@ -988,11 +1062,14 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
     tb_wave_reserve(&d->wave, px_per_wave * s_per_wave);
     TbWave& wv = d->wave;
     const TbDevScene& sc = d->sc;
-    const bool direct = sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis;
-    if (sc.integrator > kTerraIntegratorDirectMis) {
-        terra_log("terra_b200: integrator %d (debug views) is not implemented on the GPU path\n", sc.integrator);
+    const bool direct = sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis ||
+                        sc.integrator == kTerraIntegratorDebugMisWeights;
+    if (sc.integrator < 0 || sc.integrator > kTerraIntegratorDebugMisWeights) {
+        terra_log("terra_b200: unknown integrator %d\n", sc.integrator);      // assert(false), Terra.c:1134
         abort();
     }
+    // debug views (Terra.c:1140-1337) contribute at bounce 0 only: one trace + one shade per wave
+    const int last_bounce = sc.integrator > kTerraIntegratorDirectMis ? 0 : sc.bounces;
     const int shade_grid = d->sm_count * 4;
     for (size_t p0 = 0; p0 < npx; p0 += px_per_wave) {
         const size_t np = npx - p0 < px_per_wave ? npx - p0 : px_per_wave;
@@ -1010,7 +1087,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
             k_raygen<<<d->sm_count * 8, 256, 0, st>>>(rg);
             d->stats.kernel_launches += 2;
             int cur = 0;
-            for (int bounce = 0; bounce <= sc.bounces; ++bounce) {
+            for (int bounce = 0; bounce <= last_bounce; ++bounce) {
                 k_counters<<<1, 1, 0, st>>>(wv.counters, 1, 0);
                 TbTraceArgs ta;
                 memset(&ta, 0, sizeof ta);

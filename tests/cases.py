@@ -22,6 +22,12 @@ RENDER_CASES = {      # name -> cornell kwargs (jitter 0 => deterministic camera
     "simple_phong": dict(integrator=0, spp=4, bounces=8, jitter=0.0, materials="phong"),
     "direct_phong": dict(integrator=1, spp=4, bounces=4, jitter=0.0, materials="phong"),
     "mis_phong": dict(integrator=2, spp=4, bounces=4, jitter=0.0, materials="phong"),
+    # debug views, Terra.c:1140-1337 (mono / depth / normals are deterministic per pixel at jitter 0)
+    "debug_mono": dict(integrator=3, spp=2, bounces=2, jitter=0.0, materials="diffuse"),
+    "debug_depth": dict(integrator=4, spp=2, bounces=2, jitter=0.0, materials="diffuse"),
+    "debug_normals": dict(integrator=5, spp=2, bounces=2, jitter=0.0, materials="phong"),
+    "debug_mis_diffuse": dict(integrator=6, spp=4, bounces=2, jitter=0.0, materials="diffuse"),
+    "debug_mis_phong": dict(integrator=6, spp=4, bounces=2, jitter=0.0, materials="phong"),
 }
 RENDER_SIZE = (32, 32)
 

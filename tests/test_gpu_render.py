@@ -146,6 +146,57 @@ def test_converged_image_matches_cpu_renderer(api, scenes, gpu, oracle, name):
     assert (relj <= MEAN_TOL + 4 * sem + 0.003).all(), relj
 
 
+# ----------------------------------------------------------------------------- debug views
+@pytest.mark.parametrize("name", ["debug_mono", "debug_depth", "debug_normals"])
+@pytest.mark.parametrize("bvh_mode", [0, 1], ids=["reference_tree", "sah3_tree"])
+def test_debug_views_bit_exact_vs_reference_fixture(api, scenes, gpu, name, bvh_mode):
+    """terra_integrate_debug_{mono,depth,normals} (Terra.c:1140-1198) are deterministic per pixel at
+    jitter 0: the accumulated image must equal the fixture rendered by the unmodified reference bit
+    for bit (reference tree: every pixel; three-axis tree: every pixel outside exact-t ties)."""
+    g = golden("renders.npz")
+    w, h = cases.RENDER_SIZE
+    gpu.terra_b200_set_bvh_mode(bvh_mode)
+    try:
+        s, cam = scenes.cornell(gpu, **cases.RENDER_CASES[name])
+        res, _ = s.render(cam, w, h)
+        s.destroy()
+    finally:
+        gpu.terra_b200_set_bvh_mode(1)
+    assert np.array_equal(res["samples"], g[f"{name}_samples"])
+    same = (res["acc"].view(np.uint32) == g[f"{name}_acc"].view(np.uint32)).all(axis=-1)
+    if bvh_mode == 0:
+        assert same.all(), np.argwhere(~same)[:8]
+    else:
+        assert same.mean() > 0.97, same.mean()
+
+
+@pytest.mark.parametrize("materials", ["diffuse", "phong"])
+def test_debug_mis_weights_vs_cpu_renderer(api, scenes, gpu, oracle, materials):
+    """terra_integrate_debug_mis_weight (Terra.c:1200-1337): red = power-heuristic weight of the BSDF
+    sample, blue = of the light sample, green = 0. Statistical (rand()-driven): channel means of the
+    GPU image against the CPU renderer's at matched spp, within 2 % + the CPU run-to-run spread."""
+    w, h, spp = 47, 40, 256
+    kw = dict(integrator=6, materials=materials, bounces=2)
+    ref = api.TerraLib(api.REFERENCE_LIB) if api.REFERENCE_LIB.exists() else None
+    nproc = min(8, os.cpu_count() or 1)
+    build = lambda lib: scenes.cornell(lib, spp=spp, jitter=0.0, **kw)
+    A = radiance(cpu_render(api, scenes, ref, oracle, build, w, h, spp, 3, nproc))
+    B = radiance(cpu_render(api, scenes, ref, oracle, build, w, h, spp, 4, nproc))
+    s, cam = build(gpu)
+    gpu.terra_b200_set_seed(s.h, 5)
+    G = radiance(s.render(cam, w, h, passes=4)[0])
+    s.destroy()
+    assert not G[..., 1].any() and not A[..., 1].any()
+    assert G.min() >= 0 and G.max() <= 1.0 + 1e-6          # each weight is in [0,1]
+    for ch in (0, 2):
+        cpu = (A[..., ch].mean() + B[..., ch].mean()) / 2
+        spread = abs(A[..., ch].mean() - B[..., ch].mean())
+        assert cpu > 0
+        assert abs(G[..., ch].mean() - cpu) <= 0.02 * cpu + 2 * spread, (ch, G[..., ch].mean(), cpu, spread)
+    rmse = lambda x, y: float(np.sqrt(((x - y) ** 2).mean()))
+    assert max(rmse(G, A), rmse(G, B)) <= RMSE_FACTOR * rmse(A, B), (rmse(G, A), rmse(G, B), rmse(A, B))
+
+
 # ----------------------------------------------------------------------------- accumulate + tonemap
 @pytest.mark.parametrize("op", range(5))
 def test_tonemap_vs_oracle(api, scenes, gpu, oracle, op):
