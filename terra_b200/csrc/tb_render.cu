@@ -132,6 +132,10 @@ struct TbDevice {
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
+    int          v4_opt;            // k_trace_v4 OPT bits (tb_trace_v4.cuh)
+    int          coherent_kind;     // TB_K_* used for camera-ray launches when trace_kind is auto
+    int          incoherent_kind;   // TB_K_* used for incoherent launches when trace_kind is auto
+    int          tile_pixels;  // 1: waves walk the region in 8x4 pixel tiles (TERRA_B200_TILE=0 turns it off)
     int          tri_min, refetch_below;
 };
 
@@ -205,11 +209,19 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->exact_boxes = 0;
     {
         const char* e = getenv("TERRA_B200_TRACE");
-        static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128" };
+        static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128", "v4", "v4q", "packet" };
         d->trace_kind = 0;
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
+        const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
-        for (int k = 0; e && k < 7; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
+        for (int k = 0; e && k < 10; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
+        const char* vo = getenv("TERRA_B200_V4_OPT"); d->v4_opt = vo ? (atoi(vo) & 3) : 3;       // measured on B200: 256-bit loads +1.7 %, single pop +10 % (C3 1M)
+        const char* ik = getenv("TERRA_B200_INCOHERENT");      // kernel for bounce / visibility / API rays (A/B runs)
+        d->incoherent_kind = 8;                                 // TB_K_V4Q
+        for (int k = 1; ik && k < 9; ++k) if (strcmp(ik, names[k]) == 0) d->incoherent_kind = k;
+        const char* ck = getenv("TERRA_B200_COHERENT");         // kernel for camera rays (A/B runs)
+        d->coherent_kind = 9;                                   // TB_K_PACKET
+        for (int k = 1; ck && k < 10; ++k) if (strcmp(ck, names[k]) == 0) d->coherent_kind = k;
     }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
@@ -319,7 +331,14 @@ struct TbRay {
     int   kx, ky, kz;
 };
 
-__device__ __forceinline__ float tb_sel(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+// Axis select as two SELPs: written as a ternary the compiler sank the nine vertex subtractions of
+// tb_triangle into per-axis branches (BSSY/BRA/BSYNC per select, divergent across lanes).
+__device__ __forceinline__ float tb_sel(V3 v, int k) {
+    float r;
+    asm("{\n\t.reg .pred p0, p1;\n\tsetp.eq.s32 p0, %4, 0;\n\tsetp.eq.s32 p1, %4, 1;\n\t"
+        "selp.f32 %0, %2, %3, p1;\n\tselp.f32 %0, %1, %0, p0;\n\t}" : "=&f"(r) : "f"(v.x), "f"(v.y), "f"(v.z), "r"(k));
+    return r;
+}
 
 __device__ __forceinline__ V3 tb_offset_origin(V3 o, V3 d) { return vadd(o, vmul(d, 0.001f)); }
 
@@ -416,6 +435,8 @@ struct TbTraceArgs {
 #include "tb_trace_v1.cuh"
 #include "tb_trace.cuh"
 #include "tb_trace_v3.cuh"
+#include "tb_trace_v4.cuh"
+#include "tb_trace_packet.cuh"
 
 // ==================================================================================== K1: ray generation
 struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot = s_local * n_pixels + p_local
@@ -425,6 +446,7 @@ struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot
     int      s0, n_samples;    // sample range of this batch (relative to sample_base)
     uint32_t sample_base;
     uint64_t seed;
+    int      tiled;            // 1: region-linear index q walks 8x4 pixel tiles (w % 8 == 0 && h % 4 == 0)
 };
 
 struct TbRaygenArgs {
@@ -435,11 +457,43 @@ struct TbRaygenArgs {
     int*    queue;
 };
 
+// Region-linear index -> pixel offset inside the region. Tiled: consecutive indices fill an 8x4 pixel
+// tile, so the 32 camera rays of a warp span 8x4 pixels instead of 32x1 (more coherent traversal).
+__device__ __forceinline__ void tb_region_pixel(const TbBatch& b, int pr, int* rx, int* ry) {
+    if (b.tiled) {
+        const int tile = pr >> 5, in = pr & 31, tiles_x = b.w >> 3;
+        const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+        *rx = tx * 8 + (in & 7);
+        *ry = ty * 4 + (in >> 3);
+    } else {
+        *ry = pr / b.w;
+        *rx = pr - *ry * b.w;
+    }
+}
+
+// Wave slot <-> (pixel of the batch, sample of the batch). Linear: sample-major. Tiled: the samples of one
+// 8x4 tile are adjacent — slot = (tile * n_samples + s) * 32 + lane — so consecutive warps of the trace
+// kernels walk the SAME part of the tree (node fetches hit L1) and the bounce rays of a tile stay together.
+__device__ __forceinline__ int tb_slot_of(const TbBatch& b, int p_local, int s_local) {
+    if (b.tiled) return ((p_local >> 5) * b.n_samples + s_local) * 32 + (p_local & 31);
+    return s_local * b.n_pixels + p_local;
+}
+
 __device__ __forceinline__ void tb_slot_to_pixel(const TbBatch& b, int slot, int* px, int* py, uint32_t* sample) {
-    const int s_local = slot / b.n_pixels;
-    const int pr = b.p0 + (slot - s_local * b.n_pixels);
-    *py = b.y + pr / b.w;
-    *px = b.x + pr % b.w;
+    int s_local, p_local;
+    if (b.tiled) {
+        const int group = slot / (32 * b.n_samples), within = slot - group * (32 * b.n_samples);
+        s_local = within >> 5;
+        p_local = group * 32 + (within & 31);
+    } else {
+        s_local = slot / b.n_pixels;
+        p_local = slot - s_local * b.n_pixels;
+    }
+    const int pr = b.p0 + p_local;
+    int rx, ry;
+    tb_region_pixel(b, pr, &rx, &ry);
+    *py = b.y + ry;
+    *px = b.x + rx;
     *sample = b.sample_base + (uint32_t)(b.s0 + s_local);
 }
 
@@ -844,12 +898,15 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
 // the float sum order is the reference's and the result is deterministic — no atomics).
 __global__ void __launch_bounds__(256) k_accumulate(TbBatch b, const float4* lo, float4* acc) {
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < b.n_pixels; p += gridDim.x * blockDim.x) {
-        float4 s = acc[b.p0 + p];
+        int rx, ry;
+        tb_region_pixel(b, b.p0 + p, &rx, &ry);
+        const int at = ry * b.w + rx;                      // acc is region-linear, row-major
+        float4 s = acc[at];
         for (int k = 0; k < b.n_samples; ++k) {
-            const float4 l = lo[(size_t)k * b.n_pixels + p];
+            const float4 l = lo[tb_slot_of(b, p, k)];
             s.x = s.x + l.x; s.y = s.y + l.y; s.z = s.z + l.z;
         }
-        acc[b.p0 + p] = s;
+        acc[at] = s;
     }
 }
 
@@ -999,7 +1056,7 @@ static void tb_drain_events(TbDevice* d) {
 // bounce / visibility / API rays are incoherent and bound by L1 wavefronts AND by issue slots at 7 of 32
 // lanes, where the rounds kernel over 32-byte quantised nodes is fastest (3.9 vs 2.8 Grays/s on C3).
 // TERRA_B200_TRACE=v1|v2|v3|v3q|quant|ld128 forces one kernel for every launch (A/B runs).
-enum { TB_K_AUTO = 0, TB_K_V1, TB_K_V2, TB_K_V3, TB_K_V3Q, TB_K_QUANT, TB_K_LD128 };
+enum { TB_K_AUTO = 0, TB_K_V1, TB_K_V2, TB_K_V3, TB_K_V3Q, TB_K_QUANT, TB_K_LD128, TB_K_V4, TB_K_V4Q, TB_K_PACKET };
 
 template <bool COUNT>
 static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind) {
@@ -1011,6 +1068,38 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         memcpy(c.grid_cell, d->grid_cell, sizeof c.grid_cell);
     }
     if (kind == TB_K_V1) { k_trace_v1<COUNT><<<grid, TB_TRACE_THREADS, 0, st>>>(c); return; }
+    if (kind == TB_K_PACKET && !COUNT) {
+        static const int occ = getenv("TERRA_B200_PACKET_OCC") ? atoi(getenv("TERRA_B200_PACKET_OCC")) : 8;
+        if (d->exact_boxes)  k_trace_packet<true, 8><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else if (occ == 12)  k_trace_packet<false, 12><<<d->sm_count * 12, TB_TRACE_THREADS, 0, st>>>(c);
+        else if (occ == 10)  k_trace_packet<false, 10><<<d->sm_count * 10, TB_TRACE_THREADS, 0, st>>>(c);
+        else                 k_trace_packet<false, 8><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        return;
+    }
+    const bool spill = d->stack_bound > TB_V4_DEPTH;
+    if (kind == TB_K_V4 || kind == TB_K_V4Q) {
+        const bool q = kind == TB_K_V4Q && have_q && !d->exact_boxes;
+        if (d->exact_boxes) {
+            if (spill) k_trace_v4<COUNT, true, false, true, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+            else       k_trace_v4<COUNT, true, false, false, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        } else if (q) {
+            const int opt = COUNT ? 0 : d->v4_opt;
+            switch (opt * 2 + (spill ? 1 : 0)) {
+                case 0: k_trace_v4<COUNT, false, true, false, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                case 1: k_trace_v4<COUNT, false, true, true, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                case 2: k_trace_v4<false, false, true, false, 1><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                case 3: k_trace_v4<false, false, true, true, 1><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                case 4: k_trace_v4<false, false, true, false, 2><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                case 5: k_trace_v4<false, false, true, true, 2><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                case 6: k_trace_v4<false, false, true, false, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+                default: k_trace_v4<false, false, true, true, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+            }
+        } else {
+            if (spill) k_trace_v4<COUNT, false, false, true, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+            else       k_trace_v4<COUNT, false, false, false, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        }
+        return;
+    }
     if (d->exact_boxes) {           // reference tree: the reference's own box arithmetic, float nodes
         if (kind == TB_K_V3 || kind == TB_K_V3Q) k_trace_v3<COUNT, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
         else k_trace<COUNT, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
@@ -1034,7 +1123,8 @@ static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, 
     c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
     c.tri_min = d->tri_min; c.refetch_below = d->refetch_below;
     int kind = d->trace_kind;
-    if (kind == TB_K_AUTO) kind = coherent ? TB_K_V2 : TB_K_V3Q;
+    if (kind == TB_K_AUTO) kind = coherent ? d->coherent_kind : d->incoherent_kind;
+    if (kind == TB_K_PACKET && d->counting) kind = TB_K_V2;     // the work counters mean the per-ray walk
     if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind);
     else             tb_launch_trace_kernel<false>(d, st, c, kind);
     TB_CUDA(cudaEventRecord(e->b, st));
@@ -1079,6 +1169,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
             b.x = (int)x; b.y = (int)y; b.w = (int)w; b.h = (int)h; b.fbw = (int)fbw; b.fbh = (int)fbh;
             b.p0 = (int)p0; b.n_pixels = (int)np; b.s0 = (int)s0; b.n_samples = (int)ns;
             b.sample_base = (uint32_t)sample_base; b.seed = seed;
+            b.tiled = (d->tile_pixels && w % 8 == 0 && h % 4 == 0 && np % 32 == 0 && p0 % 32 == 0) ? 1 : 0;
             const int n_paths = (int)(np * ns);
             TbRaygenArgs rg;
             rg.batch = b; rg.cam = *cam; rg.jitter = sc.jitter;
