@@ -40,6 +40,7 @@ sys.path.insert(0, str(REPO))
 WORKLOADS = {
     "c1": dict(name="C1 Cornell 36 tris Lambert+emissive 256x256 16spp bounces 8", w=256, h=256, spp=16),
     "c2": dict(name="C2 100k-tri sphere field, mixed Lambert/GGX, 1920x1080, 256 spp, bounces 4", w=1920, h=1080, spp=256),
+    "c4": dict(name="C4 10M-tri displaced terrain + emissive quads + HDR lat-long env, 3840x2160, 1024 spp, bounces 4", w=3840, h=2160, spp=1024),
     "c5": dict(name="C5 glass+metal divergence stress, 1920x1080, 512 spp, bounces 32 + RR", w=1920, h=1080, spp=512),
     "c3_1m": dict(name="C3 traversal: 64M incoherent rays vs 1M-triangle terrain", rays=64_000_000, tris=1_000_000),
     "c3_10m": dict(name="C3 traversal: 64M incoherent rays vs 10M-triangle terrain", rays=64_000_000, tris=10_000_000),
@@ -51,6 +52,8 @@ def build_scene(lib, scenes, workload, spp):
         return scenes.cornell(lib, spp=spp, bounces=8)
     if workload == "c2":
         return scenes.sphere_field(lib, spp=spp, bounces=4, ggx=True)
+    if workload == "c4":
+        return scenes.terrain(lib, n_tris=10_000_000, extent=10000.0, spp=spp, bounces=4, env_tex=scenes.procedural_sky())
     if workload == "c5":
         return scenes.glass_metal(lib, spp=spp, bounces=32)
     raise ValueError(workload)
@@ -212,6 +215,12 @@ def l2_roofline(lib, achieved):
             "frac_of_gather": achieved / gather if gather else None}
 
 
+def commit_ms(lib, s):
+    out = (C.c_float * 4)()
+    lib.terra_b200_commit_ms(s.h, out)
+    return {"bvh_build": out[0], "flatten": out[1], "quantise": out[2], "upload": out[3]}
+
+
 def profile_traffic(kernel, rays_per_launch):
     """DRAM bytes per launch of `kernel`: dram bytes/ray from the committed ncu --set full capture
     (profiles/traffic.json) x the rays one launch of this run processed. None without a capture."""
@@ -349,7 +358,7 @@ def run_render_arm(args):
         "extra": {"mrays_per_s": rays_all / args.steps / (ms_dev * 1e-3) / 1e6,
                   "rays_per_path": rays_all / args.steps / paths_per_step,
                   "trace_share_of_step": trace_ms / args.steps / ms_dev if ms_dev else None,
-                  "scene_commit_s": commit_s},
+                  "scene_commit_s": commit_s, "commit_ms": commit_ms(lib, s)},
     }
     if cpu_info is not None:
         v = float(np.mean(cpu_rates))
@@ -452,7 +461,7 @@ def run_traversal_arm(args):
                      "traffic": profile_traffic("k_trace_" + args.workload, n_rays), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
                      "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "counter": src, "ms_per_launch": k_ms,
                      "l2": l2_roofline(lib, achieved)},
-        "extra": {"scene_commit_s": commit_s, "hit_t_agreement_with_oracle": agree},
+        "extra": {"scene_commit_s": commit_s, "commit_ms": commit_ms(lib, s), "hit_t_agreement_with_oracle": agree},
     }
     print(json.dumps(line), flush=True)
 

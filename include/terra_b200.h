@@ -309,12 +309,20 @@ int         terra_b200_bvh_stack_bound(HTerraScene scene);   /* worst-case order
 int         terra_b200_build_host_bvh(HTerraScene scene, int mode, float* flat_nodes_out, float* flat_tris_out);
 /* Acceleration structure built by the next terra_scene_commit, process-wide:
  *   TERRA_B200_BVH_REFERENCE  the reference's tree (x-only SAH, src/TerraBVH.c:79-244), byte-identical nodes;
- *   TERRA_B200_BVH_SAH3       binned SAH over x,y,z in the same 64-byte node format (default).
+ *   TERRA_B200_BVH_SAH3       binned SAH over x,y,z in the same 64-byte node format (default);
+ *   TERRA_B200_BVH_LBVH       linear BVH built ON THE GPU in the same node format (replaces terra_bvh_create,
+ *                             src/TerraBVH.c:128-244, where the host build dominates time-to-first-pixel).
  * Closest hits do not depend on the choice (same triangles, same intersection arithmetic);
- * traversal work does. Also settable with the environment variable TERRA_B200_BVH=reference|sah3. */
+ * traversal work does. Also settable with the environment variable TERRA_B200_BVH=reference|sah3|lbvh. */
 #define TERRA_B200_BVH_REFERENCE 0
 #define TERRA_B200_BVH_SAH3      1
+#define TERRA_B200_BVH_LBVH      2
 void        terra_b200_set_bvh_mode(int mode);
+/* Wall time of the last terra_scene_commit's stages, ms: [0] tree build (terra_bvh_create's replacement),
+ * [1] flatten to the GPU layout, [2] node quantisation, [3] host->device upload. */
+void        terra_b200_commit_ms(HTerraScene scene, float* out4);
+/* Device time (kernels + sort) and time including the triangle upload of the last LBVH build, ms. */
+void        terra_b200_lbvh_build_ms(float* device_ms, float* with_upload_ms);
 
 /* Traversal micro-benchmark / parity entry points (= terra_scene_raycast without shading).
  * Host buffers: origins/dirs are n x 3 floats; the H2D/D2H copies are part of the call. */

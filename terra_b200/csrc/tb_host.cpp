@@ -17,6 +17,7 @@
 #include <time.h>
 
 #include <algorithm>
+#include <chrono>
 #include <mutex>
 #include <vector>
 
@@ -245,6 +246,7 @@ struct TbScene {
     std::vector<TbHostNode> nodes;   // the reference-layout BVH
     int               stack_bound;
     int               bvh_mode;
+    float             commit_ms[4];   // last commit: tree build, flatten, quantise, upload
     TbDevice*         dev;
     uint64_t          seed;
     bool              seed_fixed;
@@ -255,12 +257,16 @@ struct TbScene {
 static int g_device_index = 0;
 // Acceleration structure the next commit builds: 0 = the reference's tree (x-only SAH, TerraBVH.c),
 // 1 = binned SAH over three axes in the same node format (default; see tb_bvh.cpp).
-enum { TB_BVH_REFERENCE = 0, TB_BVH_SAH3 = 1 };
+// 2 = linear BVH built on the GPU (tb_lbvh.cu): the fast-build mode for large scenes.
+enum { TB_BVH_REFERENCE = 0, TB_BVH_SAH3 = 1, TB_BVH_LBVH = 2 };
+extern "C" void tb_lbvh_build(int device_index, const TerraObject* objects, int objects_count, std::vector<TbHostNode>* nodes_out, float* ms_out);
+static float g_lbvh_ms[2] = { 0.f, 0.f };
 static int g_bvh_mode = -1;
 static int bvh_mode() {
     if (g_bvh_mode >= 0) return g_bvh_mode;
     const char* e = getenv("TERRA_B200_BVH");
     if (e && strcmp(e, "reference") == 0) return TB_BVH_REFERENCE;
+    if (e && strcmp(e, "lbvh") == 0) return TB_BVH_LBVH;
     return TB_BVH_SAH3;
 }
 static void build_bvh(TbScene* s, int mode);
@@ -277,6 +283,7 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     s->dirty_objects = s->dirty_lights = s->has_bvh = false;
     s->stack_bound = 0;
     s->bvh_mode = -1;
+    memset(s->commit_ms, 0, sizeof s->commit_ms);
     s->dev = NULL;
     s->seed = 0;
     s->seed_fixed = false;
@@ -376,6 +383,10 @@ static V3 host_attr_eval(const TerraAttribute* a, V2 uv) {                      
 
 static void build_bvh(TbScene* s, int mode) {
     if (mode == TB_BVH_REFERENCE) tb_bvh_build(s->objects, (int)s->objects_pop, s->nodes);
+    else if (mode == TB_BVH_LBVH) {
+        if (tb_cuda_device_count() <= 0) tb_fatal("the lbvh build runs on the GPU: no CUDA device (there is no CPU fallback)");
+        tb_lbvh_build(g_device_index, s->objects, (int)s->objects_pop, &s->nodes, g_lbvh_ms);
+    }
     else tb_bvh_build_sah3(s->objects, (int)s->objects_pop, s->nodes);
     s->bvh_mode = mode;
 }
@@ -417,9 +428,15 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
     TbTextureTable table;
     TbDevAttr env = classify_attribute(&s->opts.environment_map, &table, "environment_map");
     if (dirty_accelerator || s->dirty_lights) {
+        typedef std::chrono::steady_clock Clock;
+        auto ms_since = [](Clock::time_point t0) { return std::chrono::duration<float, std::milli>(Clock::now() - t0).count(); };
+        Clock::time_point t0 = Clock::now();
         if (dirty_accelerator) build_bvh(s, bvh_mode());
+        s->commit_ms[0] = ms_since(t0);
+        t0 = Clock::now();
         TbFlatBvh flat;
         tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
+        s->commit_ms[1] = ms_since(t0);
         s->stack_bound = flat.stack_bound;
         std::vector<TbDevMaterial> mats(s->objects_pop);
         for (size_t i = 0; i < s->objects_pop; ++i) {
@@ -476,6 +493,7 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         up.env = env;
         up.stack_bound = flat.stack_bound;
         up.exact_boxes = s->bvh_mode == TB_BVH_REFERENCE ? 1 : 0;
+        t0 = Clock::now();
         TbQuantBvh quant;
         if (!up.exact_boxes) {
             tb_bvh_quantize(flat, &quant);
@@ -483,7 +501,10 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
             memcpy(up.grid_lo, quant.grid_lo, sizeof up.grid_lo);
             memcpy(up.grid_cell, quant.grid_cell, sizeof up.grid_cell);
         }
+        s->commit_ms[2] = ms_since(t0);
+        t0 = Clock::now();
         tb_device_upload(s->dev, &up);
+        s->commit_ms[3] = ms_since(t0);
         s->has_bvh = true;
     }
     tb_device_set_options(s->dev, &s->opts, &env);
@@ -556,6 +577,11 @@ extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;
     *nodes_count = (int)s->nodes.size();
     return s->nodes.data();
+}
+extern "C" void terra_b200_commit_ms(HTerraScene h, float* out4) { memcpy(out4, ((TbScene*)h)->commit_ms, 4 * sizeof(float)); }
+extern "C" void terra_b200_lbvh_build_ms(float* device_ms, float* with_upload_ms) {
+    if (device_ms) *device_ms = g_lbvh_ms[0];
+    if (with_upload_ms) *with_upload_ms = g_lbvh_ms[1];
 }
 extern "C" int terra_b200_bvh_stack_bound(HTerraScene h) { return ((TbScene*)h)->stack_bound; }
 // Host-only half of terra_scene_commit (no CUDA device needed): build the BVH and flatten it.

@@ -61,14 +61,18 @@ class DistRenderer:
     """Renders a full frame across the ranks of an initialised process group; rank 0 ends up with the
     reference's framebuffer contents (results[] and tonemapped pixels[])."""
 
-    def __init__(self, lib, scene, cam, width: int, height: int, mode: str = "samples", band: int = 8):
+    def __init__(self, lib, scene, cam, width: int, height: int, mode: str = "samples", band: int | None = None):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
         self.lib, self.scene, self.cam = lib, scene, cam
-        self.w, self.h, self.mode, self.band = width, height, mode, band
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.world = dist.get_world_size() if dist.is_initialized() else 1
+        if band is None:
+            # about four interleaved bands per rank (balance against per-call launch overhead: a band is
+            # one terra_b200_render_device call), a multiple of 4 rows so the 8x4 tiled wave layout applies
+            band = max(8, -(-height // (self.world * 4) // 4) * 4)
+        self.w, self.h, self.mode, self.band = width, height, mode, band
         self.dev = torch.device("cuda", torch.cuda.current_device())
         self.results = torch.zeros(width * height * 4, dtype=torch.float32, device=self.dev)
         self.pixels = torch.zeros(width * height * 3, dtype=torch.float32, device=self.dev)

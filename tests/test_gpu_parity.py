@@ -31,7 +31,7 @@ def assert_hits(gpu_hits, want, exact_ids):
         assert differ.mean() < 0.01          # exact-t ties only (t is already bit-identical everywhere)
 
 
-@pytest.fixture(params=[0, 1], ids=["reference_tree", "sah3_tree"])
+@pytest.fixture(params=[0, 1, 2], ids=["reference_tree", "sah3_tree", "gpu_lbvh_tree"])
 def bvh_mode(request, gpu):
     gpu.terra_b200_set_bvh_mode(request.param)
     yield request.param
