@@ -318,6 +318,13 @@ int         terra_b200_build_host_bvh(HTerraScene scene, int mode, float* flat_n
 #define TERRA_B200_BVH_SAH3      1
 #define TERRA_B200_BVH_LBVH      2
 void        terra_b200_set_bvh_mode(int mode);
+/* Extension mode "env-lit" (NOT the reference's behaviour): the reference evaluates the environment map on
+ * a miss, multiplies it into the throughput and then discards it — `//Lo = terra_addf3 ( &Lo, &throughput );`
+ * is commented out at src/Terra.c:1056 — so environment light contributes nothing. With on != 0 a path that
+ * leaves the scene adds throughput * environment_map(direction) (constant, 2-D texture or lat-long texture,
+ * src/Terra.c:468-477, 1804-1810). Off by default; call after terra_scene_commit. Checked against the
+ * reference compiled with exactly that one line restored (oracle/Makefile, "patched oracle"). */
+void        terra_b200_set_env_lit(HTerraScene scene, int on);
 /* Wall time of the last terra_scene_commit's stages, ms: [0] tree build (terra_bvh_create's replacement),
  * [1] flatten to the GPU layout, [2] node quantisation, [3] host->device upload. */
 void        terra_b200_commit_ms(HTerraScene scene, float* out4);

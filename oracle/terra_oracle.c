@@ -217,6 +217,7 @@ typedef struct { f3 power; float area; int object; float* tri_area; } OLight;   
 struct OracleScene {
     const TerraObject* objects;
     int                n_objects;
+    int                env_lit;      /* extension mode: Terra.c:1056 un-commented */
     TerraSceneOptions  opts;
     ONode*             nodes;
     int                n_nodes;
@@ -592,6 +593,7 @@ static f3 o_glass_eval(const TerraShadingSurface* s, const f3* wi, const f3* wo)
     return scl(s->attributes[0], s->attributes[2].x / NoL);
 }
 
+void oracle_set_env_lit(OracleScene* s, int on) { s->env_lit = on; }
 void terra_oracle_bsdf_diffuse_init(TerraBSDF* b) { b->sample = o_diffuse_sample; b->pdf = o_diffuse_pdf; b->eval = o_diffuse_eval; }
 void terra_oracle_bsdf_phong_init(TerraBSDF* b)   { b->sample = o_phong_sample;   b->pdf = o_phong_pdf;   b->eval = o_phong_eval; }
 void terra_oracle_bsdf_ggx_init(TerraBSDF* b)     { b->sample = o_ggx_sample;     b->pdf = o_ggx_pdf;     b->eval = o_ggx_eval; }
@@ -779,7 +781,14 @@ static f3 trace_path(const OracleScene* s, f3 o, f3 d) {
         TerraShadingSurface sf;
         f3 p;
         int obj = raycast(s, o, d, &sf, &p, NULL);
-        if (obj < 0) break;       /* the environment lookup's result is discarded by the reference (:1054-1057) */
+        if (obj < 0) {            /* the environment lookup's result is discarded by the reference (:1054-1057) */
+            if (s->env_lit) {     /* "patched oracle": the commented-out `Lo = Lo + throughput` of :1056 restored */
+                f3 env = attr_eval(&s->opts.environment_map, &d, &p);
+                thr = had(thr, env);
+                Lo = add(Lo, thr);
+            }
+            break;
+        }
         const TerraObject* ob = &s->objects[obj];
         f3 wo = neg(d);
         Lo = add(Lo, integrate(s, &o, ob, &sf, &p, &wo, &thr, bounce));

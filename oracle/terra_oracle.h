@@ -29,6 +29,10 @@ typedef struct { float t; uint32_t prim; float u, v; } OracleHit;     /* == Terr
 /* Builds the BVH (reference builder restated) and the light table over caller-owned objects. */
 OracleScene* oracle_scene_create(const TerraObject* objects, int n_objects, const TerraSceneOptions* opts);
 void         oracle_scene_destroy(OracleScene* s);
+/* Extension mode "env-lit" (SURVEY §8a row 12): a path that leaves the scene adds throughput * environment,
+ * i.e. the reference with the commented-out line Terra.c:1056 restored. Off by default (parity mode).
+ * Pinned against oracle/_ref/libterra_ref_envlit.so, the reference compiled with exactly that line restored. */
+void         oracle_set_env_lit(OracleScene* s, int on);
 const void*  oracle_bvh_nodes(const OracleScene* s, int* n_nodes);              /* 64-byte reference-layout nodes */
 
 /* terra_scene_raycast without shading, reference (un-culled, LIFO) walk. */

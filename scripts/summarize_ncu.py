@@ -17,6 +17,8 @@ if src.exists():
         if row.get("Metric Name") != "gpu__time_duration.sum":
             continue
         name = row["Kernel Name"].split("(")[0].replace("void ", "")
+        if name.startswith("k_probe_") or name.startswith("at::"):      # bench.py's own L2 probes / torch fills: not the path
+            continue
         v = float(row["Metric Value"].replace(",", ""))
         v *= {"ns": 1, "nsecond": 1, "us": 1e3, "usecond": 1e3, "ms": 1e6, "msecond": 1e6}[row["Metric Unit"]]
         tot[name] += v; cnt[name] += 1

@@ -164,6 +164,7 @@ class TerraLib:
             sig("terra_b200_device_count", C.c_int)
             sig("terra_b200_set_device", None, C.c_int)
             sig("terra_b200_probe_bandwidth", C.c_double, _sz, C.c_int)
+            sig("terra_b200_set_env_lit", None, _vp, C.c_int)
             sig("terra_b200_commit_ms", None, _vp, C.POINTER(C.c_float))
             sig("terra_b200_lbvh_build_ms", None, C.POINTER(C.c_float), C.POINTER(C.c_float))
             sig("terra_b200_set_seed", None, _vp, C.c_uint64)

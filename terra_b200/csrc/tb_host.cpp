@@ -572,6 +572,7 @@ extern "C" void terra_b200_set_seed(HTerraScene h, uint64_t seed) {
 }
 extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) { tb_device_get_stats(committed(h, "terra_b200_get_stats")->dev, out); }
 extern "C" void terra_b200_reset_stats(HTerraScene h) { tb_device_reset_stats(committed(h, "terra_b200_reset_stats")->dev); }
+extern "C" void terra_b200_set_env_lit(HTerraScene h, int on) { tb_device_set_env_lit(committed(h, "terra_b200_set_env_lit")->dev, on); }
 extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;

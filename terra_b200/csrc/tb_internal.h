@@ -76,6 +76,7 @@ struct TbDevScene {
     TbDevAttr            env;
     int32_t              integrator, bounces, tonemap, preset_mask;
     float                jitter, exposure, gamma, inv_gamma;
+    int32_t              env_lit;          // extension mode: a miss adds throughput * environment (Terra.c:1056 restored)
 };
 
 // ---------------------------------------------------------------- host scene
@@ -128,6 +129,7 @@ void      tb_device_bsdf_kat(TbDevice* dev, size_t object_idx, size_t n, const f
 void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
+void      tb_device_set_env_lit(TbDevice* dev, int on);
 int       tb_cuda_device_count(void);
 double    tb_device_probe_bandwidth(int device_index, size_t bytes, int mode);
 #ifdef __cplusplus

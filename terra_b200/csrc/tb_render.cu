@@ -893,6 +893,25 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
     }
 }
 
+// Env-lit extension mode (include/terra_b200.h, terra_b200_set_env_lit): the paths of this bounce that
+// left the scene add throughput * environment (Terra.c:1053-1057 with the commented-out line restored).
+// terra_attribute_eval(&environment_map, &ray.direction, ...): the direction is the lat-long lookup's
+// argument, and what a 2-D texture callback would read as its uv.
+__global__ void __launch_bounds__(256) k_miss(TbDevScene sc, const int* q, const int* q_count, const float4* ray_d,
+                                               const float4* hit, const float4* thr, float4* lo) {
+    const int count = *q_count;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = q[i];
+        if (hit[slot].x >= 0.f) continue;
+        const float4 d4 = ray_d[slot], t4 = thr[slot], l4 = lo[slot];
+        const V3 d = v3(d4.x, d4.y, d4.z);
+        V2 uv; uv.x = d.x; uv.y = d.y;
+        const V3 env = tb_attr_eval(sc.env, sc.textures, uv, d);
+        const V3 add = vpoint(v3(t4.x, t4.y, t4.z), env);
+        lo[slot] = make_float4(l4.x + add.x, l4.y + add.y, l4.z + add.z, 0.f);
+    }
+}
+
 // ==================================================================================== K6: accumulate + tonemap
 // Terra.c:551-567: acc = sum over the pixel's samples in sample order (one thread per pixel, so
 // the float sum order is the reference's and the result is deterministic — no atomics).
@@ -1190,6 +1209,10 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 ta.emit_prim = 0;
                 tb_launch_trace(d, st, ta, bounce == 0);
                 d->stats.kernel_launches += 1;
+                if (sc.env_lit && last_bounce == sc.bounces) {
+                    k_miss<<<d->sm_count * 4, 256, 0, st>>>(sc, wv.queue[cur], wv.counters + 1, wv.ray_d, wv.hit, wv.thr, wv.lo);
+                    d->stats.kernel_launches += 1;
+                }
                 TbShadeArgs sa;
                 sa.sc = sc;
                 sa.ray_o = wv.ray_o; sa.ray_d = wv.ray_d; sa.thr = wv.thr; sa.lo = wv.lo; sa.hit = wv.hit;
@@ -1475,6 +1498,7 @@ extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
 }
 
 extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; }
+extern "C" void tb_device_set_env_lit(TbDevice* d, int on) { d->sc.env_lit = on ? 1 : 0; }
 
 extern "C" void tb_device_reset_stats(TbDevice* d) {
     TB_CUDA(cudaSetDevice(d->index));
