@@ -18,6 +18,7 @@ import numpy as np
 REPO = Path(__file__).resolve().parent.parent
 PRODUCT_LIB = REPO / "terra_b200" / "libterra_b200.so"
 REFERENCE_LIB = REPO / "oracle" / "_ref" / "libterra_ref.so"
+REFERENCE_ENVLIT_LIB = REPO / "oracle" / "_ref" / "libterra_ref_envlit.so"   # reference with Terra.c:1056 restored ("patched oracle")
 ORACLE_LIB = REPO / "oracle" / "libterra_oracle.so"
 
 MAX_ATTR = 8
@@ -431,6 +432,7 @@ class OracleLib:
 
         sig("oracle_scene_create", _vp, _vp, C.c_int, C.POINTER(SceneOptions))
         sig("oracle_scene_destroy", None, _vp)
+        sig("oracle_set_env_lit", None, _vp, C.c_int)
         sig("oracle_bvh_nodes", _vp, _vp, C.POINTER(C.c_int))
         sig("oracle_trace_rays", None, _vp, _sz, _vp, _vp, _vp)
         sig("oracle_trace_counted", None, _vp, _vp, _sz, _vp, _vp, _vp, _vp)
@@ -457,6 +459,9 @@ class OracleScene:
         if self.h:
             self.o.oracle_scene_destroy(self.h)
             self.h = None
+
+    def set_env_lit(self, on: bool = True):
+        self.o.oracle_set_env_lit(self.h, 1 if on else 0)
 
     def bvh_nodes(self) -> np.ndarray:
         n = C.c_int(0)

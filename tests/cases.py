@@ -30,6 +30,33 @@ RENDER_CASES = {      # name -> cornell kwargs (jitter 0 => deterministic camera
     "debug_mis_phong": dict(integrator=6, spp=4, bounces=2, jitter=0.0, materials="phong"),
 }
 RENDER_SIZE = (32, 32)
+# env-lit extension mode: open scenes where paths escape to the environment
+ENVLIT_CASES = {
+    "envlit_const": dict(integrator=0, spp=4, bounces=4, jitter=0.0, env="const"),
+    "envlit_latlong": dict(integrator=0, spp=4, bounces=4, jitter=0.0, env="latlong"),
+    "envlit_latlong_direct": dict(integrator=1, spp=4, bounces=3, jitter=0.0, env="latlong"),
+}
+
+
+def envlit_scene(scenes, api, lib, *, integrator, spp, bounces, jitter, env, commit=True):
+    """Small sphere field (open to the sky) with a constant or a lat-long HDR environment map."""
+    import ctypes as C
+    import numpy as np
+    orig = api.Scene.commit
+    api.Scene.commit = lambda self: None
+    try:
+        s, cam = scenes.sphere_field(lib, **dict(SMALL_FIELD, integrator=integrator, spp=spp, bounces=bounces, jitter=jitter))
+    finally:
+        api.Scene.commit = orig
+    o = s.options()
+    if env == "const":
+        s.const_attr(o.environment_map, (0.4, 0.52, 1.0))
+    else:
+        tex = s.make_texture(scenes.procedural_sky(64, 32, seed=5))
+        lib.terra_attribute_init_cubemap(C.byref(o.environment_map), C.byref(tex))
+    if commit:
+        s.commit()
+    return s, cam
 
 
 def build(scenes, lib, name, **over):

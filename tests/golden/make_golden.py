@@ -93,6 +93,23 @@ def main():
         s.destroy()
     np.savez_compressed(OUT / "renders.npz", **out)
 
+    # 3b. env-lit extension mode: the reference with Terra.c:1056 restored (oracle/Makefile, "patched oracle")
+    if api.REFERENCE_ENVLIT_LIB.exists():
+        pref = api.TerraLib(api.REFERENCE_ENVLIT_LIB)
+        out = {}
+        for name, kw in cases.ENVLIT_CASES.items():
+            s, cam = cases.envlit_scene(scenes, api, pref, **kw)
+            _, rays, paths, res, pix = s.ref_render_farm(cam, w, h, kw["spp"], tile=max(w, h), nproc=1, seed=cases.RENDER_SEED)
+            out[f"{name}_acc"] = res["acc"]
+            out[f"{name}_samples"] = res["samples"]
+            s.destroy()
+            # and what the UNPATCHED reference makes of the same scene (parity mode: the environment adds nothing)
+            s, cam = cases.envlit_scene(scenes, api, ref, **kw)
+            _, _, _, res0, _ = s.ref_render_farm(cam, w, h, kw["spp"], tile=max(w, h), nproc=1, seed=cases.RENDER_SEED)
+            out[f"{name}_acc_parity_mode"] = res0["acc"]
+            s.destroy()
+        np.savez_compressed(OUT / "envlit.npz", **out)
+
     # 4. BSDF known answers from the reference's live presets (TerraPresets.c:34-146)
     e, wo, nrm = cases.bsdf_kat_inputs()
     out = {}

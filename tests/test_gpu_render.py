@@ -197,6 +197,57 @@ def test_debug_mis_weights_vs_cpu_renderer(api, scenes, gpu, oracle, materials):
     assert max(rmse(G, A), rmse(G, B)) <= RMSE_FACTOR * rmse(A, B), (rmse(G, A), rmse(G, B), rmse(A, B))
 
 
+# ----------------------------------------------------------------------------- env-lit extension mode
+@pytest.mark.parametrize("name", ["envlit_const", "envlit_latlong", "envlit_latlong_direct"])
+def test_envlit_mode_matches_patched_cpu_renderer(api, scenes, gpu, oracle, name):
+    """terra_b200_set_env_lit: a miss adds throughput * environment.
+    CPU side = the reference compiled with Terra.c:1056 restored (oracle/_ref/libterra_ref_envlit.so) when
+    present, else the oracle in env-lit mode (pinned bit-exact against it by
+    tests/test_oracle_render_pin.py). At jitter 0 the PRIMARY misses are deterministic: on pixels whose
+    camera ray leaves the scene the radiance is exactly the environment value, bit for bit. The rest is
+    statistical: per-channel mean within 0.5 % + CPU spread, RMSE within 1.25 x the CPU run-to-run RMSE."""
+    w, h, spp = 48, 28, 512
+    kw = dict(cases.ENVLIT_CASES[name], spp=spp)
+    patched = api.TerraLib(api.REFERENCE_ENVLIT_LIB) if api.REFERENCE_ENVLIT_LIB.exists() else None
+    nproc = min(8, os.cpu_count() or 1)
+
+    def cpu(seed):
+        if patched is not None:
+            s, cam = cases.envlit_scene(scenes, api, patched, **kw)
+            _, _, _, res, _ = s.ref_render_farm(cam, w, h, spp, tile=8, nproc=nproc, seed=seed)
+            s.destroy()
+            return radiance(res)
+        s, cam = cases.envlit_scene(scenes, api, api.TerraLib(), commit=False, **kw)
+        osc = api.OracleScene(oracle, s)
+        osc.set_env_lit(True)
+        api.srand(seed)
+        res, _ = osc.render(cam, w, h, pcg_seed=seed)
+        osc.destroy(); s.destroy()
+        return radiance(res)
+
+    A, B = cpu(5), cpu(6)
+    s, cam = cases.envlit_scene(scenes, api, gpu, **kw)
+    gpu.terra_b200_set_seed(s.h, 3)
+    off = radiance(s.render(cam, w, h)[0])
+    gpu.terra_b200_set_env_lit(s.h, 1)
+    gpu.terra_b200_set_seed(s.h, 3)
+    G = radiance(s.render(cam, w, h)[0])
+    G4 = radiance(s.render(cam, w, h, passes=3)[0])
+    hits = s.primary_hits(cam, w, h)
+    s.destroy()
+    assert np.isfinite(G).all() and G.mean() > off.mean() * 1.05          # the environment lights the scene
+    sky = hits["t"] < 0                                                      # camera ray leaves the scene
+    assert sky.mean() > 0.05
+    assert np.array_equal(G[sky].view(np.uint32), A[sky].view(np.uint32))   # exactly the environment lookup
+    rmse = lambda x, y: float(np.sqrt(((x - y) ** 2).mean()))
+    assert max(rmse(G, A), rmse(G, B)) <= RMSE_FACTOR * rmse(A, B), (rmse(G, A), rmse(G, B), rmse(A, B))
+    cpu_mean = ((A + B) / 2).mean(axis=(0, 1))
+    sem = np.abs(A.mean(axis=(0, 1)) - B.mean(axis=(0, 1))) / 2 / cpu_mean
+    rel = np.abs(G4.mean(axis=(0, 1)) - cpu_mean) / cpu_mean
+    print(f"{name}: mean rel err {rel}, cpu sem {sem}")
+    assert (rel <= MEAN_TOL + 2 * sem).all(), (rel, sem)
+
+
 # ----------------------------------------------------------------------------- accumulate + tonemap
 @pytest.mark.parametrize("op", range(5))
 def test_tonemap_vs_oracle(api, scenes, gpu, oracle, op):

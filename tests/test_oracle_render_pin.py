@@ -108,3 +108,50 @@ def test_oracle_presets_inside_reference_render(api, scenes, ref, oracle):
     _, _, _, r2, _ = s2.ref_render_farm(cam, 24, 24, 2, tile=32, nproc=1, seed=5)
     assert np.array_equal(bits(r1["acc"]), bits(r2["acc"]))
     s1.destroy(); s2.destroy()
+
+
+# ----------------------------------------------------------------------------- env-lit extension mode
+def oracle_envlit_render(api, scenes, prod, oracle, kw, env_lit, seed=cases.RENDER_SEED):
+    w, h = cases.RENDER_SIZE
+    s, cam = cases.envlit_scene(scenes, api, prod, commit=False, **kw)
+    osc = api.OracleScene(oracle, s)
+    osc.set_env_lit(env_lit)
+    api.srand(seed + 1)
+    res, _ = osc.render(cam, w, h)
+    osc.destroy(); s.destroy()
+    return res
+
+
+@pytest.mark.parametrize("name", list(cases.ENVLIT_CASES))
+def test_envlit_oracle_bit_exact_vs_patched_reference_fixture(api, scenes, prod, oracle, oracle_presets, name):
+    """the oracle's env-lit mode (miss adds throughput * environment) against the
+    reference compiled with exactly Terra.c:1056 restored (tests/golden/envlit.npz, made by
+    oracle/_ref/libterra_ref_envlit.so): constant and lat-long HDR environment (Terra.c:468-477),
+    bit for bit; and with the mode off the oracle still equals the UNPATCHED reference."""
+    g = golden("envlit.npz")
+    res = oracle_envlit_render(api, scenes, prod, oracle, cases.ENVLIT_CASES[name], True)
+    assert np.array_equal(bits(res["acc"]), bits(g[f"{name}_acc"]))
+    assert res["acc"].sum() > g[f"{name}_acc_parity_mode"].sum()          # the environment does light the scene
+    res0 = oracle_envlit_render(api, scenes, prod, oracle, cases.ENVLIT_CASES[name], False)
+    assert np.array_equal(bits(res0["acc"]), bits(g[f"{name}_acc_parity_mode"]))
+
+
+def test_envlit_oracle_vs_patched_reference_live(api, scenes, oracle, oracle_presets):
+    if not api.REFERENCE_ENVLIT_LIB.exists():
+        pytest.skip("oracle/_ref/libterra_ref_envlit.so not built here; the fixture test covers the pin")
+    pref = api.TerraLib(api.REFERENCE_ENVLIT_LIB)
+    kw = dict(integrator=2, spp=3, bounces=5, jitter=0.0, env="latlong")
+    s, cam = cases.envlit_scene(scenes, api, pref, **kw)
+    _, _, _, rres, _ = s.ref_render_farm(cam, 24, 24, 3, tile=32, nproc=1, seed=77)
+    old = dict(api.Scene.default_preset_overrides)
+    api.Scene.default_preset_overrides = {}
+    try:
+        s2, _ = cases.envlit_scene(scenes, api, pref, **kw)          # reference presets, oracle integrator
+    finally:
+        api.Scene.default_preset_overrides = old
+    osc = api.OracleScene(oracle, s2)
+    osc.set_env_lit(True)
+    api.srand(78)
+    res, _ = osc.render(cam, 24, 24)
+    assert np.array_equal(bits(res["acc"]), bits(rres["acc"]))
+    osc.destroy(); s2.destroy(); s.destroy()
