@@ -135,6 +135,7 @@ struct TbDevice {
     int          v4_opt;            // k_trace_v4 OPT bits (tb_trace_v4.cuh)
     int          coherent_kind;     // TB_K_* used for camera-ray launches when trace_kind is auto
     int          incoherent_kind;   // TB_K_* used for incoherent launches when trace_kind is auto
+    int          warp_samples; // at most this many samples of one pixel share a warp (TERRA_B200_WARP_SAMPLES, default 32)
     int          tile_pixels;  // 1: waves walk the region in 8x4 pixel tiles (TERRA_B200_TILE=0 turns it off)
     int          tri_min, refetch_below;
 };
@@ -213,6 +214,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
         d->trace_kind = 0;
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
+        const char* ws = getenv("TERRA_B200_WARP_SAMPLES"); d->warp_samples = ws ? atoi(ws) : 32;
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
         for (int k = 0; e && k < 10; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
         const char* vo = getenv("TERRA_B200_V4_OPT"); d->v4_opt = vo ? (atoi(vo) & 3) : 3;       // measured on B200: 256-bit loads +1.7 %, single pop +10 % (C3 1M)
@@ -447,6 +449,7 @@ struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot
     uint32_t sample_base;
     uint64_t seed;
     int      tiled;            // 1: region-linear index q walks 8x4 pixel tiles (w % 8 == 0 && h % 4 == 0)
+    int      sub;              // tiled: samples of one pixel that share a warp (power of two dividing n_samples, <= 32)
 };
 
 struct TbRaygenArgs {
@@ -471,20 +474,28 @@ __device__ __forceinline__ void tb_region_pixel(const TbBatch& b, int pr, int* r
     }
 }
 
-// Wave slot <-> (pixel of the batch, sample of the batch). Linear: sample-major. Tiled: the samples of one
-// 8x4 tile are adjacent — slot = (tile * n_samples + s) * 32 + lane — so consecutive warps of the trace
-// kernels walk the SAME part of the tree (node fetches hit L1) and the bounce rays of a tile stay together.
+// Wave slot <-> (pixel of the batch, sample of the batch). Linear: sample-major. Tiled: a warp's 32 slots are
+// `sub` samples of each of 32/sub neighbouring pixels (sub = gcd(n_samples, 32) unless capped), and
+// consecutive warps are the next samples of the same pixels, then the next pixels of the 8x4 tile order:
+//   slot = ((p / P) * (n_samples / sub) + s / sub) * 32 + (p % P) * sub + s % sub,   P = 32 / sub.
+// sub = 32: a warp is 32 samples of ONE pixel — its camera rays differ by the sub-pixel jitter only, so the
+// packet kernel walks barely more nodes than a single ray would, and the bounce rays of a pixel sit together.
 __device__ __forceinline__ int tb_slot_of(const TbBatch& b, int p_local, int s_local) {
-    if (b.tiled) return ((p_local >> 5) * b.n_samples + s_local) * 32 + (p_local & 31);
+    if (b.tiled) {
+        const int sub = b.sub, P = 32 / sub;
+        return ((p_local / P) * (b.n_samples / sub) + s_local / sub) * 32 + (p_local % P) * sub + s_local % sub;
+    }
     return s_local * b.n_pixels + p_local;
 }
 
 __device__ __forceinline__ void tb_slot_to_pixel(const TbBatch& b, int slot, int* px, int* py, uint32_t* sample) {
     int s_local, p_local;
     if (b.tiled) {
-        const int group = slot / (32 * b.n_samples), within = slot - group * (32 * b.n_samples);
-        s_local = within >> 5;
-        p_local = group * 32 + (within & 31);
+        const int sub = b.sub, P = 32 / sub, sg = b.n_samples / sub;
+        const int group = slot >> 5, in = slot & 31;
+        const int pgroup = group / sg, sgroup = group - pgroup * sg;
+        p_local = pgroup * P + in / sub;
+        s_local = sgroup * sub + in % sub;
     } else {
         s_local = slot / b.n_pixels;
         p_local = slot - s_local * b.n_pixels;
@@ -1189,6 +1200,8 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
             b.p0 = (int)p0; b.n_pixels = (int)np; b.s0 = (int)s0; b.n_samples = (int)ns;
             b.sample_base = (uint32_t)sample_base; b.seed = seed;
             b.tiled = (d->tile_pixels && w % 8 == 0 && h % 4 == 0 && np % 32 == 0 && p0 % 32 == 0) ? 1 : 0;
+            b.sub = 1;
+            while (b.sub < 32 && b.sub < d->warp_samples && ns % (size_t)(b.sub * 2) == 0) b.sub *= 2;
             const int n_paths = (int)(np * ns);
             TbRaygenArgs rg;
             rg.batch = b; rg.cam = *cam; rg.jitter = sc.jitter;
