@@ -9,6 +9,10 @@
 #include "tb_math.h"
 
 TB_HD size_t tb_mini(size_t a, size_t b) { return a < b ? a : b; }
+// x % m and x / m for m <= 65535 (TerraTexture dims are uint16_t): 32-bit arithmetic whenever x fits — the
+// 64-bit forms are ~100-instruction subroutines on the GPU and took 12 % of k_shade (ncu n5). Same values.
+TB_HD size_t tb_modz(size_t x, uint32_t m) { return x <= 0xffffffffull ? (size_t)((uint32_t)x % m) : x % m; }
+TB_HD size_t tb_divz(size_t x, uint32_t m) { return x <= 0xffffffffull ? (size_t)((uint32_t)x / m) : x / m; }
 
 TB_HD V3 tb_texture_read(const TbDevTexture& t, size_t x, size_t y) {
     switch (t.address_mode) {
@@ -17,17 +21,17 @@ TB_HD V3 tb_texture_read(const TbDevTexture& t, size_t x, size_t y) {
             y = tb_mini(y, (size_t)t.height - 1);
             break;
         case kTerraTextureAddressMirror:
-            if ((x / t.width) % 2 == 0) {
-                x = x % t.width;
-                y = y % t.height;
+            if (tb_divz(x, t.width) % 2 == 0) {
+                x = tb_modz(x, t.width);
+                y = tb_modz(y, t.height);
             } else {
-                x = tb_mini(t.width - (x % t.width), (size_t)t.width - 1);
-                y = tb_mini(t.height - (y % t.height), (size_t)t.height - 1);
+                x = tb_mini(t.width - tb_modz(x, t.width), (size_t)t.width - 1);
+                y = tb_mini(t.height - tb_modz(y, t.height), (size_t)t.height - 1);
             }
             break;
         default:   // kTerraTextureAddressWrap
-            x = x % t.width;
-            y = y % t.height;
+            x = tb_modz(x, t.width);
+            y = tb_modz(y, t.height);
             break;
     }
     size_t at = (y * t.width + x) * t.components;
