@@ -105,6 +105,8 @@ struct TbDevice {
     // owned device memory
     float4 *d_nodes, *d_tris, *d_props;
     uint4*  d_qnodes;
+    uint4*  d_qnodes4;       // 4-wide quantised nodes (tb_trace_v5.cuh)
+    int     stack_bound4;
     float   grid_lo[3], grid_cell[3];
     TbDevMaterial* d_mats;
     TbDevTexture*  d_texs;
@@ -196,7 +198,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     memset(&d->sc, 0, sizeof d->sc);
     d->d_nodes = d->d_tris = d->d_props = NULL;
-    d->d_qnodes = NULL;
+    d->d_qnodes = NULL; d->d_qnodes4 = NULL; d->stack_bound4 = 0;
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
     d->stack_bound = 0;
     memset(&d->wave, 0, sizeof d->wave);
@@ -210,17 +212,17 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->exact_boxes = 0;
     {
         const char* e = getenv("TERRA_B200_TRACE");
-        static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128", "v4", "v4q", "packet" };
+        static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128", "v4", "v4q", "packet", "v5" };
         d->trace_kind = 0;
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
         const char* ws = getenv("TERRA_B200_WARP_SAMPLES"); d->warp_samples = ws ? atoi(ws) : 32;
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
-        for (int k = 0; e && k < 10; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
+        for (int k = 0; e && k < 11; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
         const char* vo = getenv("TERRA_B200_V4_OPT"); d->v4_opt = vo ? (atoi(vo) & 3) : 3;       // measured on B200: 256-bit loads +1.7 %, single pop +10 % (C3 1M)
         const char* ik = getenv("TERRA_B200_INCOHERENT");      // kernel for bounce / visibility / API rays (A/B runs)
         d->incoherent_kind = 8;                                 // TB_K_V4Q
-        for (int k = 1; ik && k < 9; ++k) if (strcmp(ik, names[k]) == 0) d->incoherent_kind = k;
+        for (int k = 1; ik && k < 11; ++k) if (strcmp(ik, names[k]) == 0) d->incoherent_kind = k;
         const char* ck = getenv("TERRA_B200_COHERENT");         // kernel for camera rays (A/B runs)
         d->coherent_kind = 9;                                   // TB_K_PACKET
         for (int k = 1; ck && k < 10; ++k) if (strcmp(ck, names[k]) == 0) d->coherent_kind = k;
@@ -233,6 +235,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
 static void tb_scene_free(TbDevice* d) {
     tb_free(d->d_nodes); tb_free(d->d_tris); tb_free(d->d_props); tb_free(d->d_mats); tb_free(d->d_texs);
     tb_free(d->d_qnodes); d->d_qnodes = NULL;
+    tb_free(d->d_qnodes4); d->d_qnodes4 = NULL;
     tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
     for (void* p : d->tex_pixels) tb_free(p);
     d->tex_pixels.clear();
@@ -274,6 +277,10 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
     d->d_tris = (float4*)tb_upload(f->tris, f->n_tris * 12, d);
     if (f->qnodes) {
         d->d_qnodes = (uint4*)tb_upload(f->qnodes, f->n_nodes * 8, d);
+        if (f->qnodes4 && f->stack_bound4 <= TB_STACK_SMEM + TB_STACK_LOCAL) {
+            d->d_qnodes4 = (uint4*)tb_upload(f->qnodes4, f->n_nodes4 * 16, d);
+            d->stack_bound4 = f->stack_bound4;
+        }
         memcpy(d->grid_lo, f->grid_lo, sizeof d->grid_lo);
         memcpy(d->grid_cell, f->grid_cell, sizeof d->grid_cell);
     }
@@ -430,6 +437,7 @@ struct TbTraceArgs {
     int           emit_prim;    // 1: write object|tri<<8 (API), 0: write rank (wavefront)
     unsigned long long* visit_counters;   // COUNT variant only: [0] nodes fetched, [1] triangles tested
     const uint4*  qnodes;       // quantised 32-byte nodes (tb_trace.cuh), or NULL
+    const uint4*  qnodes4;      // quantised 64-byte 4-wide nodes (tb_trace_v5.cuh), or NULL
     float         grid_lo[3], grid_cell[3];
     int           tri_min, refetch_below;   // rounds kernel tunables (tb_trace_v3.cuh)
 };
@@ -438,6 +446,7 @@ struct TbTraceArgs {
 #include "tb_trace.cuh"
 #include "tb_trace_v3.cuh"
 #include "tb_trace_v4.cuh"
+#include "tb_trace_v5.cuh"
 #include "tb_trace_packet.cuh"
 
 // ==================================================================================== K1: ray generation
@@ -1086,7 +1095,7 @@ static void tb_drain_events(TbDevice* d) {
 // bounce / visibility / API rays are incoherent and bound by L1 wavefronts AND by issue slots at 7 of 32
 // lanes, where the rounds kernel over 32-byte quantised nodes is fastest (3.9 vs 2.8 Grays/s on C3).
 // TERRA_B200_TRACE=v1|v2|v3|v3q|quant|ld128 forces one kernel for every launch (A/B runs).
-enum { TB_K_AUTO = 0, TB_K_V1, TB_K_V2, TB_K_V3, TB_K_V3Q, TB_K_QUANT, TB_K_LD128, TB_K_V4, TB_K_V4Q, TB_K_PACKET };
+enum { TB_K_AUTO = 0, TB_K_V1, TB_K_V2, TB_K_V3, TB_K_V3Q, TB_K_QUANT, TB_K_LD128, TB_K_V4, TB_K_V4Q, TB_K_PACKET, TB_K_V5 };
 
 template <bool COUNT>
 static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind) {
@@ -1098,6 +1107,15 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         memcpy(c.grid_cell, d->grid_cell, sizeof c.grid_cell);
     }
     if (kind == TB_K_V1) { k_trace_v1<COUNT><<<grid, TB_TRACE_THREADS, 0, st>>>(c); return; }
+    if (kind == TB_K_V5) {            // 4-wide tree; the work counters and the reference tree stay on the binary kernels
+        if (!COUNT && d->d_qnodes4 && !d->exact_boxes) {
+            c.qnodes4 = d->d_qnodes4;
+            if (d->stack_bound4 > TB_V5_DEPTH) k_trace_v5<true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+            else                               k_trace_v5<false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+            return;
+        }
+        kind = TB_K_V4Q;
+    }
     if (kind == TB_K_PACKET && !COUNT) {
         static const int occ = getenv("TERRA_B200_PACKET_OCC") ? atoi(getenv("TERRA_B200_PACKET_OCC")) : 8;
         if (d->exact_boxes)  k_trace_packet<true, 8><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
