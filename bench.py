@@ -74,6 +74,9 @@ class ClockSampler:
                                           "-lms", "200", "-i", str(self.gpu_index)], stdout=subprocess.PIPE, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
+            t0 = time.time()                      # nvidia-smi takes ~0.2 s to print its first line: a short timed
+            while not self.rows and time.time() - t0 < 2.0:     # region must not end before the sampler is running
+                time.sleep(0.02)
         except OSError:
             self.proc = None
 

@@ -16,7 +16,7 @@ from pathlib import Path
 import numpy as np
 
 REPO = Path(__file__).resolve().parent.parent
-PRODUCT_LIB = REPO / "terra_b200" / "libterra_b200.so"
+PRODUCT_LIB = Path(os.environ.get("TERRA_B200_LIB", REPO / "terra_b200" / "libterra_b200.so"))   # override: A/B builds only
 REFERENCE_LIB = REPO / "oracle" / "_ref" / "libterra_ref.so"
 REFERENCE_ENVLIT_LIB = REPO / "oracle" / "_ref" / "libterra_ref_envlit.so"   # reference with Terra.c:1056 restored ("patched oracle")
 ORACLE_LIB = REPO / "oracle" / "libterra_oracle.so"

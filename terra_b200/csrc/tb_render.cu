@@ -46,6 +46,9 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_REFETCH_ROUNDS     26           // rounds kernel: refill the warp when fewer lanes own a ray (swept on B200: 16/20/26/30)
 #define TB_REFETCH_BELOW      20           // dynamic fetch: refill the warp when fewer lanes are busy
 #define TB_SHADE_THREADS      256
+#ifndef TB_SHADE_MIN_BLOCKS
+#define TB_SHADE_MIN_BLOCKS    1            // resident CTAs per SM the shade kernels are compiled for (register cap)
+#endif
 #define TB_QUEUE_SENTINEL     0x7fffffff
 
 // ------------------------------------------------------------------------------------ RNG
@@ -744,7 +747,7 @@ __device__ __forceinline__ V3 tb_integrate_debug(const TbDevScene& sc, int integ
 }
 
 template <int PRESET, int STAGE>
-__global__ void __launch_bounds__(TB_SHADE_THREADS) k_shade(TbShadeArgs a) {
+__global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade(TbShadeArgs a) {
     const int count = *a.q_count;
     const int stride = gridDim.x * blockDim.x;
     const int rounds = (count + stride - 1) / stride;
