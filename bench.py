@@ -131,6 +131,9 @@ def cpu_reference_rate(workload, budget_s, seed=1, steps=1, warmup=0):
         n_probe = len(range(0, all_tiles, 17))
         secs, _, _, _, _ = s.ref_render_farm(cam, w, h, spp_cpu, tile=tile, nproc=min(cores, n_probe), seed=seed, tile_stride=17)
         per_tile = max(secs, 1e-3) * min(cores, n_probe) / n_probe
+        # the 1-core figure: the same probe tiles rendered by ONE process
+        one_secs, _, one_paths, _, _ = s.ref_render_farm(cam, w, h, spp_cpu, tile=tile, nproc=1, seed=seed, tile_stride=17 * 2)
+        one_core = one_paths / max(one_secs, 1e-6) / 1e6
         want_tiles = budget_s * cores / per_tile
         if want_tiles >= all_tiles:
             stride = 1
@@ -151,7 +154,8 @@ def cpu_reference_rate(workload, budget_s, seed=1, steps=1, warmup=0):
                 "sample": f"every {stride}th 128x128 tile of the {w}x{h} frame ({len(range(0, tx * ty, stride))} tiles) at {spp_cpu} spp, "
                           f"{cores}-process tile farm over libterra_ref.so; {paths_total} paths, {rays_total} rays, {secs_total:.2f} s; "
                           f"reference BVH build {build_s:.2f} s excluded",
-                "mrays_per_s": rays_total / secs_total / 1e6 if secs_total else None}
+                "mrays_per_s": rays_total / secs_total / 1e6 if secs_total else None,
+                "one_core_value": one_core}
         return rates, info
     # port: oracle renderer on one core, a centred crop
     prod, ora = api.TerraLib(), api.OracleLib()
@@ -222,6 +226,16 @@ def commit_ms(lib, s):
     out = (C.c_float * 4)()
     lib.terra_b200_commit_ms(s.h, out)
     return {"bvh_build": out[0], "flatten": out[1], "quantise": out[2], "upload": out[3]}
+
+
+def profile_issue(kernel):
+    """Issue-slot roofline of SURVEY §8(d) (warp instructions issued / (#SM x 4 schedulers x SM clock)) for the
+    named kernel, from the committed ncu --set full capture (smsp__issue_active.avg.pct_of_peak_sustained_active
+    and active lanes per instruction). Measured under ncu, so it explains the line; it is not a bench value."""
+    p = REPO / "profiles" / "traffic.json"
+    if p.exists():
+        return json.loads(p.read_text()).get("issue", {}).get(kernel)
+    return None
 
 
 def profile_traffic(kernel, rays_per_launch):
@@ -356,6 +370,7 @@ def run_render_arm(args):
                      "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
                      "rays_per_launch": rays_per_launch, "ms_per_launch": trace_ms_per_launch,
                      "l2": l2_roofline(lib, achieved),
+                     "issue": {"k_trace_packet": profile_issue("k_trace_packet"), "k_trace_v4": profile_issue("k_trace_v4_c2")},
                      "note": "working set (nodes+tris ~11 MB) is L2-resident: the HBM figure is the contract's denominator, "
                              "the L2 fraction is in profiles/"},
         "extra": {"mrays_per_s": rays_all / args.steps / (ms_dev * 1e-3) / 1e6,
@@ -463,7 +478,7 @@ def run_traversal_arm(args):
         "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": profile_traffic("k_trace_" + args.workload, n_rays), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
                      "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "counter": src, "ms_per_launch": k_ms,
-                     "l2": l2_roofline(lib, achieved)},
+                     "l2": l2_roofline(lib, achieved), "issue": {"k_trace_v4": profile_issue("k_trace_v4_c3")}},
         "extra": {"scene_commit_s": commit_s, "commit_ms": commit_ms(lib, s), "hit_t_agreement_with_oracle": agree},
     }
     print(json.dumps(line), flush=True)

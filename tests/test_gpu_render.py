@@ -298,6 +298,46 @@ def test_progressive_accumulation_and_regions(api, scenes, gpu):
     s.destroy()
 
 
+def test_concurrent_tile_calls_from_many_threads(api, scenes, gpu):
+    """The reference's only caller renders one frame as many terra_render calls on disjoint 128x128 tiles
+    from a thread pool sharing one committed scene and one framebuffer (satellite/src/Renderer.cpp:70-98,
+    316-349; SURVEY §8b threading). Same contract here: calls from 6 threads, every pixel ends up with
+    exactly spp samples, nothing outside a call's tile is touched by it, and the image agrees with a
+    single full-frame call (different random numbers per call, so statistically)."""
+    import threading
+    w, h, spp, tile = 96, 64, 64, 32
+    s, cam = scenes.cornell(gpu, spp=spp)
+    gpu.terra_b200_set_seed(s.h, 17)
+    full, _ = s.render(cam, w, h)
+    fb = api.Framebuffer()
+    assert gpu.terra_framebuffer_create(C.byref(fb), w, h)
+    tiles = [(x, y) for y in range(0, h, tile) for x in range(0, w, tile)]
+    errors = []
+
+    def worker(k):
+        try:
+            for (x, y) in tiles[k::6]:
+                gpu.terra_render(C.byref(cam), s.h, C.byref(fb), x, y, tile, tile)
+        except Exception as e:       # pragma: no cover
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(6)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors
+    res = np.ctypeslib.as_array(C.cast(fb.results, C.POINTER(C.c_float)), (h, w, 4)).copy()
+    samples = res[..., 3].view(np.int32)
+    assert (samples == spp).all()
+    rad = res[..., :3] / spp
+    assert np.isfinite(rad).all()
+    ref = full["acc"] / spp
+    assert np.allclose(rad.mean(axis=(0, 1)), ref.mean(axis=(0, 1)), rtol=0.05)
+    gpu.terra_framebuffer_destroy(C.byref(fb))
+    s.destroy()
+
+
 def test_stratified_rounds_spp_like_the_reference(api, scenes, gpu):
     """sampling_method only changes spp: cur = strata^2; while (spp > cur) cur *= cur (Terra.c:519-527)."""
     s, cam = scenes.cornell(gpu, spp=5)
