@@ -149,12 +149,30 @@ extern "C" void terra_attribute_init_cubemap(TerraAttribute* attr, TerraTexture*
 }
 
 // =============================================================================== framebuffer
+// Framebuffer memory is page-locked when a CUDA device is present (the copies inside terra_render then run at
+// PCIe speed); the struct stays the reference's, and a caller-provided (pageable) buffer works just the same.
+static std::mutex g_pinned_lock;
+static std::vector<void*> g_pinned;
+static void* fb_alloc(size_t bytes) {
+    void* p = tb_host_alloc_pinned(bytes);
+    if (p) { std::lock_guard<std::mutex> g(g_pinned_lock); g_pinned.push_back(p); return p; }
+    return terra_malloc(bytes);
+}
+static void fb_free(void* p) {
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> g(g_pinned_lock);
+        auto it = std::find(g_pinned.begin(), g_pinned.end(), p);
+        if (it != g_pinned.end()) { g_pinned.erase(it); tb_host_free_pinned(p); return; }
+    }
+    terra_free(p);
+}
 extern "C" bool terra_framebuffer_create(TerraFramebuffer* fb, size_t width, size_t height) {     // :309-326
     if (width == 0 || height == 0) return false;
     fb->width = width;
     fb->height = height;
-    fb->pixels = (TerraFloat3*)terra_malloc(sizeof(TerraFloat3) * width * height);
-    fb->results = (TerraRawIntegrationResult*)terra_malloc(sizeof(TerraRawIntegrationResult) * width * height);
+    fb->pixels = (TerraFloat3*)fb_alloc(sizeof(TerraFloat3) * width * height);
+    fb->results = (TerraRawIntegrationResult*)fb_alloc(sizeof(TerraRawIntegrationResult) * width * height);
     terra_framebuffer_clear(fb);
     return true;
 }
@@ -165,8 +183,8 @@ extern "C" void terra_framebuffer_clear(TerraFramebuffer* fb) {                 
 }
 extern "C" void terra_framebuffer_destroy(TerraFramebuffer* fb) {                                  // :338-345
     if (fb == NULL) return;
-    terra_free(fb->results);
-    terra_free(fb->pixels);
+    fb_free(fb->results);
+    fb_free(fb->pixels);
 }
 
 // =============================================================================== textures

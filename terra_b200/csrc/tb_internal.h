@@ -134,6 +134,8 @@ void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 void      tb_device_set_env_lit(TbDevice* dev, int on);
 int       tb_cuda_device_count(void);
+void*     tb_host_alloc_pinned(size_t bytes);
+void      tb_host_free_pinned(void* p);
 double    tb_device_probe_bandwidth(int device_index, size_t bytes, int mode);
 #ifdef __cplusplus
 }

@@ -152,6 +152,18 @@ template <typename T> static T* tb_alloc(size_t n) {
     return (T*)p;
 }
 
+// Page-locked host memory for framebuffers the library allocates itself (terra_framebuffer_create): the
+// H2D of results[] and the D2H of results[] + pixels[] inside terra_render then run at PCIe speed instead
+// of being staged through the driver's bounce buffers. NULL when there is no device or no memory to pin.
+extern "C" void* tb_host_alloc_pinned(size_t bytes) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { cudaGetLastError(); return NULL; }
+    void* p = NULL;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return NULL; }
+    return p;
+}
+extern "C" void tb_host_free_pinned(void* p) { cudaFreeHost(p); }
+
 extern "C" int tb_cuda_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
