@@ -15,10 +15,46 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "tb_bvh.h"
 #include "tb_math.h"
+
+// ------------------------------------------------------------------------------------ host threads
+// The commit stages below (sah3 build, flatten, quantise) are loops over millions of independent
+// primitives / nodes: they are split over the host cores in contiguous chunks. Results never depend on the
+// thread count (exact min/max merges, disjoint writes).
+namespace {
+
+int g_par_min = 1 << 16;        // ranges below this are handled by one thread (TERRA_B200_BUILD_PAR_MIN: tests lower it)
+
+template <typename F> void parallel_chunks(int begin, int end, int threads, F fn) {     // fn(lo, hi, tid)
+    const int n = end - begin;
+    if (threads <= 1 || n < g_par_min) { fn(begin, end, 0); return; }
+    std::vector<std::thread> pool;
+    const int per = (n + threads - 1) / threads;
+    for (int t = 0; t < threads; ++t) {
+        const int lo = begin + t * per, hi = std::min(end, lo + per);
+        if (lo >= hi) break;
+        pool.emplace_back([=]() { fn(lo, hi, t); });
+    }
+    for (std::thread& th : pool) th.join();
+}
+
+int host_threads() {
+    int threads = (int)std::thread::hardware_concurrency();
+    if (const char* e = getenv("TERRA_B200_BUILD_THREADS")) threads = atoi(e);
+    if (threads < 1) threads = 1;
+    if (threads > 64) threads = 64;
+    g_par_min = 1 << 16;
+    if (const char* e = getenv("TERRA_B200_BUILD_PAR_MIN")) g_par_min = std::max(2, atoi(e));
+    return threads;
+}
+
+}  // namespace
+
 
 namespace {
 
@@ -202,7 +238,8 @@ void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* obj
     }
     out->stack_bound = max_depth;
     // pass 2: write nodes and rank-ordered triangle/property records
-    for (size_t i = 0; i < nodes.size(); ++i) {
+    parallel_chunks(0, (int)nodes.size(), host_threads(), [&](int lo_, int hi_, int) {
+    for (size_t i = (size_t)lo_; i < (size_t)hi_; ++i) {
         const TbHostNode& n = nodes[i];
         float* q = &out->nodes[i * 16];
         memcpy(q, &n.aabb[0], 48);             // min0 max0 min1 max1, same order as the reference node
@@ -225,6 +262,7 @@ void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* obj
         }
         memcpy(q + 12, ref, 16);
     }
+    });
     out->object_base = object_base;
 }
 
@@ -255,111 +293,261 @@ inline float bin_area(const Bin* b) {
 inline float pad_lo(float v) { return v - (1e-4f + 2e-6f * fabsf(v)); }
 inline float pad_hi(float v) { return v + (1e-4f + 2e-6f * fabsf(v)); }
 
-struct SahTask { int begin, end, node, slot; };   // slot: which child of `node` this range fills (-1 root)
+}  // namespace
+
+// The build is parallel on the host: a subtree over n primitives has exactly n-1 nodes, so node ids can be
+// assigned in PREORDER before anything is built (left child = id+1, right child = id + n_left) and disjoint
+// ranges can be built by different threads without talking to each other. The top levels (ranges above
+// `grain`) run one node at a time with the binning / bounding passes split over the threads; the ranges
+// below run as independent serial tasks. A last serial pass renumbers the nodes into the allocation order
+// of the original serial builder (a node's two inner children are adjacent), so the node array — and with
+// it every committed measurement — is byte-identical to what the serial code produced.
+namespace {
+
+const int SAH_NB = 16;
+inline int bin_of(const BuildPrim& q, int k, float clo, float scale) {
+    int b = (int)((q.c[k] - clo) * scale);
+    if (b >= SAH_NB) b = SAH_NB - 1;
+    if (b < 0) b = 0;
+    return b;
+}
+
+// std::partition over a big range, on all threads, with the SAME resulting permutation as the serial
+// call: the two-pointer (Hoare) scheme swaps the k-th misplaced element counted from the left end with the
+// k-th misplaced element counted from the right end and touches nothing else, so once the split point is
+// known (a count) the misplaced elements of both sides can be listed per chunk and swapped pairwise.
+template <typename P> int hoare_partition_parallel(BuildPrim* prims, int begin, int end, int T, P left) {
+    std::vector<int> cnt((size_t)T, 0);
+    std::vector<int> lo_of((size_t)T, end), hi_of((size_t)T, end);
+    parallel_chunks(begin, end, T, [&](int lo, int hi, int tid) {
+        int c = 0;
+        for (int i = lo; i < hi; ++i) c += left(prims[i]) ? 1 : 0;
+        cnt[(size_t)tid] = c; lo_of[(size_t)tid] = lo; hi_of[(size_t)tid] = hi;
+    });
+    int n_left = 0;
+    for (int t = 0; t < T; ++t) n_left += cnt[(size_t)t];
+    const int mid = begin + n_left;
+    // misplaced on the left side (ascending) / on the right side (listed ascending per chunk, read descending)
+    std::vector<std::vector<int>> wrong_l((size_t)T), wrong_r((size_t)T);
+    parallel_chunks(begin, end, T, [&](int lo, int hi, int tid) {
+        std::vector<int>& wl = wrong_l[(size_t)tid];
+        std::vector<int>& wr = wrong_r[(size_t)tid];
+        for (int i = lo; i < hi; ++i) {
+            const bool l = left(prims[i]);
+            if (i < mid) { if (!l) wl.push_back(i); } else { if (l) wr.push_back(i); }
+        }
+    });
+    std::vector<int> all_l, all_r;
+    for (int t = 0; t < T; ++t) all_l.insert(all_l.end(), wrong_l[(size_t)t].begin(), wrong_l[(size_t)t].end());
+    for (int t = T - 1; t >= 0; --t) all_r.insert(all_r.end(), wrong_r[(size_t)t].rbegin(), wrong_r[(size_t)t].rend());
+    const int pairs = (int)all_l.size();                   // == all_r.size()
+    parallel_chunks(0, pairs, pairs >= g_par_min ? T : 1, [&](int lo, int hi, int) {
+        for (int i = lo; i < hi; ++i) std::swap(prims[all_l[(size_t)i]], prims[all_r[(size_t)i]]);
+    });
+    return mid;
+}
+
+// Split [begin,end) (n > 2): 16-bin SAH over the three axes; falls back to the median. Returns mid.
+int sah3_split(BuildPrim* prims, int begin, int end, int threads) {
+    const int n = end - begin;
+    const int T = (threads > 1 && n >= g_par_min) ? threads : 1;
+    float part_local[6];                                  // serial nodes (the vast majority) stay off the heap
+    std::vector<float> part_heap;
+    float* part = part_local;
+    if (T > 1) { part_heap.resize((size_t)T * 6); part = part_heap.data(); }
+    for (int t = 0; t < T; ++t) { part[t * 6] = FLT_MAX; part[t * 6 + 3] = -FLT_MAX; }
+    parallel_chunks(begin, end, T, [&](int lo, int hi, int tid) {
+        float* c = &part[(size_t)tid * 6];
+        for (int k = 0; k < 3; ++k) { c[k] = FLT_MAX; c[3 + k] = -FLT_MAX; }
+        for (int i = lo; i < hi; ++i)
+            for (int k = 0; k < 3; ++k) { if (prims[i].c[k] < c[k]) c[k] = prims[i].c[k]; if (prims[i].c[k] > c[3 + k]) c[3 + k] = prims[i].c[k]; }
+    });
+    float clo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, chi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    for (int t = 0; t < T; ++t) {
+        const float* c = &part[(size_t)t * 6];
+        if (c[0] == FLT_MAX && c[3] == -FLT_MAX) continue;           // chunk that got no work
+        for (int k = 0; k < 3; ++k) { if (c[k] < clo[k]) clo[k] = c[k]; if (c[3 + k] > chi[k]) chi[k] = c[3 + k]; }
+    }
+    float scale[3]; bool usable[3];
+    for (int k = 0; k < 3; ++k) { const float ext = chi[k] - clo[k]; usable[k] = ext > 0.f; scale[k] = usable[k] ? SAH_NB / ext : 0.f; }
+    Bin tbins_local[3 * SAH_NB];
+    std::vector<Bin> tbins_heap;
+    Bin* tbins = tbins_local;
+    if (T > 1) { tbins_heap.resize((size_t)T * 3 * SAH_NB); tbins = tbins_heap.data(); }
+    for (int i = 0; i < T * 3 * SAH_NB; ++i) bin_reset(&tbins[i]);
+    parallel_chunks(begin, end, T, [&](int lo, int hi, int tid) {
+        Bin* bins = &tbins[(size_t)tid * 3 * SAH_NB];
+        for (int i = lo; i < hi; ++i)
+            for (int k = 0; k < 3; ++k) {
+                if (!usable[k]) continue;
+                Bin* b = &bins[k * SAH_NB + bin_of(prims[i], k, clo[k], scale[k])];
+                bin_grow(b, prims[i].lo, prims[i].hi);
+                b->count++;
+            }
+    });
+    float best_cost = FLT_MAX; int best_axis = -1, best_bin = -1;
+    for (int k = 0; k < 3; ++k) {
+        if (!usable[k]) continue;
+        Bin bins[SAH_NB];
+        for (int b = 0; b < SAH_NB; ++b) {
+            bin_reset(&bins[b]);
+            for (int t = 0; t < T; ++t) {
+                const Bin* src = &tbins[((size_t)t * 3 + k) * SAH_NB + b];
+                if (src->count) { bin_grow(&bins[b], src->lo, src->hi); bins[b].count += src->count; }
+            }
+        }
+        float right_area[SAH_NB]; int right_count[SAH_NB];
+        Bin acc; bin_reset(&acc); int cnt = 0;
+        for (int b = SAH_NB - 1; b > 0; --b) {
+            if (bins[b].count) bin_grow(&acc, bins[b].lo, bins[b].hi);
+            cnt += bins[b].count;
+            right_area[b] = cnt ? bin_area(&acc) : 0.f; right_count[b] = cnt;
+        }
+        bin_reset(&acc); cnt = 0;
+        for (int b = 0; b < SAH_NB - 1; ++b) {
+            if (bins[b].count) bin_grow(&acc, bins[b].lo, bins[b].hi);
+            cnt += bins[b].count;
+            if (cnt == 0 || right_count[b + 1] == 0) continue;
+            const float cost = cnt * bin_area(&acc) + right_count[b + 1] * right_area[b + 1];
+            if (cost < best_cost) { best_cost = cost; best_axis = k; best_bin = b; }
+        }
+    }
+    int mid = begin + n / 2;
+    if (best_axis >= 0) {
+        const int k = best_axis;
+        auto left = [&](const BuildPrim& q) { return bin_of(q, k, clo[k], scale[k]) <= best_bin; };
+        if (T == 1) {
+            BuildPrim* m = std::partition(prims + begin, prims + end, left);
+            mid = (int)(m - prims);
+        } else {
+            mid = hoare_partition_parallel(prims, begin, end, T, left);
+        }
+    }
+    if (best_axis < 0 || mid == begin || mid == end) mid = begin + n / 2;     // coincident centroids: median split
+    return mid;
+}
+
+void range_box(const BuildPrim* prims, int b0, int b1, int threads, Bin* out) {
+    const int T = (threads > 1 && b1 - b0 >= g_par_min) ? threads : 1;
+    bin_reset(out);
+    if (T == 1) { for (int i = b0; i < b1; ++i) bin_grow(out, prims[i].lo, prims[i].hi); return; }
+    std::vector<Bin> part((size_t)T);
+    for (Bin& b : part) bin_reset(&b);
+    parallel_chunks(b0, b1, T, [&](int lo, int hi, int tid) { for (int i = lo; i < hi; ++i) bin_grow(&part[(size_t)tid], prims[i].lo, prims[i].hi); });
+    for (const Bin& b : part) if (b.lo[0] <= b.hi[0]) bin_grow(out, b.lo, b.hi);
+}
+
+struct SahRange { int begin, end, node; };
+
+// One node: split its range, write the two child slots with PREORDER child ids, hand back the inner children.
+int sah3_node(BuildPrim* prims, TbHostNode* nodes, const SahRange& t, int threads, SahRange out[2]) {
+    const int n = t.end - t.begin;
+    const int mid = n > 2 ? sah3_split(prims, t.begin, t.end, threads) : t.begin + 1;
+    TbHostNode* node = &nodes[(size_t)t.node];
+    const int ranges[2][2] = { { t.begin, mid }, { mid, t.end } };
+    const int child_id[2] = { t.node + 1, t.node + (mid - t.begin) };
+    int produced = 0;
+    for (int c = 0; c < 2; ++c) {
+        const int b0 = ranges[c][0], b1 = ranges[c][1];
+        Bin box;
+        range_box(prims, b0, b1, threads, &box);
+        node->aabb[c].min.x = box.lo[0]; node->aabb[c].min.y = box.lo[1]; node->aabb[c].min.z = box.lo[2];
+        node->aabb[c].max.x = box.hi[0]; node->aabb[c].max.y = box.hi[1]; node->aabb[c].max.z = box.hi[2];
+        if (b1 - b0 == 1) {
+            node->type[c] = 1;
+            node->index[c] = (int32_t)prims[b0].index;
+        } else {
+            node->type[c] = -1;
+            node->index[c] = child_id[c];
+            out[produced++] = SahRange{ b0, b1, child_id[c] };
+        }
+    }
+    return produced;
+}
 
 }  // namespace
 
 void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes) {
     size_t total = 0;
-    for (int j = 0; j < objects_count; ++j) total += objects[j].triangles_count;
+    std::vector<size_t> base((size_t)objects_count + 1, 0);
+    for (int j = 0; j < objects_count; ++j) { base[j] = total; total += objects[j].triangles_count; }
+    if (total < 2) { tb_bvh_build(objects, objects_count, nodes); return; }   // nothing to split: same tree as the reference mode
+    const int threads = host_threads();
     std::vector<BuildPrim> prims(total);
-    size_t p = 0;
-    for (int j = 0; j < objects_count; ++j)
-        for (size_t i = 0; i < objects[j].triangles_count; ++i, ++p) {
-            const TerraTriangle* t = &objects[j].triangles[i];
-            const float xs[3][3] = { { t->a.x, t->b.x, t->c.x }, { t->a.y, t->b.y, t->c.y }, { t->a.z, t->b.z, t->c.z } };
-            for (int k = 0; k < 3; ++k) {
-                float lo = xs[k][0] < xs[k][1] ? xs[k][0] : xs[k][1]; if (xs[k][2] < lo) lo = xs[k][2];
-                float hi = xs[k][0] > xs[k][1] ? xs[k][0] : xs[k][1]; if (xs[k][2] > hi) hi = xs[k][2];
-                prims[p].lo[k] = pad_lo(lo); prims[p].hi[k] = pad_hi(hi);
-                prims[p].c[k] = 0.5f * (lo + hi);
-            }
-            prims[p].index = (uint32_t)(j | ((int)i << 8));
-        }
-    nodes.assign(total > 1 ? total - 1 : 1, TbHostNode());
-    int nodes_count = 1;
-    std::vector<SahTask> stack;
-    stack.push_back(SahTask{ 0, (int)total, 0, -1 });
-    const int NB = 16;
-    while (!stack.empty()) {
-        SahTask t = stack.back();
-        stack.pop_back();
-        // range [begin,end) becomes node t.node: choose a split, children are leaves or new nodes
-        const int n = t.end - t.begin;
-        int mid = t.begin + n / 2;
-        if (n > 2) {
-            float clo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, chi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
-            for (int i = t.begin; i < t.end; ++i)
-                for (int k = 0; k < 3; ++k) { if (prims[i].c[k] < clo[k]) clo[k] = prims[i].c[k]; if (prims[i].c[k] > chi[k]) chi[k] = prims[i].c[k]; }
-            float best_cost = FLT_MAX; int best_axis = -1, best_bin = -1;
-            for (int k = 0; k < 3; ++k) {
-                const float ext = chi[k] - clo[k];
-                if (!(ext > 0.f)) continue;
-                Bin bins[NB];
-                for (int b = 0; b < NB; ++b) bin_reset(&bins[b]);
-                const float scale = NB / ext;
-                for (int i = t.begin; i < t.end; ++i) {
-                    int b = (int)((prims[i].c[k] - clo[k]) * scale);
-                    if (b >= NB) b = NB - 1;
-                    if (b < 0) b = 0;
-                    bin_grow(&bins[b], prims[i].lo, prims[i].hi);
-                    bins[b].count++;
+    for (int j = 0; j < objects_count; ++j) {
+        const TerraTriangle* tris = objects[j].triangles;
+        BuildPrim* dst = prims.data() + base[j];
+        parallel_chunks(0, (int)objects[j].triangles_count, threads, [=](int lo_, int hi_, int) {
+            for (int i = lo_; i < hi_; ++i) {
+                const TerraTriangle* t = &tris[i];
+                const float xs[3][3] = { { t->a.x, t->b.x, t->c.x }, { t->a.y, t->b.y, t->c.y }, { t->a.z, t->b.z, t->c.z } };
+                for (int k = 0; k < 3; ++k) {
+                    float lo = xs[k][0] < xs[k][1] ? xs[k][0] : xs[k][1]; if (xs[k][2] < lo) lo = xs[k][2];
+                    float hi = xs[k][0] > xs[k][1] ? xs[k][0] : xs[k][1]; if (xs[k][2] > hi) hi = xs[k][2];
+                    dst[i].lo[k] = pad_lo(lo); dst[i].hi[k] = pad_hi(hi);
+                    dst[i].c[k] = 0.5f * (lo + hi);
                 }
-                float right_area[NB]; int right_count[NB];
-                Bin acc; bin_reset(&acc); int cnt = 0;
-                for (int b = NB - 1; b > 0; --b) {
-                    if (bins[b].count) bin_grow(&acc, bins[b].lo, bins[b].hi);
-                    cnt += bins[b].count;
-                    right_area[b] = cnt ? bin_area(&acc) : 0.f; right_count[b] = cnt;
-                }
-                bin_reset(&acc); cnt = 0;
-                for (int b = 0; b < NB - 1; ++b) {
-                    if (bins[b].count) bin_grow(&acc, bins[b].lo, bins[b].hi);
-                    cnt += bins[b].count;
-                    if (cnt == 0 || right_count[b + 1] == 0) continue;
-                    const float cost = cnt * bin_area(&acc) + right_count[b + 1] * right_area[b + 1];
-                    if (cost < best_cost) { best_cost = cost; best_axis = k; best_bin = b; }
-                }
+                dst[i].index = (uint32_t)(j | (i << 8));
             }
-            if (best_axis >= 0) {
-                const int k = best_axis;
-                const float scale = NB / (chi[k] - clo[k]);
-                BuildPrim* first = prims.data() + t.begin;
-                BuildPrim* last = prims.data() + t.end;
-                BuildPrim* m = std::partition(first, last, [&](const BuildPrim& q) {
-                    int b = (int)((q.c[k] - clo[k]) * scale);
-                    if (b >= NB) b = NB - 1;
-                    if (b < 0) b = 0;
-                    return b <= best_bin;
-                });
-                mid = (int)(m - prims.data());
-            }
-            if (best_axis < 0 || mid == t.begin || mid == t.end) {     // coincident centroids: median split
-                mid = t.begin + n / 2;
-            }
-        } else {
-            mid = t.begin + 1;
-        }
-        TbHostNode* node = &nodes[(size_t)t.node];
-        const int ranges[2][2] = { { t.begin, mid }, { mid, t.end } };
-        for (int c = 0; c < 2; ++c) {
-            const int b0 = ranges[c][0], b1 = ranges[c][1];
-            Bin box; bin_reset(&box);
-            for (int i = b0; i < b1; ++i) bin_grow(&box, prims[i].lo, prims[i].hi);
-            node->aabb[c].min.x = box.lo[0]; node->aabb[c].min.y = box.lo[1]; node->aabb[c].min.z = box.lo[2];
-            node->aabb[c].max.x = box.hi[0]; node->aabb[c].max.y = box.hi[1]; node->aabb[c].max.z = box.hi[2];
-            if (b1 - b0 == 1) {
-                node->type[c] = 1;
-                node->index[c] = (int32_t)prims[b0].index;
-            } else {
-                node->type[c] = -1;
-                node->index[c] = nodes_count;
-                stack.push_back(SahTask{ b0, b1, nodes_count, c });
-                ++nodes_count;
-            }
-        }
+        });
     }
-    nodes.resize((size_t)nodes_count);
+    std::vector<TbHostNode> pre(total > 1 ? total - 1 : 1, TbHostNode());
+    // ---- top levels: big ranges one at a time, passes split over the threads
+    const int grain = std::max(std::min(4096, g_par_min), (int)(total / ((size_t)threads * 8)));
+    std::vector<SahRange> top, tasks;
+    top.push_back(SahRange{ 0, (int)total, 0 });
+    while (!top.empty()) {
+        const SahRange t = top.back();
+        top.pop_back();
+        if (threads > 1 && t.end - t.begin <= grain) { tasks.push_back(t); continue; }
+        SahRange ch[2];
+        const int k = sah3_node(prims.data(), pre.data(), t, threads, ch);
+        for (int c = 0; c < k; ++c) top.push_back(ch[c]);
+    }
+    // ---- subtrees: independent serial builds
+    std::atomic<size_t> next(0);
+    auto worker = [&]() {
+        std::vector<SahRange> stack;
+        for (size_t i = next.fetch_add(1); i < tasks.size(); i = next.fetch_add(1)) {
+            stack.push_back(tasks[i]);
+            while (!stack.empty()) {
+                const SahRange t = stack.back();
+                stack.pop_back();
+                SahRange ch[2];
+                const int k = sah3_node(prims.data(), pre.data(), t, 1, ch);
+                for (int c = 0; c < k; ++c) stack.push_back(ch[c]);
+            }
+        }
+    };
+    if (!tasks.empty()) {
+        std::vector<std::thread> pool;
+        for (int t = 1; t < threads; ++t) pool.emplace_back(worker);
+        worker();
+        for (std::thread& th : pool) th.join();
+    }
+    // ---- renumber preorder ids into the serial builder's allocation order (pop a node, number its inner
+    //      children consecutively, push them: siblings end up adjacent in memory)
+    const size_t n_nodes = total > 1 ? total - 1 : 1;
+    std::vector<int32_t> new_id(n_nodes, -1);
+    std::vector<int32_t> order;                        // order[new] = old
+    order.reserve(n_nodes);
+    std::vector<int32_t> stack;
+    new_id[0] = 0; order.push_back(0); stack.push_back(0);
+    while (!stack.empty()) {
+        const int32_t old = stack.back();
+        stack.pop_back();
+        const TbHostNode& nd = pre[(size_t)old];
+        for (int c = 0; c < 2; ++c)
+            if (nd.type[c] == -1) { new_id[(size_t)nd.index[c]] = (int32_t)order.size(); order.push_back(nd.index[c]); stack.push_back(nd.index[c]); }
+    }
+    nodes.assign(order.size(), TbHostNode());
+    parallel_chunks(0, (int)order.size(), threads, [&](int lo_, int hi_, int) {
+        for (int i = lo_; i < hi_; ++i) {
+            TbHostNode nd = pre[(size_t)order[(size_t)i]];
+            for (int c = 0; c < 2; ++c) if (nd.type[c] == -1) nd.index[c] = new_id[(size_t)nd.index[c]];
+            nodes[(size_t)i] = nd;
+        }
+    });
 }
 
 // ------------------------------------------------------------------------------------ quantised nodes
@@ -369,15 +557,27 @@ void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vecto
 // rounding of the kernel's folded decode constant. The decoded box therefore contains the float box.
 void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out) {
     const size_t n = flat.nodes.size() / 16;
+    const int threads = host_threads();
+    std::vector<double> part((size_t)threads * 6);
+    for (int t = 0; t < threads; ++t) for (int k = 0; k < 3; ++k) { part[(size_t)t * 6 + k] = DBL_MAX; part[(size_t)t * 6 + 3 + k] = -DBL_MAX; }
+    parallel_chunks(0, (int)n, threads, [&](int lo_, int hi_, int tid) {
+        double* plo = &part[(size_t)tid * 6];
+        double* phi = plo + 3;
+        for (size_t i = (size_t)lo_; i < (size_t)hi_; ++i) {
+            const float* q = &flat.nodes[i * 16];
+            for (int c = 0; c < 2; ++c)
+                for (int k = 0; k < 3; ++k) {
+                    if (q[6 * c + k] < plo[k]) plo[k] = q[6 * c + k];
+                    if (q[6 * c + 3 + k] > phi[k]) phi[k] = q[6 * c + 3 + k];
+                }
+        }
+    });
     double lo[3] = { DBL_MAX, DBL_MAX, DBL_MAX }, hi[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
-    for (size_t i = 0; i < n; ++i) {
-        const float* q = &flat.nodes[i * 16];
-        for (int c = 0; c < 2; ++c)
-            for (int k = 0; k < 3; ++k) {
-                if (q[6 * c + k] < lo[k]) lo[k] = q[6 * c + k];
-                if (q[6 * c + 3 + k] > hi[k]) hi[k] = q[6 * c + 3 + k];
-            }
-    }
+    for (int t = 0; t < threads; ++t)
+        for (int k = 0; k < 3; ++k) {
+            if (part[(size_t)t * 6 + k] < lo[k]) lo[k] = part[(size_t)t * 6 + k];
+            if (part[(size_t)t * 6 + 3 + k] > hi[k]) hi[k] = part[(size_t)t * 6 + 3 + k];
+        }
     for (int k = 0; k < 3; ++k) {
         double ext = hi[k] - lo[k];
         if (!(ext > 0)) ext = 1.0;
@@ -386,7 +586,8 @@ void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out) {
         out->grid_cell[k] = (float)((ext + 2 * pad) / 65535.0);
     }
     out->nodes.assign(n * 8, 0u);
-    for (size_t i = 0; i < n; ++i) {
+    parallel_chunks(0, (int)n, threads, [&](int lo_, int hi_, int) {
+    for (size_t i = (size_t)lo_; i < (size_t)hi_; ++i) {
         const float* q = &flat.nodes[i * 16];
         uint16_t g[12];
         for (int c = 0; c < 2; ++c)
@@ -407,6 +608,7 @@ void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out) {
         for (int j = 0; j < 6; ++j) w[j] = (uint32_t)g[2 * j] | ((uint32_t)g[2 * j + 1] << 16);
         memcpy(&w[6], &q[12], 8);              // the two child references, as in the float node
     }
+    });
 }
 
 // ------------------------------------------------------------------------------------ 4-wide nodes

@@ -191,6 +191,30 @@ def test_sah3_tree_is_a_valid_bvh(api, host_scene):
             assert (box[0:3] <= sub_lo[n, c]).all() and (box[3:6] >= sub_hi[n, c]).all()
 
 
+def test_sah3_parallel_build_matches_serial(api, prod, monkeypatch):
+    """The host sah3 build runs on all cores (preorder node ids, parallel binning + two-pointer partition on
+    the top ranges, independent subtree tasks below, renumbering at the end); the node array must not
+    depend on the thread count or on where the serial/parallel switch sits. The scene has clusters of
+    identical triangles (coincident centroids -> median fallback, order-sensitive)."""
+    rng = np.random.default_rng(11)
+    n = 6000
+    c = rng.uniform(-50, 50, (n, 1, 3)).astype(np.float32)
+    tris = (c + rng.uniform(-1, 1, (n, 3, 3)).astype(np.float32)).astype(np.float32)
+    tris[1000:1400] = tris[1000]                    # 400 coincident triangles
+    tris[3000:3003] = tris[3000]
+    s = api.Scene(prod)
+    s.add_object(tris[:2500])
+    s.add_object(tris[2500:])
+    hashes = set()
+    for threads, par_min in (("1", "65536"), ("2", "64"), ("5", "16"), ("8", "1000"), ("7", "2")):
+        monkeypatch.setenv("TERRA_B200_BUILD_THREADS", threads)
+        monkeypatch.setenv("TERRA_B200_BUILD_PAR_MIN", par_min)
+        assert prod.lib.terra_b200_build_host_bvh(s.h, api.BVH_SAH3, None, None) == n - 1
+        hashes.add(hashlib.sha256(s.bvh_nodes().tobytes()).hexdigest())
+    assert len(hashes) == 1
+    s.destroy()
+
+
 def test_sah3_and_reference_trees_give_identical_hits(api, scenes, prod, oracle, host_scene):
     """Closest hits do not depend on the tree: canonical walk over the sah3 node array vs the
     reference walk over the reference tree (ids may differ only on exact-t ties)."""
