@@ -443,12 +443,28 @@ def run_traversal_arm(args):
     ms = tot / args.steps
     # e2e through host buffers on a 16M-ray slice
     n_e2e = min(n_rays, 1 << 24)
-    oh = o4[:n_e2e, :3].contiguous().cpu().numpy()
-    dh = d4[:n_e2e, :3].contiguous().cpu().numpy()
-    s.trace_rays(oh[:1000], dh[:1000])
+    # (page-locked buffers from terra_b200_host_alloc, as the bench contract asks; best of 3 calls after one
+    # warm-up call that sizes the staging buffers; the pageable figure is reported beside it)
+    oh_pin, dh_pin = api.PinnedArray(lib, (n_e2e, 3), np.float32), api.PinnedArray(lib, (n_e2e, 3), np.float32)
+    hh_pin = api.PinnedArray(lib, n_e2e, api.HIT_DTYPE)
+    oh, dh, hh = oh_pin.array, dh_pin.array, hh_pin.array
+    oh[:] = o4[:n_e2e, :3].contiguous().cpu().numpy()
+    dh[:] = d4[:n_e2e, :3].contiguous().cpu().numpy()
+    s.trace_rays(oh, dh, out=hh)
+    e2e_s = float("inf")
+    for _ in range(3):
+        flush.zero_(); torch.cuda.synchronize()
+        t0 = time.time()
+        s.trace_rays(oh, dh, out=hh)
+        e2e_s = min(e2e_s, time.time() - t0)
+    if not np.array_equal(hh["t"].view(np.uint32), hits[:n_e2e, 0].contiguous().cpu().numpy().view(np.uint32)):
+        raise SystemExit("bench.py: the host-buffer path disagrees with the resident path")
+    oh_page, dh_page = np.array(oh), np.array(dh)
+    s.trace_rays(oh_page[:1000], dh_page[:1000])
     t0 = time.time()
-    hh = s.trace_rays(oh, dh)
-    e2e_s = time.time() - t0
+    s.trace_rays(oh_page, dh_page)
+    e2e_pageable_s = time.time() - t0
+    del oh_page, dh_page
     # canonical work counters: oracle walk of the SAME tree over a 200k-ray sample (CPU, untimed)
     ora = api.OracleLib()
     osc = api.OracleScene(ora, s) if wl["tris"] <= 2_000_000 and not args.no_cpu_baseline else None
@@ -473,7 +489,8 @@ def run_traversal_arm(args):
         "config": {"workload": wl["name"], "rays": n_rays, "triangles": wl["tris"], "bvh": os.environ.get("TERRA_B200_BVH", "sah3"),
                    "l2": "flushed between timed iterations; rays+hits (3 GB) exceed L2"},
         "e2e": {"value": n_e2e / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": n_e2e * 24, "d2h_bytes_per_step": n_e2e * 16,
-                "rays": n_e2e},
+                "rays": n_e2e, "host_buffers": "page-locked (terra_b200_host_alloc), best of 3 calls",
+                "pageable_value": n_e2e / e2e_pageable_s / 1e6},
         "gpu_launches": int(st.kernel_launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": profile_traffic("k_trace_" + args.workload, n_rays), "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,

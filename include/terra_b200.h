@@ -325,14 +325,50 @@ void        terra_b200_set_bvh_mode(int mode);
  * src/Terra.c:468-477, 1804-1810). Off by default; call after terra_scene_commit. Checked against the
  * reference compiled with exactly that one line restored (oracle/Makefile, "patched oracle"). */
 void        terra_b200_set_env_lit(HTerraScene scene, int on);
+/* on = 2 ("env-lit, importance sampled"): the same radiance as on = 1, estimated with explicit environment
+ * samples in the direct and direct-MIS integrators: the reference's written-but-never-called
+ * TerraDistributon2D (src/Terra.c:760-846) over luminance x sin(theta) of the lat-long environment texture picks
+ * a direction per bounce, a visibility ray tests it, power-heuristic weights combine it with the BSDF sample
+ * under MIS, and rays that leave the scene count at the camera ray only. Needs a lat-long environment
+ * (terra_attribute_init_cubemap); anything else behaves as on = 1. The simple integrator is unchanged. */
+
+/* terra_distribution_2d_init + n x terra_distribution_2d_sample (src/Terra.c:811-846) on the device, for a
+ * function f of ny rows x nx columns: out4[4*i] = { s1 (row axis), s2 (column axis), pdf, 0 } for (e1[i], e2[i]).
+ * Bit-identical to the reference's exported functions (tests/test_gpu_distribution.py). */
+void        terra_b200_distribution_2d_sample(HTerraScene scene, const float* f, size_t nx, size_t ny, size_t n,
+                                              const float* e1, const float* e2, float* out4);
 /* Wall time of the last terra_scene_commit's stages, ms: [0] tree build (terra_bvh_create's replacement),
  * [1] flatten to the GPU layout, [2] node quantisation, [3] host->device upload. */
 void        terra_b200_commit_ms(HTerraScene scene, float* out4);
 /* Device time (kernels + sort) and time including the triangle upload of the last LBVH build, ms. */
 void        terra_b200_lbvh_build_ms(float* device_ms, float* with_upload_ms);
 
-/* Traversal micro-benchmark / parity entry points (= terra_scene_raycast without shading).
- * Host buffers: origins/dirs are n x 3 floats; the H2D/D2H copies are part of the call. */
+/* Asynchronous tile jobs: what satellite's TerraRenderer does with its worker threads
+ * (satellite/src/Renderer.cpp:70-98 terra_render_launcher, :316-349 tile grid + job push) as a library call.
+ * The region is cut into tile_size x tile_size tiles in row-major order (tile_size 0 = one call for the whole
+ * region) and a worker thread calls terra_render on each; the call returns at once. on_tile_begin / on_tile_end
+ * (either may be NULL) run on the worker thread around each tile. The camera is copied; scene and framebuffer
+ * must outlive the job. Results are those of the same terra_render calls made in that order by the caller. */
+typedef struct TerraB200Job* HTerraB200Job;
+typedef void (*TerraB200TileEvent)(size_t x, size_t y, size_t width, size_t height, void* user);
+HTerraB200Job terra_b200_render_async(const TerraCamera* camera, HTerraScene scene, const TerraFramebuffer* framebuffer,
+                                      size_t x, size_t y, size_t width, size_t height, size_t tile_size,
+                                      TerraB200TileEvent on_tile_begin, TerraB200TileEvent on_tile_end, void* user);
+int         terra_b200_job_poll(HTerraB200Job job);      /* tiles left (the reference's _tile_counter); 0 = finished */
+void        terra_b200_job_wait(HTerraB200Job job);      /* block until every tile is done */
+void        terra_b200_job_cancel(HTerraB200Job job);    /* skip tiles not started yet; returns once the running one ends */
+void        terra_b200_job_release(HTerraB200Job job);   /* wait, then free the handle */
+
+/* Page-locked host memory for large ray batches (and anything else handed to the entry points below):
+ * copies from / to it run at PCIe speed and overlap the kernels. NULL when no CUDA device is visible.
+ * Framebuffers made by terra_framebuffer_create are page-locked already. */
+void*       terra_b200_host_alloc(size_t bytes);
+void        terra_b200_host_free(void* p);
+
+/* Traversal micro-benchmark / parity entry points (= terra_scene_raycast without shading, src/Terra.c:276-279,
+ * for a whole batch). Host buffers: origins/dirs are n x 3 floats; the H2D/D2H copies are part of the call
+ * and are pipelined against the traversal in chunks (copy in | trace | copy out on three streams) when the
+ * buffers are page-locked; pageable buffers give the same hits, serially. */
 void terra_b200_trace_rays(HTerraScene scene, size_t n, const float* origins, const float* directions,
                            TerraB200Hit* hits_out);
 /* Device buffers: float4 per ray (xyz used), caller's stream (cudaStream_t as void*). */

@@ -874,3 +874,83 @@ void oracle_render(const OracleScene* s, const TerraCamera* cam, const TerraFram
             fb->pixels[i * fb->width + j] = c;
         }
 }
+
+/* ================================================================================ discrete distributions
+ * terra_distribution_1d_init (Terra.c:760-779): running float sum in index order -> unnormalised cdf; every
+ * entry divided by the total afterwards. */
+float oracle_distribution_1d_init(const float* f, size_t n, float* cdf_out) {
+    float integral = 0;
+    for (size_t i = 0; i < n; ++i) {
+        integral += f[i];
+        cdf_out[i] = integral;
+    }
+    for (size_t i = 0; i < n; ++i) cdf_out[i] /= integral;
+    return integral;
+}
+
+/* terra_distribution_1d_sample (Terra.c:781-809): first bucket with e < cdf[i]; pdf = f[i] / integral; the
+ * returned coordinate interpolates inside the bucket, (i + (e - prev) / (cdf[i] - prev)) / n. No bucket
+ * (e >= cdf[n-1]): the reference asserts, and returns FLT_MAX under NDEBUG. */
+float oracle_distribution_1d_sample(const float* f, const float* cdf, float integral, size_t n, float e,
+                                    float* pdf_out, size_t* idx_out) {
+    float prev = 0;
+    for (size_t i = 0; i < n; ++i) {
+        float curr = cdf[i];
+        if (e < curr) {
+            if (pdf_out) *pdf_out = f[i] / integral;
+            if (idx_out) *idx_out = i;
+            float d = e - prev;
+            d /= curr - prev;
+            return (i + d) / n;
+        }
+        prev = curr;
+    }
+    return FLT_MAX;
+}
+
+/* terra_distribution_2d_init (Terra.c:811-833): one conditional per row; the marginal is the 1-D distribution
+ * of the row integrals (built by the same running sum). */
+OracleDistribution2D* oracle_distribution_2d_create(const float* f, size_t nx, size_t ny) {
+    OracleDistribution2D* d = (OracleDistribution2D*)calloc(1, sizeof *d);
+    d->nx = nx; d->ny = ny;
+    d->f = (float*)malloc(sizeof(float) * nx * ny);
+    d->cdf = (float*)malloc(sizeof(float) * nx * ny);
+    d->row_integral = (float*)malloc(sizeof(float) * ny);
+    d->marginal_cdf = (float*)malloc(sizeof(float) * ny);
+    memcpy(d->f, f, sizeof(float) * nx * ny);
+    for (size_t i = 0; i < ny; ++i) d->row_integral[i] = oracle_distribution_1d_init(f + nx * i, nx, d->cdf + nx * i);
+    d->integral = oracle_distribution_1d_init(d->row_integral, ny, d->marginal_cdf);
+    return d;
+}
+
+void oracle_distribution_2d_destroy(OracleDistribution2D* d) {
+    if (!d) return;
+    free(d->f); free(d->cdf); free(d->row_integral); free(d->marginal_cdf); free(d);
+}
+
+/* terra_distribution_2d_sample (Terra.c:835-846): row from the marginal with e1, column from that row's
+ * conditional with e2, pdf = product of the two bucket probabilities. */
+void oracle_distribution_2d_sample(const OracleDistribution2D* d, size_t n, const float* e1, const float* e2, float* out) {
+    for (size_t k = 0; k < n; ++k) {
+        float pdfs[2] = { 0.f, 0.f };
+        size_t i = 0;
+        float s1 = oracle_distribution_1d_sample(d->row_integral, d->marginal_cdf, d->integral, d->ny, e1[k], &pdfs[0], &i);
+        float s2 = oracle_distribution_1d_sample(d->f + d->nx * i, d->cdf + d->nx * i, d->row_integral[i], d->nx, e2[k], &pdfs[1], NULL);
+        out[4 * k] = s1; out[4 * k + 1] = s2; out[4 * k + 2] = pdfs[0] * pdfs[1]; out[4 * k + 3] = 0.f;
+    }
+}
+
+/* Importance of a lat-long texel for the env-NEE extension (no reference counterpart: the reference never
+ * builds the distribution): luminance with the reference's weights (Terra.c:1036) times the solid-angle
+ * factor of the row, sin(theta) at the row centre, theta = terra_PI * (y + 0.5) / ny as in
+ * terra_texture_sample_latlong's v = theta / terra_PI * height (Terra.c:468-477). */
+void oracle_env_importance(const float* rgb, size_t nx, size_t ny, float* f_out) {
+    for (size_t y = 0; y < ny; ++y) {
+        const float w = sinf(OPI * (((float)y + 0.5f) / (float)ny));
+        for (size_t x = 0; x < nx; ++x) {
+            const float* p = rgb + (y * nx + x) * 3;
+            const float lum = 0.212671f * p[0] + 0.715160f * p[1] + 0.072169f * p[2];
+            f_out[y * nx + x] = lum * w;
+        }
+    }
+}

@@ -57,6 +57,28 @@ int  oracle_raycast_surface(const OracleScene* s, const float* origin, const flo
 void oracle_surface_from_normal(const float* normal, const float* attributes24, TerraShadingSurface* sf);
 
 /* Presets as TerraBSDF callbacks (usable inside the reference's terra_render). */
+/* Discrete distributions (src/Terra.c:760-846, src/TerraPrivate.h:85-102): the reference's written-but-unused
+ * building block for an importance-sampled environment. Flat API over caller arrays: cdf/func_out have n
+ * (nx*ny) floats. Pinned bit-exact against the functions libterra_ref.so exports. */
+float oracle_distribution_1d_init(const float* f, size_t n, float* cdf_out);                      /* returns the integral */
+float oracle_distribution_1d_sample(const float* f, const float* cdf, float integral, size_t n, float e,
+                                    float* pdf_out, size_t* idx_out);
+typedef struct {
+    size_t nx, ny;
+    float* f;            /* ny rows of nx */
+    float* cdf;          /* conditional cdfs, ny rows of nx */
+    float* row_integral; /* = marginal f, ny */
+    float* marginal_cdf; /* ny */
+    float  integral;
+} OracleDistribution2D;
+OracleDistribution2D* oracle_distribution_2d_create(const float* f, size_t nx, size_t ny);
+void  oracle_distribution_2d_destroy(OracleDistribution2D* d);
+/* n samples: out[4*i] = {s1 (row axis), s2 (column axis), pdf, 0} */
+void  oracle_distribution_2d_sample(const OracleDistribution2D* d, size_t n, const float* e1, const float* e2, float* out);
+/* Environment importance function of the env-NEE extension: luminance (Terra.c:1036 weights) of the point-sampled
+ * lat-long texel times sin(pi_ref * (y + 0.5) / ny). rgb = ny*nx*3 floats. */
+void  oracle_env_importance(const float* rgb, size_t nx, size_t ny, float* f_out);
+
 void terra_oracle_bsdf_diffuse_init(TerraBSDF* b);
 void terra_oracle_bsdf_phong_init(TerraBSDF* b);
 void terra_oracle_bsdf_ggx_init(TerraBSDF* b);

@@ -132,7 +132,11 @@ class TerraLib:
         self.is_product = hasattr(L, "terra_b200_device_count")
         self.is_reference = hasattr(L, "ref_bvh_build")
 
+        older_build = bool(os.environ.get("TERRA_B200_LIB"))     # A/B runs against a previous build of the library
+
         def sig(name, res, *args):
+            if older_build and not hasattr(L, name):
+                return None                     # an entry point that build does not have yet: calling it raises
             f = getattr(L, name)
             f.restype, f.argtypes = res, list(args)
             return f
@@ -166,6 +170,14 @@ class TerraLib:
             sig("terra_b200_set_device", None, C.c_int)
             sig("terra_b200_probe_bandwidth", C.c_double, _sz, C.c_int)
             sig("terra_b200_set_env_lit", None, _vp, C.c_int)
+            sig("terra_b200_render_async", _vp, C.POINTER(Camera), _vp, C.POINTER(Framebuffer), _sz, _sz, _sz, _sz, _sz, _vp, _vp, _vp)
+            sig("terra_b200_job_poll", C.c_int, _vp)
+            sig("terra_b200_job_wait", None, _vp)
+            sig("terra_b200_job_cancel", None, _vp)
+            sig("terra_b200_job_release", None, _vp)
+            sig("terra_b200_distribution_2d_sample", None, _vp, _vp, _sz, _sz, _sz, _vp, _vp, _vp)
+            sig("terra_b200_host_alloc", _vp, _sz)
+            sig("terra_b200_host_free", None, _vp)
             sig("terra_b200_commit_ms", None, _vp, C.POINTER(C.c_float))
             sig("terra_b200_lbvh_build_ms", None, C.POINTER(C.c_float), C.POINTER(C.c_float))
             sig("terra_b200_set_seed", None, _vp, C.c_uint64)
@@ -203,6 +215,37 @@ def _ptr(a: np.ndarray) -> int:
 
 
 _oracle_for_presets = None
+
+
+TILE_EVENT = C.CFUNCTYPE(None, _sz, _sz, _sz, _sz, _vp)      # TerraB200TileEvent
+
+
+class PinnedArray:
+    """numpy view of page-locked host memory from terra_b200_host_alloc (freed with the object).
+    `a = PinnedArray(lib, (n, 3), np.float32); a.array[...] = ...`"""
+
+    def __init__(self, lib: "TerraLib", shape, dtype):
+        dtype = np.dtype(dtype)
+        shape = (shape,) if isinstance(shape, int) else tuple(shape)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        self._lib = lib
+        self._p = lib.lib.terra_b200_host_alloc(max(1, nbytes))
+        if not self._p:
+            raise MemoryError("terra_b200_host_alloc: no CUDA device or no memory to page-lock")
+        buf = (C.c_uint8 * max(1, nbytes)).from_address(self._p)
+        self.array = np.frombuffer(buf, dtype=np.uint8, count=nbytes).view(dtype).reshape(shape)
+
+    def free(self):
+        if self._p:
+            self.array = None
+            self._lib.lib.terra_b200_host_free(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 class Scene:
@@ -345,10 +388,13 @@ class Scene:
         return res.reshape(height, width), pix
 
     # -- product extensions ---------------------------------------------------------------
-    def trace_rays(self, origins: np.ndarray, dirs: np.ndarray) -> np.ndarray:
+    def trace_rays(self, origins: np.ndarray, dirs: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """Closest hits of a host ray batch. Page-locked arrays (`PinnedArray`) for origins / dirs / out make
+        the copies overlap the traversal; plain numpy arrays give the same hits."""
         o = np.ascontiguousarray(origins, np.float32)
         d = np.ascontiguousarray(dirs, np.float32)
-        hits = np.empty(o.shape[0], HIT_DTYPE)
+        hits = np.empty(o.shape[0], HIT_DTYPE) if out is None else out
+        assert hits.dtype == HIT_DTYPE and hits.shape[0] == o.shape[0] and hits.flags.c_contiguous
         self.lib.terra_b200_trace_rays(self.h, o.shape[0], _ptr(o), _ptr(d), _ptr(hits))
         return hits
 
@@ -442,9 +488,62 @@ class OracleLib:
         sig("oracle_surface_from_normal", None, _vp, _vp, C.POINTER(ShadingSurface))
         for p in ("diffuse", "phong", "ggx", "glass"):
             sig(f"terra_oracle_bsdf_{p}_init", None, C.POINTER(BSDF))
+        sig("oracle_distribution_1d_init", C.c_float, _vp, _sz, _vp)
+        sig("oracle_distribution_1d_sample", C.c_float, _vp, _vp, C.c_float, _sz, C.c_float, C.POINTER(C.c_float), C.POINTER(_sz))
+        sig("oracle_distribution_2d_create", _vp, _vp, _sz, _sz)
+        sig("oracle_distribution_2d_destroy", None, _vp)
+        sig("oracle_distribution_2d_sample", None, _vp, _sz, _vp, _vp, _vp)
+        sig("oracle_env_importance", None, _vp, _sz, _sz, _vp)
 
     def __getattr__(self, name):
         return getattr(self.lib, name)
+
+    def distribution_2d_sample(self, f: np.ndarray, e1: np.ndarray, e2: np.ndarray) -> np.ndarray:
+        """(n,4) = s1 (row axis), s2 (column axis), pdf, 0 for a (ny,nx) function (oracle restatement)."""
+        f = np.ascontiguousarray(f, np.float32)
+        e1, e2 = np.ascontiguousarray(e1, np.float32), np.ascontiguousarray(e2, np.float32)
+        d = self.lib.oracle_distribution_2d_create(_ptr(f), f.shape[1], f.shape[0])
+        out = np.zeros((e1.shape[0], 4), np.float32)
+        self.lib.oracle_distribution_2d_sample(d, e1.shape[0], _ptr(e1), _ptr(e2), _ptr(out))
+        self.lib.oracle_distribution_2d_destroy(d)
+        return out
+
+    def env_importance(self, rgb: np.ndarray) -> np.ndarray:
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        out = np.zeros(rgb.shape[:2], np.float32)
+        self.lib.oracle_env_importance(_ptr(rgb), rgb.shape[1], rgb.shape[0], _ptr(out))
+        return out
+
+
+class _RefDistribution1D(C.Structure):          # src/TerraPrivate.h:85-90
+    _fields_ = [("f", C.POINTER(C.c_float)), ("n", C.c_size_t), ("cdf", C.POINTER(C.c_float)), ("integral", C.c_float)]
+
+
+class _RefDistribution2D(C.Structure):          # src/TerraPrivate.h:93-96
+    _fields_ = [("marginal", _RefDistribution1D), ("conditionals", C.POINTER(_RefDistribution1D))]
+
+
+def reference_distribution_2d_sample(ref: "TerraLib", f: np.ndarray, e1: np.ndarray, e2: np.ndarray):
+    """The reference's own terra_distribution_2d_init / _sample (exported by libterra_ref.so, called by nothing
+    in the reference). Returns ((n,4) samples like OracleLib.distribution_2d_sample, marginal cdf, conditional cdfs)."""
+    L = ref.lib
+    L.terra_distribution_2d_init.restype, L.terra_distribution_2d_init.argtypes = None, [C.POINTER(_RefDistribution2D), _vp, _sz, _sz]
+    L.terra_distribution_2d_sample.restype = Float2
+    L.terra_distribution_2d_sample.argtypes = [C.POINTER(_RefDistribution2D), C.c_float, C.c_float, C.POINTER(C.c_float)]
+    f = np.ascontiguousarray(f, np.float32)
+    ny, nx = f.shape
+    cond = (_RefDistribution1D * ny)()
+    d = _RefDistribution2D()
+    d.conditionals = cond                       # the caller provides the array (Terra.c:812-814 indexes it)
+    L.terra_distribution_2d_init(C.byref(d), _ptr(f), nx, ny)
+    out = np.zeros((len(e1), 4), np.float32)
+    pdf = C.c_float()
+    for k in range(len(e1)):
+        r = L.terra_distribution_2d_sample(C.byref(d), float(e1[k]), float(e2[k]), C.byref(pdf))
+        out[k, 0], out[k, 1], out[k, 2] = r.x, r.y, pdf.value
+    marg = np.ctypeslib.as_array(d.marginal.cdf, (ny,)).copy()
+    ccdf = np.stack([np.ctypeslib.as_array(cond[i].cdf, (nx,)).copy() for i in range(ny)])
+    return out, marg, ccdf
 
 
 class OracleScene:

@@ -18,7 +18,9 @@
 
 #include <algorithm>
 #include <chrono>
+#include <atomic>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include <vector_types.h>
@@ -588,6 +590,59 @@ extern "C" void terra_render(const TerraCamera* camera, HTerraScene h, const Ter
     tb_device_render(s->dev, &cam, fb, x, y, width, height, effective_spp(&s->opts), next_seed(s));
 }
 
+// =============================================================================== async tile jobs
+// The satellite front-end renders a frame as square tiles pushed to worker threads that each call
+// terra_render and report tile begin / end to the UI thread, with an atomic count of tiles left
+// (satellite/src/Renderer.cpp:70-98, 316-349). The same contract as a library call: the region is cut into
+// tiles in the same row-major order, ONE worker thread per job walks them (a tile already fills the GPU;
+// the scene lock serialises jobs that share a scene), and the caller polls, waits or cancels.
+struct TerraB200Job {
+    TerraCamera camera;
+    HTerraScene scene;
+    const TerraFramebuffer* fb;
+    size_t x, y, w, h, tile;
+    TerraB200TileEvent on_begin, on_end;
+    void* user;
+    std::atomic<int> tiles_left;
+    std::atomic<bool> cancel;
+    std::thread worker;
+};
+
+static void job_main(TerraB200Job* j) {
+    const size_t t = j->tile ? j->tile : (j->w > j->h ? j->w : j->h);
+    for (size_t ty = 0; ty < j->h; ty += t)
+        for (size_t tx = 0; tx < j->w; tx += t) {
+            const size_t tw = tx + t < j->w ? t : j->w - tx, th = ty + t < j->h ? t : j->h - ty;
+            if (!j->cancel.load()) {
+                if (j->on_begin) j->on_begin(j->x + tx, j->y + ty, tw, th, j->user);
+                terra_render(&j->camera, j->scene, j->fb, j->x + tx, j->y + ty, tw, th);
+                if (j->on_end) j->on_end(j->x + tx, j->y + ty, tw, th, j->user);
+            }
+            j->tiles_left.fetch_sub(1);
+        }
+}
+
+extern "C" HTerraB200Job terra_b200_render_async(const TerraCamera* camera, HTerraScene h, const TerraFramebuffer* fb,
+                                                 size_t x, size_t y, size_t width, size_t height, size_t tile_size,
+                                                 TerraB200TileEvent on_tile_begin, TerraB200TileEvent on_tile_end, void* user) {
+    committed(h, "terra_b200_render_async");
+    if (x + width > fb->width || y + height > fb->height) tb_fatal("terra_b200_render_async region outside the framebuffer");
+    TerraB200Job* j = new TerraB200Job();
+    j->camera = *camera; j->scene = h; j->fb = fb;
+    j->x = x; j->y = y; j->w = width; j->h = height; j->tile = tile_size;
+    j->on_begin = on_tile_begin; j->on_end = on_tile_end; j->user = user;
+    const size_t t = tile_size ? tile_size : (width > height ? width : height);
+    const size_t nx = t ? (width + t - 1) / t : 0, ny = t ? (height + t - 1) / t : 0;
+    j->tiles_left.store((int)(nx * ny));
+    j->cancel.store(false);
+    j->worker = std::thread(job_main, j);
+    return j;
+}
+extern "C" int terra_b200_job_poll(HTerraB200Job j) { return j->tiles_left.load(); }
+extern "C" void terra_b200_job_wait(HTerraB200Job j) { if (j->worker.joinable()) j->worker.join(); }
+extern "C" void terra_b200_job_cancel(HTerraB200Job j) { j->cancel.store(true); terra_b200_job_wait(j); }
+extern "C" void terra_b200_job_release(HTerraB200Job j) { terra_b200_job_wait(j); delete j; }
+
 // =============================================================================== extensions
 extern "C" int  terra_b200_device_count(void) { return tb_cuda_device_count(); }
 extern "C" void terra_b200_set_device(int device) { g_device_index = device; }
@@ -599,6 +654,13 @@ extern "C" void terra_b200_set_seed(HTerraScene h, uint64_t seed) {
 extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) { tb_device_get_stats(committed(h, "terra_b200_get_stats")->dev, out); }
 extern "C" void terra_b200_reset_stats(HTerraScene h) { tb_device_reset_stats(committed(h, "terra_b200_reset_stats")->dev); }
 extern "C" void terra_b200_set_env_lit(HTerraScene h, int on) { tb_device_set_env_lit(committed(h, "terra_b200_set_env_lit")->dev, on); }
+extern "C" void terra_b200_distribution_2d_sample(HTerraScene h, const float* f, size_t nx, size_t ny, size_t n,
+                                                  const float* e1, const float* e2, float* out4) {
+    TbScene* s = committed(h, "terra_b200_distribution_2d_sample");
+    if (nx == 0 || ny == 0) tb_fatal("terra_b200_distribution_2d_sample: empty function");
+    std::lock_guard<std::mutex> guard(s->lock);
+    tb_device_distribution_2d_sample(s->dev, f, nx, ny, n, e1, e2, out4);
+}
 extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;
@@ -627,6 +689,8 @@ extern "C" int terra_b200_build_host_bvh(HTerraScene h, int mode, float* flat_no
     return (int)s->nodes.size();
 }
 
+extern "C" void* terra_b200_host_alloc(size_t bytes) { return tb_host_alloc_pinned(bytes ? bytes : 1); }
+extern "C" void terra_b200_host_free(void* p) { if (p) tb_host_free_pinned(p); }
 extern "C" void terra_b200_trace_rays(HTerraScene h, size_t n, const float* origins, const float* directions, TerraB200Hit* hits_out) {
     TbScene* s = committed(h, "terra_b200_trace_rays");
     std::lock_guard<std::mutex> guard(s->lock);

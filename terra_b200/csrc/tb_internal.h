@@ -62,6 +62,15 @@ struct TbDevLight {
     float    area;
 };
 
+struct TbDevDist2D {          // TerraDistributon2D (src/TerraPrivate.h:85-96) as flat device arrays
+    const float* f;              // ny rows of nx: the function
+    const float* cdf;            // ny rows of nx: conditional cdfs
+    const float* row_integral;   // ny: marginal function (row totals)
+    const float* marginal_cdf;   // ny
+    float        integral;
+    int          nx, ny;
+};
+
 struct TbDevScene {
     const float4*        nodes;
     const float4*        tris;
@@ -77,6 +86,8 @@ struct TbDevScene {
     int32_t              integrator, bounces, tonemap, preset_mask;
     float                jitter, exposure, gamma, inv_gamma;
     int32_t              env_lit;          // extension mode: a miss adds throughput * environment (Terra.c:1056 restored)
+    int32_t              env_nee;          // env_lit mode 2: the direct integrators sample the lat-long environment explicitly (tb_distribution.cuh)
+    TbDevDist2D          env_dist;
 };
 
 // ---------------------------------------------------------------- host scene
@@ -133,6 +144,8 @@ void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 void      tb_device_set_env_lit(TbDevice* dev, int on);
+void      tb_device_distribution_2d_sample(TbDevice* dev, const float* f, size_t nx, size_t ny, size_t n,
+                                           const float* e1, const float* e2, float* out4);
 int       tb_cuda_device_count(void);
 void*     tb_host_alloc_pinned(size_t bytes);
 void      tb_host_free_pinned(void* p);

@@ -78,6 +78,7 @@ enum {  // dimensions per bounce (16 reserved)
     TB_DIM_BSDF0 = 0, TB_DIM_BSDF1 = 1, TB_DIM_BSDF2 = 2, TB_DIM_RR = 3,
     TB_DIM_LIGHT_PICK = 4, TB_DIM_TRI_PICK = 5, TB_DIM_LIGHT_U = 6, TB_DIM_LIGHT_V = 7,
     TB_DIM_MIS0 = 8, TB_DIM_MIS1 = 9, TB_DIM_MIS2 = 10,
+    TB_DIM_ENV0 = 11, TB_DIM_ENV1 = 12,        // explicit environment sample (env_lit mode 2)
     TB_DIMS_PER_BOUNCE = 16
 };
 
@@ -89,7 +90,7 @@ struct TbWave {                // wavefront buffers, `capacity` path slots
     float4*  thr;              // throughput
     float4*  lo;               // radiance gathered so far by this path
     float4*  hit;              // t, rank (int bits), u, v
-    float4*  aux_o;            // light / MIS visibility rays (2 per slot)
+    float4*  aux_o;            // light / MIS visibility rays (2 per slot: [2*slot + k]) + explicit environment rays ([2*capacity + slot])
     float4*  aux_d;
     float4*  aux_hit;
     int*     queue[2];         // live path slots, ping-pong
@@ -117,6 +118,8 @@ struct TbDevice {
     float*         d_light_area;
     uint32_t*      d_light_rank;
     std::vector<void*> tex_pixels;
+    std::vector<TbDevTexture> h_texs;    // host copy of the texture table (dims for the environment importance map)
+    float       *d_env_f, *d_env_cdf, *d_env_rows, *d_env_marg;   // TbDevDist2D storage of sc.env_dist
     int          stack_bound;
     TbWave       wave;
     // per-call staging for terra_render
@@ -129,6 +132,12 @@ struct TbDevice {
     size_t       io_capacity;
     float4      *d_io_o, *d_io_d;
     TerraB200Hit* d_io_hit;
+    // terra_b200_trace_rays pipeline: copy-in / compute / copy-out streams, two slots of raw xyz input and hits
+    cudaStream_t st_in, st_out;
+    size_t       pipe_capacity;
+    float       *d_pipe_o3[2], *d_pipe_d3[2];
+    TerraB200Hit* d_pipe_hit[2];
+    cudaEvent_t  ev_in[2], ev_pack[2], ev_trace[2], ev_out[2];
     // stats
     TerraB200Stats stats;
     std::vector<TbEventPair> ev_pool;
@@ -187,13 +196,13 @@ static void tb_wave_reserve(TbWave* w, size_t capacity) {
     w->thr = tb_alloc<float4>(capacity);
     w->lo = tb_alloc<float4>(capacity);
     w->hit = tb_alloc<float4>(capacity);
-    w->aux_o = tb_alloc<float4>(capacity * 2);
-    w->aux_d = tb_alloc<float4>(capacity * 2);
-    w->aux_hit = tb_alloc<float4>(capacity * 2);
+    w->aux_o = tb_alloc<float4>(capacity * 3);
+    w->aux_d = tb_alloc<float4>(capacity * 3);
+    w->aux_hit = tb_alloc<float4>(capacity * 3);
     w->queue[0] = tb_alloc<int>(capacity);
     w->queue[1] = tb_alloc<int>(capacity);
     w->matq = tb_alloc<int>(capacity * TB_PRESET_COUNT);
-    w->auxq = tb_alloc<int>(capacity * 2);
+    w->auxq = tb_alloc<int>(capacity * 3);
 }
 
 extern "C" TbDevice* tb_device_create(int device_index) {
@@ -221,6 +230,9 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaMemset(d->wave.counters, 0, 16 * sizeof(int)));
     d->fb_capacity = 0; d->d_results = NULL; d->d_pixels = NULL; d->d_acc = NULL; d->acc_capacity = 0;
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
+    d->st_in = d->st_out = NULL; d->pipe_capacity = 0;
+    d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
+    for (int k = 0; k < 2; ++k) { d->d_pipe_o3[k] = d->d_pipe_d3[k] = NULL; d->d_pipe_hit[k] = NULL; }
     memset(&d->stats, 0, sizeof d->stats);
     d->ev_used = 0;
     d->counting = 0;
@@ -254,6 +266,9 @@ static void tb_scene_free(TbDevice* d) {
     tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
     for (void* p : d->tex_pixels) tb_free(p);
     d->tex_pixels.clear();
+    tb_free(d->d_env_f); tb_free(d->d_env_cdf); tb_free(d->d_env_rows); tb_free(d->d_env_marg);
+    d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
+    d->sc.env_nee = 0;
     d->d_nodes = d->d_tris = d->d_props = NULL;
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
 }
@@ -266,6 +281,11 @@ extern "C" void tb_device_destroy(TbDevice* d) {
     tb_free(d->wave.counters);
     tb_free(d->d_results); tb_free(d->d_pixels); tb_free(d->d_acc);
     tb_free(d->d_io_o); tb_free(d->d_io_d); tb_free(d->d_io_hit);
+    for (int k = 0; k < 2; ++k) { tb_free(d->d_pipe_o3[k]); tb_free(d->d_pipe_d3[k]); tb_free(d->d_pipe_hit[k]); }
+    if (d->st_in) {
+        for (int k = 0; k < 2; ++k) { cudaEventDestroy(d->ev_in[k]); cudaEventDestroy(d->ev_pack[k]); cudaEventDestroy(d->ev_trace[k]); cudaEventDestroy(d->ev_out[k]); }
+        cudaStreamDestroy(d->st_in); cudaStreamDestroy(d->st_out);
+    }
     for (TbEventPair& e : d->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     cudaEventDestroy(d->ev_call_a);
     cudaEventDestroy(d->ev_call_b);
@@ -315,6 +335,7 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
         texs[i].pad_ = 0;
     }
     d->d_texs = tb_upload(texs.data(), texs.size(), d);
+    d->h_texs = texs;
     d->d_lights = tb_upload(f->lights, f->n_lights, d);
     d->d_light_area = tb_upload(f->light_tri_area, f->n_light_tris, d);
     d->d_light_rank = tb_upload(f->light_tri_rank, f->n_light_tris, d);
@@ -643,6 +664,7 @@ struct TbShadeArgs {
     int*  auxq;                // visibility rays to trace between the two stages
     int*  aux_count;
     int   bounce;
+    int   env_base;            // aux id of slot s's environment visibility ray = env_base + s
 };
 
 // Warp-aggregated append; every lane of the warp must call it (full mask).
@@ -758,6 +780,8 @@ __device__ __forceinline__ V3 tb_integrate_debug(const TbDevScene& sc, int integ
     return vpoint(Lo, thr);
 }
 
+#include "tb_distribution.cuh"
+
 template <int PRESET, int STAGE>
 __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade(TbShadeArgs a) {
     const int count = *a.q_count;
@@ -767,9 +791,9 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade
     for (int it = 0; it < rounds; ++it) {
         const int i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         const bool valid = i < count;
-        bool alive = false, want_aux0 = false, want_aux1 = false;
+        bool alive = false, want_aux0 = false, want_aux1 = false, want_aux2 = false;
         int slot = 0;
-        V3 next_o = v3s(0.f), next_d = v3s(0.f), aux0_d = v3s(0.f), aux1_d = v3s(0.f), aux_o = v3s(0.f);
+        V3 next_o = v3s(0.f), next_d = v3s(0.f), aux0_d = v3s(0.f), aux1_d = v3s(0.f), aux2_d = v3s(0.f), aux_o = v3s(0.f);
         float4 o4 = make_float4(0, 0, 0, 0), d4 = o4;
         if (valid) {
             slot = a.q[i];
@@ -789,18 +813,26 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade
             const bool mis = integ == kTerraIntegratorDirectMis || dbg_mis;
             const bool debug = integ > kTerraIntegratorDirectMis;
 
+            const bool env_nee = sc.env_nee && direct && !dbg_mis;                    // extension: explicit environment samples
             if (STAGE == 0) {
                 // ---- emit the visibility rays of terra_integrate_direct / _direct_mis
-                if (direct && sc.n_lights > 0) {
+                if (direct && (sc.n_lights > 0 || env_nee)) {
                     aux_o = tb_surface_ray_origin(s, point);
                     if (mis) {
                         aux1_d = tb_bsdf_sample(PRESET, s, tb_randf_libc(key, dim0 + TB_DIM_MIS0), tb_randf_libc(key, dim0 + TB_DIM_MIS1),
                                                 tb_randf_libc(key, dim0 + TB_DIM_MIS2), wo);
                         want_aux1 = true;
                     }
-                    const TbLightSample ls = tb_sample_light(sc, key, dim0);
-                    aux0_d = vnorm(vsub(ls.pos, point));
-                    want_aux0 = true;
+                    if (sc.n_lights > 0) {
+                        const TbLightSample ls = tb_sample_light(sc, key, dim0);
+                        aux0_d = vnorm(vsub(ls.pos, point));
+                        want_aux0 = true;
+                    }
+                    if (env_nee) {
+                        float pdf_e;
+                        want_aux2 = tb_env_sample(sc.env_dist, tb_randf_libc(key, dim0 + TB_DIM_ENV0), tb_randf_libc(key, dim0 + TB_DIM_ENV1), &aux2_d, &pdf_e)
+                                    && vdot(aux2_d, s.n) > 0.f;
+                    }
                 }
             } else {
                 // ---- terra_integrate (Terra.c:1099-1138)
@@ -813,10 +845,11 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade
                     if (vdot(wo, s.n) > 0) Lo = vpoint(s.emissive, thr);
                 } else {
                     if (a.bounce == 0 && vdot(wo, s.n) > 0) Lo = vadd(Lo, s.emissive);
+                    V3 bsdf_sample = v3s(0.f);
+                    if (mis && (sc.n_lights > 0 || env_nee))
+                        bsdf_sample = tb_bsdf_sample(PRESET, s, tb_randf_libc(key, dim0 + TB_DIM_MIS0), tb_randf_libc(key, dim0 + TB_DIM_MIS1),
+                                                     tb_randf_libc(key, dim0 + TB_DIM_MIS2), wo);
                     if (sc.n_lights > 0) {
-                        V3 bsdf_sample = v3s(0.f);
-                        if (mis) bsdf_sample = tb_bsdf_sample(PRESET, s, tb_randf_libc(key, dim0 + TB_DIM_MIS0), tb_randf_libc(key, dim0 + TB_DIM_MIS1),
-                                                              tb_randf_libc(key, dim0 + TB_DIM_MIS2), wo);
                         const TbLightSample ls = tb_sample_light(sc, key, dim0);
                         const float light_pick_pdf = 1.f / (float)sc.lights_triangles_count;
                         const V3 p_to_light = vsub(ls.pos, point);
@@ -875,6 +908,36 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade
                             }
                         }
                     }
+                    if (env_nee) {
+                        // ---- explicit environment sample (no reference counterpart; same estimator shapes as the
+                        //      area-light code above: f * L * cos / pdf, power-heuristic weights under MIS)
+                        V3 wi_e; float pdf_e;
+                        if (tb_env_sample(sc.env_dist, tb_randf_libc(key, dim0 + TB_DIM_ENV0), tb_randf_libc(key, dim0 + TB_DIM_ENV1), &wi_e, &pdf_e)
+                            && vdot(wi_e, s.n) > 0.f && a.aux_hit[(size_t)a.env_base + slot].x < 0.f) {
+                            V2 uv; uv.x = wi_e.x; uv.y = wi_e.y;
+                            const V3 env = tb_attr_eval(sc.env, sc.textures, uv, wi_e);
+                            const V3 f = tb_bsdf_eval(PRESET, s, wi_e, wo);
+                            float weight = 1.f;
+                            if (mis) {
+                                const float bsdf_pdf = tb_bsdf_pdf(PRESET, s, wi_e, wo);
+                                weight = (pdf_e * pdf_e) / (pdf_e * pdf_e + bsdf_pdf * bsdf_pdf);
+                            }
+                            Lo = vadd(Lo, vmul(vpoint(env, f), vdot(wi_e, s.n) * weight / pdf_e));
+                        }
+                        if (mis && a.aux_hit[(size_t)slot * 2 + 1].x < 0.f) {       // the BSDF sample left the scene
+                            const V3 wi2 = bsdf_sample;
+                            const float bsdf_pdf = tb_bsdf_pdf(PRESET, s, wi2, wo);
+                            if (bsdf_pdf != 0) {
+                                // the environment technique cannot produce a direction below the surface: weight 1 there
+                                const float pe = vdot(wi2, s.n) > 0.f ? tb_env_pdf(sc.env_dist, wi2) : 0.f;
+                                const float weight = (bsdf_pdf * bsdf_pdf) / (pe * pe + bsdf_pdf * bsdf_pdf);
+                                V2 uv; uv.x = wi2.x; uv.y = wi2.y;
+                                const V3 env = tb_attr_eval(sc.env, sc.textures, uv, wi2);
+                                const V3 f = tb_bsdf_eval(PRESET, s, wi2, wo);
+                                Lo = vadd(Lo, vmul(vpoint(env, f), vdot(wi2, s.n) * weight / bsdf_pdf));
+                            }
+                        }
+                    }
                     Lo = vpoint(Lo, thr);
                 }
                 if (Lo.x != 0.f || Lo.y != 0.f || Lo.z != 0.f) {
@@ -916,6 +979,14 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade
                 a.aux_o[(size_t)slot * 2 + 1] = make_float4(aux_o.x, aux_o.y, aux_o.z, 0.f);
                 a.aux_d[(size_t)slot * 2 + 1] = make_float4(aux1_d.x, aux1_d.y, aux1_d.z, 0.f);
                 a.auxq[i1] = slot * 2 + 1;
+            }
+            if (sc.env_nee) {                      // warp-uniform (scene constant)
+                const int i2 = tb_append(a.aux_count, want_aux2);
+                if (want_aux2) {
+                    a.aux_o[(size_t)a.env_base + slot] = make_float4(aux_o.x, aux_o.y, aux_o.z, 0.f);
+                    a.aux_d[(size_t)a.env_base + slot] = make_float4(aux2_d.x, aux2_d.y, aux2_d.z, 0.f);
+                    a.auxq[i2] = a.env_base + slot;
+                }
             }
         } else {
             const int at = tb_append(a.next_count, alive);
@@ -1217,6 +1288,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
     const TbDevScene& sc = d->sc;
     const bool direct = sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis ||
                         sc.integrator == kTerraIntegratorDebugMisWeights;
+    const bool env_nee = sc.env_nee && (sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis);
     if (sc.integrator < 0 || sc.integrator > kTerraIntegratorDebugMisWeights) {
         terra_log("terra_b200: unknown integrator %d\n", sc.integrator);      // assert(false), Terra.c:1134
         abort();
@@ -1255,7 +1327,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 ta.emit_prim = 0;
                 tb_launch_trace(d, st, ta, bounce == 0);
                 d->stats.kernel_launches += 1;
-                if (sc.env_lit && last_bounce == sc.bounces) {
+                if (sc.env_lit && last_bounce == sc.bounces && (!env_nee || bounce == 0)) {
                     k_miss<<<d->sm_count * 4, 256, 0, st>>>(sc, wv.queue[cur], wv.counters + 1, wv.ray_d, wv.hit, wv.thr, wv.lo);
                     d->stats.kernel_launches += 1;
                 }
@@ -1266,7 +1338,8 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 sa.next_q = wv.queue[cur ^ 1]; sa.next_count = wv.counters + 2;
                 sa.auxq = wv.auxq; sa.aux_count = wv.counters + 3;
                 sa.bounce = bounce;
-                if (direct && sc.n_lights > 0) {
+                sa.env_base = (int)(2 * wv.capacity);
+                if (direct && (sc.n_lights > 0 || env_nee)) {
                     for (int p = 0; p < TB_PRESET_COUNT; ++p) {
                         if (!(sc.preset_mask & (1 << p))) continue;
                         sa.q = wv.matq + (size_t)p * wv.capacity; sa.q_count = wv.counters + 4 + p;
@@ -1419,29 +1492,67 @@ extern "C" void tb_device_trace_resident(TbDevice* d, size_t n, const void* d_o,
     tb_finish_call(d, st, false);
 }
 
+// Host-buffer ray batches (terra_b200_trace_rays). The batch moves through three streams in chunks:
+//   st_in:   H2D of chunk k+1's origins / directions (12 B + 12 B per ray, as the caller holds them)
+//   stream:  pack to float4 + closest hit of chunk k
+//   st_out:  D2H of chunk k-1's hits (16 B per ray)
+// with two slots of staging, so that a batch costs max(copy in, trace, copy out) instead of their sum: PCIe
+// is full duplex and the copy engines run beside the SMs. The overlap needs page-locked caller buffers
+// (terra_b200_host_alloc); with pageable memory the driver stages every copy and the calls serialise, the
+// results are the same. TERRA_B200_IO_CHUNK sets the chunk (rays).
+static void tb_pipe_reserve(TbDevice* d, size_t chunk) {
+    if (!d->st_in) {
+        TB_CUDA(cudaStreamCreateWithFlags(&d->st_in, cudaStreamNonBlocking));
+        TB_CUDA(cudaStreamCreateWithFlags(&d->st_out, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_in[k], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_pack[k], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_trace[k], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_out[k], cudaEventDisableTiming));
+        }
+    }
+    if (chunk <= d->pipe_capacity) return;
+    for (int k = 0; k < 2; ++k) {
+        tb_free(d->d_pipe_o3[k]); tb_free(d->d_pipe_d3[k]); tb_free(d->d_pipe_hit[k]);
+        d->d_pipe_o3[k] = tb_alloc<float>(chunk * 3);
+        d->d_pipe_d3[k] = tb_alloc<float>(chunk * 3);
+        d->d_pipe_hit[k] = tb_alloc<TerraB200Hit>(chunk);
+    }
+    d->pipe_capacity = chunk;
+}
+
 extern "C" void tb_device_trace_host(TbDevice* d, size_t n, const float* origins, const float* dirs, TerraB200Hit* out) {
     TB_CUDA(cudaSetDevice(d->index));
+    if (n == 0) return;
     cudaStream_t st = d->stream;
-    const size_t chunk = (size_t)1 << 24;
-    tb_io_reserve(d, n < chunk ? n : chunk);
-    // the xyz staging reuses the tail of the hit buffer: 16 B/ray >= 12 B/ray
-    float* d_o3 = NULL; float* d_d3 = NULL;
-    TB_CUDA(cudaMalloc((void**)&d_o3, (n < chunk ? n : chunk) * 12));
-    TB_CUDA(cudaMalloc((void**)&d_d3, (n < chunk ? n : chunk) * 12));
-    for (size_t at = 0; at < n; at += chunk) {
+    size_t chunk = (size_t)1 << 21;
+    if (const char* e = getenv("TERRA_B200_IO_CHUNK")) { const long long v = atoll(e); if (v >= 1024) chunk = (size_t)v; }
+    if (chunk > n) chunk = n;
+    tb_io_reserve(d, chunk);
+    tb_pipe_reserve(d, chunk);
+    size_t k = 0;
+    for (size_t at = 0; at < n; at += chunk, ++k) {
         const size_t m = n - at < chunk ? n - at : chunk;
-        TB_CUDA(cudaMemcpyAsync(d_o3, origins + 3 * at, m * 12, cudaMemcpyHostToDevice, st));
-        TB_CUDA(cudaMemcpyAsync(d_d3, dirs + 3 * at, m * 12, cudaMemcpyHostToDevice, st));
-        k_pack_rays<<<d->sm_count * 8, 256, 0, st>>>(m, d_o3, d_d3, d->d_io_o, d->d_io_d);
+        const int slot = (int)(k & 1);
+        if (k >= 2) TB_CUDA(cudaStreamWaitEvent(d->st_in, d->ev_pack[slot], 0));       // chunk k-2 has been packed: its raw input is free
+        TB_CUDA(cudaMemcpyAsync(d->d_pipe_o3[slot], origins + 3 * at, m * 12, cudaMemcpyHostToDevice, d->st_in));
+        TB_CUDA(cudaMemcpyAsync(d->d_pipe_d3[slot], dirs + 3 * at, m * 12, cudaMemcpyHostToDevice, d->st_in));
+        TB_CUDA(cudaEventRecord(d->ev_in[slot], d->st_in));
+        TB_CUDA(cudaStreamWaitEvent(st, d->ev_in[slot], 0));
+        k_pack_rays<<<d->sm_count * 8, 256, 0, st>>>(m, d->d_pipe_o3[slot], d->d_pipe_d3[slot], d->d_io_o, d->d_io_d);
+        TB_CUDA(cudaEventRecord(d->ev_pack[slot], st));
         d->stats.kernel_launches += 1;
-        tb_trace_generic(d, st, m, d->d_io_o, d->d_io_d, (float4*)d->d_io_hit);
-        TB_CUDA(cudaMemcpyAsync(out + at, d->d_io_hit, m * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, st));
+        if (k >= 2) TB_CUDA(cudaStreamWaitEvent(st, d->ev_out[slot], 0));              // chunk k-2's hits have left the slot
+        tb_trace_generic(d, st, m, d->d_io_o, d->d_io_d, (float4*)d->d_pipe_hit[slot]);
+        TB_CUDA(cudaEventRecord(d->ev_trace[slot], st));
+        TB_CUDA(cudaStreamWaitEvent(d->st_out, d->ev_trace[slot], 0));
+        TB_CUDA(cudaMemcpyAsync(out + at, d->d_pipe_hit[slot], m * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, d->st_out));
+        TB_CUDA(cudaEventRecord(d->ev_out[slot], d->st_out));
         d->stats.h2d_bytes += m * 24;
         d->stats.d2h_bytes += m * sizeof(TerraB200Hit);
     }
+    TB_CUDA(cudaStreamSynchronize(d->st_out));
     tb_finish_call(d, st, false);
-    TB_CUDA(cudaFree(d_o3));
-    TB_CUDA(cudaFree(d_d3));
 }
 
 extern "C" void tb_device_primary_hits(TbDevice* d, const TbCameraFrame* cam, size_t w, size_t h, TerraB200Hit* out) {
@@ -1544,7 +1655,69 @@ extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
 }
 
 extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; }
-extern "C" void tb_device_set_env_lit(TbDevice* d, int on) { d->sc.env_lit = on ? 1 : 0; }
+// Builds TbDevDist2D over `f` (ny rows of nx, device) into freshly allocated device arrays.
+static void tb_dist2d_build(TbDevice* d, cudaStream_t st, const float* d_f, int nx, int ny, float** cdf_out, float** rows_out,
+                            float** marg_out, TbDevDist2D* out) {
+    float* cdf = tb_alloc<float>((size_t)nx * ny);
+    float* rows = tb_alloc<float>((size_t)ny);
+    float* marg = tb_alloc<float>((size_t)ny);
+    float* total = tb_alloc<float>(1);
+    k_dist_rows<<<(ny + 127) / 128, 128, 0, st>>>(d_f, nx, ny, cdf, rows);            // conditionals, Terra.c:812-814
+    k_dist_rows<<<1, 128, 0, st>>>(rows, ny, 1, marg, total);                          // marginal over the row totals, :816-832
+    d->stats.kernel_launches += 2;
+    float h_total = 0.f;
+    TB_CUDA(cudaMemcpyAsync(&h_total, total, sizeof(float), cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    tb_free(total);
+    out->f = d_f; out->cdf = cdf; out->row_integral = rows; out->marginal_cdf = marg;
+    out->integral = h_total; out->nx = nx; out->ny = ny;
+    *cdf_out = cdf; *rows_out = rows; *marg_out = marg;
+}
+
+// on = 1: a miss adds throughput * environment at every bounce (Terra.c:1056 restored). on = 2: the same
+// radiance, but the direct integrators sample a lat-long environment explicitly through the reference's
+// distributions (tb_distribution.cuh) and misses count at the camera ray only; falls back to mode 1 when
+// the environment is not a lat-long texture.
+extern "C" void tb_device_set_env_lit(TbDevice* d, int on) {
+    TB_CUDA(cudaSetDevice(d->index));
+    d->sc.env_lit = on ? 1 : 0;
+    d->sc.env_nee = 0;
+    tb_free(d->d_env_f); tb_free(d->d_env_cdf); tb_free(d->d_env_rows); tb_free(d->d_env_marg);
+    d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
+    if (on != 2 || (d->sc.env.kind_tex & 3) != TB_ATTR_LATLONG) return;
+    const TbDevTexture t = d->h_texs[(size_t)(d->sc.env.kind_tex >> 2)];
+    const int nx = t.width, ny = t.height;
+    std::vector<float> w((size_t)ny);
+    for (int y = 0; y < ny; ++y) w[(size_t)y] = sinf(TB_PI * (((float)y + 0.5f) / (float)ny));
+    float* d_w = tb_upload(w.data(), w.size(), d);
+    d->d_env_f = tb_alloc<float>((size_t)nx * ny);
+    k_env_importance<<<d->sm_count * 4, 256, 0, d->stream>>>(t, d_w, d->d_env_f);
+    d->stats.kernel_launches += 1;
+    tb_dist2d_build(d, d->stream, d->d_env_f, nx, ny, &d->d_env_cdf, &d->d_env_rows, &d->d_env_marg, &d->sc.env_dist);
+    tb_free(d_w);
+    d->sc.env_nee = d->sc.env_dist.integral > 0.f ? 1 : 0;
+}
+
+// terra_distribution_2d_init + n x terra_distribution_2d_sample on the device (known-answer entry point):
+// out[4*i] = {s1 (row axis), s2 (column axis), pdf, 0}.
+extern "C" void tb_device_distribution_2d_sample(TbDevice* d, const float* f, size_t nx, size_t ny, size_t n,
+                                                 const float* e1, const float* e2, float* out4) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    float* d_f = tb_upload(f, nx * ny, d);
+    float *cdf, *rows, *marg;
+    TbDevDist2D dist;
+    tb_dist2d_build(d, st, d_f, (int)nx, (int)ny, &cdf, &rows, &marg, &dist);
+    float* d_e1 = tb_upload(e1, n, d);
+    float* d_e2 = tb_upload(e2, n, d);
+    float4* d_out = tb_alloc<float4>(n);
+    k_dist_sample<<<d->sm_count * 4, 256, 0, st>>>(dist, n, d_e1, d_e2, d_out);
+    d->stats.kernel_launches += 1;
+    TB_CUDA(cudaMemcpyAsync(out4, d_out, n * sizeof(float4), cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    TB_CUDA(cudaGetLastError());
+    tb_free(d_f); tb_free(cdf); tb_free(rows); tb_free(marg); tb_free(d_e1); tb_free(d_e2); tb_free(d_out);
+}
 
 extern "C" void tb_device_reset_stats(TbDevice* d) {
     TB_CUDA(cudaSetDevice(d->index));

@@ -152,7 +152,38 @@ def main():
         out[f"{tname}_latlong"] = r
     out["tex8"], out["texf"] = tex8, texf
     np.savez_compressed(OUT / "textures.npz", **out)
+    # ---- discrete distributions (Terra.c:760-846), the reference's exported functions called directly
+    np.savez_compressed(OUT / "distribution.npz", **distribution_fixture(api, ref))
     print("golden fixtures written to", OUT)
+
+
+def distribution_cases():
+    """name -> (f (ny,nx), e1, e2): random maps with zero rows / columns / one huge bucket, edge random numbers."""
+    rng = np.random.default_rng(41)
+    one = np.nextafter(np.float32(1), np.float32(0))
+    out = {}
+    for name, (ny, nx) in (("d1x1", (1, 1)), ("d3x5", (3, 5)), ("d16x33", (16, 33)), ("d64x128", (64, 128))):
+        f = (rng.random((ny, nx)).astype(np.float32) ** 4).astype(np.float32)
+        if ny > 3:
+            f[2] = 0
+            f[2, 0] = 1e-6
+            f[:, 3] = 0
+            f[5, 7] = 1000.0
+        n = 1500
+        e1, e2 = rng.random(n).astype(np.float32), rng.random(n).astype(np.float32)
+        e1[:4] = [0, one, 0.5, 0.25]
+        e2[:4] = [0, one, 0.5, 0.25]
+        out[name] = (f, e1, e2)
+    return out
+
+
+def distribution_fixture(api, ref):
+    out = {}
+    for name, (f, e1, e2) in distribution_cases().items():
+        got, marg, ccdf = api.reference_distribution_2d_sample(ref, f, e1, e2)
+        out[f"{name}_f"], out[f"{name}_e1"], out[f"{name}_e2"] = f, e1, e2
+        out[f"{name}_samples"], out[f"{name}_marginal_cdf"], out[f"{name}_cdf"] = got, marg, ccdf
+    return out
 
 
 if __name__ == "__main__":

@@ -79,6 +79,33 @@ def test_empty_and_ragged_ray_batches(api, scenes, gpu):
     s.destroy()
 
 
+def test_pipelined_host_batches_equal_one_shot(api, scenes, gpu, monkeypatch):
+    """terra_b200_trace_rays moves a host batch through copy-in | trace | copy-out streams in chunks, two
+    staging slots: any chunking, page-locked or pageable buffers, gives the bytes of the one-chunk call
+    (ragged last chunk, more chunks than slots, a batch smaller than a chunk)."""
+    s, cam, wh = cases.build(scenes, gpu, "field")
+    n = 50_001
+    o, d = cases.rays_for(s, api, scenes, n)
+    monkeypatch.setenv("TERRA_B200_IO_CHUNK", str(1 << 20))
+    want = s.trace_rays(o, d)
+    po, pd = api.PinnedArray(gpu, (n, 3), np.float32), api.PinnedArray(gpu, (n, 3), np.float32)
+    ph = api.PinnedArray(gpu, n, api.HIT_DTYPE)
+    po.array[:] = o
+    pd.array[:] = d
+    for chunk in (1024, 4096, 16384, 50_001, 50_002):
+        monkeypatch.setenv("TERRA_B200_IO_CHUNK", str(chunk))
+        ph.array.view(np.uint8)[:] = 0xff
+        got = s.trace_rays(po.array, pd.array, out=ph.array)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), chunk
+        assert np.array_equal(s.trace_rays(o, d).view(np.uint32), want.view(np.uint32)), chunk
+        assert np.array_equal(s.trace_rays(po.array[:777], pd.array[:777]).view(np.uint32), want[:777].view(np.uint32))
+    st = s.stats()
+    assert st.h2d_bytes > 0 and st.d2h_bytes > 0
+    for a in (po, pd, ph):
+        a.free()
+    s.destroy()
+
+
 def test_medium_scene_vs_oracle(api, scenes, gpu, oracle):
     """100k-triangle sphere field (config C2's geometry) and a 200k-triangle terrain: 200k incoherent
     rays against the oracle's canonical walk over the same tree, plus primary hits at 320x180."""
