@@ -83,6 +83,8 @@ enum {  // dimensions per bounce (16 reserved)
 };
 
 // ------------------------------------------------------------------------------------ device state
+#define TB_SORT_BINS 32          // direction bins of the optional queue reordering (k_bin_count / k_bin_scatter)
+
 struct TbWave {                // wavefront buffers, `capacity` path slots
     size_t   capacity;
     float4*  ray_o;            // xyz origin (before the 0.001*dir raycast offset)
@@ -97,6 +99,7 @@ struct TbWave {                // wavefront buffers, `capacity` path slots
     int*     matq;             // TB_PRESET_COUNT x capacity: slots binned by preset after the trace
     int*     auxq;             // aux ray ids to trace
     int*     counters;         // [0] fetch cursor, [1] queue count cur, [2] next, [3] aux count, [4..7] matq counts
+    int*     bins;             // 2 x TB_SORT_BINS: counts, then cursors, of the direction binning of the next queue
 };
 
 struct TbEventPair { cudaEvent_t a, b; };
@@ -152,6 +155,7 @@ struct TbDevice {
     int          warp_samples; // at most this many samples of one pixel share a warp (TERRA_B200_WARP_SAMPLES, default 32)
     int          tile_pixels;  // 1: waves walk the region in 8x4 pixel tiles (TERRA_B200_TILE=0 turns it off)
     int          tri_min, refetch_below;
+    int          sort_rays, sort_bounces;   // TERRA_B200_SORT (0 off, 1 octant, 2 octant + dominant axis) for the first TERRA_B200_SORT_BOUNCES bounces
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -182,7 +186,7 @@ extern "C" int tb_cuda_device_count(void) {
 static void tb_wave_free(TbWave* w) {
     tb_free(w->ray_o); tb_free(w->ray_d); tb_free(w->thr); tb_free(w->lo); tb_free(w->hit);
     tb_free(w->aux_o); tb_free(w->aux_d); tb_free(w->aux_hit);
-    tb_free(w->queue[0]); tb_free(w->queue[1]); tb_free(w->matq); tb_free(w->auxq);
+    tb_free(w->queue[0]); tb_free(w->queue[1]); tb_free(w->matq); tb_free(w->auxq); tb_free(w->bins);
     int* counters = w->counters;                 // lives as long as the device (holds the ray statistics)
     memset(w, 0, sizeof *w);
     w->counters = counters;
@@ -203,6 +207,7 @@ static void tb_wave_reserve(TbWave* w, size_t capacity) {
     w->queue[1] = tb_alloc<int>(capacity);
     w->matq = tb_alloc<int>(capacity * TB_PRESET_COUNT);
     w->auxq = tb_alloc<int>(capacity * 3);
+    w->bins = tb_alloc<int>(2 * TB_SORT_BINS);
 }
 
 extern "C" TbDevice* tb_device_create(int device_index) {
@@ -244,6 +249,8 @@ extern "C" TbDevice* tb_device_create(int device_index) {
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
         const char* ws = getenv("TERRA_B200_WARP_SAMPLES"); d->warp_samples = ws ? atoi(ws) : 32;
+        const char* so = getenv("TERRA_B200_SORT"); d->sort_rays = so ? atoi(so) : 0;
+        const char* sb = getenv("TERRA_B200_SORT_BOUNCES"); d->sort_bounces = sb ? atoi(sb) : 2;
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
         for (int k = 0; e && k < 11; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
         const char* vo = getenv("TERRA_B200_V4_OPT"); d->v4_opt = vo ? (atoi(vo) & 3) : 3;       // measured on B200: 256-bit loads +1.7 %, single pop +10 % (C3 1M)
@@ -1147,6 +1154,60 @@ __global__ void k_counters(int* c, int mode, int value) {
     }
 }
 
+// ---- direction binning of the next bounce's queue (TERRA_B200_SORT=1|2; A/B option, off by default)
+// The rays a shade pass emits sit in the queue in slot order: a warp of the next trace launch gets 32 rays
+// leaving (nearly) one point in 32 unrelated directions. Reordering the queue ids — the rays stay where they
+// are — so that a warp's rays share their direction octant (mode 1) or octant and dominant axis (mode 2)
+// makes the lanes agree on near / far children. Two passes over the ids: histogram, then scatter at
+// warp-aggregated cursors. Results do not depend on the order of the queue.
+__device__ __forceinline__ int tb_dir_bin(float4 d, int mode) {
+    int key = (d.x < 0.f ? 1 : 0) | (d.y < 0.f ? 2 : 0) | (d.z < 0.f ? 4 : 0);
+    if (mode >= 2) {
+        const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+        const int major = ax >= ay ? (ax >= az ? 0 : 2) : (ay >= az ? 1 : 2);
+        key |= major << 3;
+    }
+    return key;
+}
+__global__ void __launch_bounds__(256) k_bin_count(const int* __restrict__ q, const int* __restrict__ q_count,
+                                                   const float4* __restrict__ ray_d, int mode, int* __restrict__ bins) {
+    __shared__ int s_bins[TB_SORT_BINS];
+    if (threadIdx.x < TB_SORT_BINS) s_bins[threadIdx.x] = 0;
+    __syncthreads();
+    const int count = *q_count;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+        atomicAdd(&s_bins[tb_dir_bin(ray_d[q[i]], mode)], 1);
+    __syncthreads();
+    if (threadIdx.x < TB_SORT_BINS && s_bins[threadIdx.x]) atomicAdd(&bins[threadIdx.x], s_bins[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256) k_bin_scatter(const int* __restrict__ q, const int* __restrict__ q_count,
+                                                     const float4* __restrict__ ray_d, int mode, int* __restrict__ bins,
+                                                     int* __restrict__ out) {
+    __shared__ int s_base[TB_SORT_BINS];
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int b = 0; b < TB_SORT_BINS; ++b) { s_base[b] = acc; acc += bins[b]; }
+    }
+    __syncthreads();
+    int* cursors = bins + TB_SORT_BINS;
+    const int count = *q_count;
+    const int stride = gridDim.x * blockDim.x;
+    const int rounds = (count + stride - 1) / stride;
+    const unsigned lane = threadIdx.x & 31u;
+    for (int it = 0; it < rounds; ++it) {
+        const int i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const bool valid = i < count;
+        int slot = 0, key = TB_SORT_BINS;                 // invalid lanes share a dummy key
+        if (valid) { slot = q[i]; key = tb_dir_bin(ray_d[slot], mode); }
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs(peers) - 1;
+        int base = 0;
+        if (valid && (int)lane == leader) base = atomicAdd(&cursors[key], __popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (valid) out[s_base[key] + base + __popc(peers & ((1u << lane) - 1u))] = slot;
+    }
+}
+
 static size_t tb_batch_capacity() {
     const char* e = getenv("TERRA_B200_BATCH");
     size_t cap = e ? (size_t)strtoull(e, NULL, 10) : ((size_t)1 << 26);
@@ -1365,7 +1426,15 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 }
                 k_counters<<<1, 1, 0, st>>>(wv.counters, 3, 0);
                 d->stats.kernel_launches += 1;
-                cur ^= 1;
+                if (d->sort_rays && bounce < last_bounce && bounce < d->sort_bounces) {
+                    // next queue (queue[cur^1], count in counters[1]) -> queue[cur] in direction bins; no flip
+                    TB_CUDA(cudaMemsetAsync(wv.bins, 0, 2 * TB_SORT_BINS * sizeof(int), st));
+                    k_bin_count<<<d->sm_count * 4, 256, 0, st>>>(wv.queue[cur ^ 1], wv.counters + 1, wv.ray_d, d->sort_rays, wv.bins);
+                    k_bin_scatter<<<d->sm_count * 4, 256, 0, st>>>(wv.queue[cur ^ 1], wv.counters + 1, wv.ray_d, d->sort_rays, wv.bins, wv.queue[cur]);
+                    d->stats.kernel_launches += 2;
+                } else {
+                    cur ^= 1;
+                }
             }
             k_accumulate<<<d->sm_count * 4, 256, 0, st>>>(b, wv.lo, d_acc);
             d->stats.kernel_launches += 1;

@@ -118,3 +118,89 @@ def test_product_front_end_matches_reference_front_end(model, tmp_path):
     run(BIN_REF, *common, "--spp", 2, "--jitter", 0, "--integrator", "normals", "--out", tmp_path / "ref_n.pfm")
     rn = read_pfm(tmp_path / "ref_n.pfm")
     assert (np.abs(gn - rn).max(axis=-1) > 1e-6).mean() < 0.01      # bit-level parity is pinned elsewhere; ties only
+
+
+CONFIG = """# satellite.config as the reference front-end reads it (Config.cpp:170-231)
+scene = {scene}
+tile-size = 16
+integrator = mis
+bounces = 2
+
+campos = 1 1 -2.5
+camdir = 0 0 1
+width = 40
+height = 24
+samples = 8
+tonemap = reinhard
+sampler = random
+envmap = 0.1 0.1 0.2
+workers = 3
+"""
+
+
+def test_satellite_config_drives_the_front_end(model, tmp_path):
+    """--config: names and value spellings of satellite/include/Config.hpp, later command-line options win."""
+    ensure_built()
+    cfg = tmp_path / "satellite.config"
+    cfg.write_text(CONFIG.format(scene=str(model).replace("/", "\\")))        # Windows separators, as shipped
+    out = run(BIN, "--config", cfg, "--dry-run")
+    assert "6 triangles in 3 objects" in out and "40x24, 8 spp" in out and "2 bounces, integrator mis, tiled calls" in out
+    out = run(BIN, "--config", cfg, "--spp", 2, "--dry-run")
+    assert "40x24, 2 spp" in out
+    bad = tmp_path / "bad.config"
+    bad.write_text("width = twelve\nno separator here\nheight = 24\n")
+    r = subprocess.run([str(BIN), "--config", str(bad), "--dry-run"], capture_output=True, text=True)
+    assert r.returncode == 0 and "bad value 'twelve' for width" in r.stderr and "unrecognised name=value" in r.stderr
+    assert "256x24" in r.stdout                                               # the default width is kept
+
+
+def _png_pixels(path):
+    import struct
+    import zlib
+    data = Path(path).read_bytes()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    at, idat, w, h = 8, b"", 0, 0
+    while at < len(data):
+        n, tag = struct.unpack(">I4s", data[at:at + 8])
+        body = data[at + 8:at + 8 + n]
+        assert struct.unpack(">I", data[at + 8 + n:at + 12 + n])[0] == zlib.crc32(tag + body)
+        if tag == b"IHDR":
+            w, h, depth, ctype = struct.unpack(">IIBB", body[:10])
+            assert (depth, ctype) == (8, 2)
+        elif tag == b"IDAT":
+            idat += body
+        at += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)
+    assert (raw[:, 0] == 0).all()
+    return raw[:, 1:].reshape(h, w, 3)
+
+
+def _hdr_pixels(path):
+    data = Path(path).read_bytes()
+    head, _, rest = data.partition(b"\n\n")
+    assert head.startswith(b"#?RADIANCE") and b"FORMAT=32-bit_rle_rgbe" in head
+    dims, _, body = rest.partition(b"\n")
+    m = re.match(rb"-Y (\d+) \+X (\d+)", dims)
+    h, w = int(m.group(1)), int(m.group(2))
+    rgbe = np.frombuffer(body, np.uint8).reshape(h, w, 4).astype(np.float32)
+    return rgbe[..., :3] * np.exp2(rgbe[..., 3:] - 136.0) * (rgbe[..., 3:] > 0)
+
+
+def test_png_and_hdr_output_like_satellites_save(model, tmp_path):
+    """save (Visualization.cpp:286-349): .png = (uint8)(clamp(pixel) * 255), .hdr = Radiance RGBE of pixels[];
+    checked against the .ppm / tonemapped pixels of the same deterministic render (reference build: CPU only)."""
+    ensure_built()
+    if not BIN_REF.exists():
+        pytest.skip("reference library not built here")
+    common = ["--obj", model, "--width", 24, "--height", 16, "--spp", 1, "--jitter", 0, "--integrator", "normals",
+              "--camera", 1, 1, -2.5, 0, 0, 1, "--tonemap", "linear"]
+    for ext in ("png", "hdr", "ppm"):
+        run(BIN_REF, *common, "--out", tmp_path / f"img.{ext}", "--tile", 8, "--progress")
+    png = _png_pixels(tmp_path / "img.png")
+    ppm = np.frombuffer((tmp_path / "img.ppm").read_bytes().split(b"255\n", 1)[1], np.uint8).reshape(16, 24, 3)
+    assert png.shape == (16, 24, 3) and png.max() > 0
+    assert np.abs(png.astype(int) - ppm.astype(int)).max() <= 1               # truncation vs rounding
+    hdr = _hdr_pixels(tmp_path / "img.hdr")
+    assert np.abs(hdr - png / 255.0).max() < 0.02                             # 8-bit mantissas on both sides
+    out = run(BIN_REF, *common, "--out", tmp_path / "p.png", "--tile", 8, "--progress")
+    assert out.count("tile begin") == 6 and out.count("tile end") == 6 and "(6/6)" in out

@@ -10,7 +10,11 @@
  *   terra_headless [--obj model.obj] [--width W --height H] [--spp N] [--bounces N]
  *                  [--integrator simple|direct|mis|mono|depth|normals|misweights] [--jitter J]
  *                  [--camera px py pz dx dy dz] [--fov deg] [--tonemap none|linear|reinhard|filmic|uncharted2]
- *                  [--exposure E] [--gamma G] [--env r g b] [--tile N] [--passes N] [--out image.pfm|.ppm] [--dry-run]
+ *                  [--exposure E] [--gamma G] [--env r g b] [--tile N] [--passes N] [--progress]
+ *                  [--config satellite.config] [--out image.pfm|.ppm|.png|.hdr] [--dry-run]
+ * --config reads the reference front-end's `name = value` file (satellite/include/Config.hpp:19-117,
+ * satellite/src/Config.cpp:170-231); options are applied in command-line order. .png / .hdr are written the way
+ * satellite's save_to_file does (Visualization.cpp:286-349): 8-bit clamp(v)*255 and Radiance RGBE of pixels[].
  * Without --obj a built-in Cornell box is rendered. --tile N renders the frame as NxN-pixel terra_render
  * calls (the reference caller's pattern); the default is one full-frame call. --dry-run builds the scene
  * and prints what it would render, without terra_scene_commit (needs no GPU).
@@ -164,11 +168,88 @@ static void builtin_cornell(GroupVec* groups, MtlVec* mtls) {
 }
 
 /* ------------------------------------------------------------------ image output */
+/* PNG without a compression library: 8-bit RGB, filter 0, zlib stream of STORED deflate blocks.
+ * Bytes as satellite's save_to_file makes them (Visualization.cpp:325-333): (uint8_t)(clamp(v, 0, 1) * 255.f). */
+static unsigned long crc_table[256];
+static void crc_init(void) {
+    for (unsigned long n = 0; n < 256; ++n) { unsigned long c = n; for (int k = 0; k < 8; ++k) c = (c & 1) ? 0xedb88320UL ^ (c >> 1) : c >> 1; crc_table[n] = c; }
+}
+static unsigned long crc_update(unsigned long c, const unsigned char* b, size_t n) {
+    for (size_t i = 0; i < n; ++i) c = crc_table[(c ^ b[i]) & 0xff] ^ (c >> 8);
+    return c;
+}
+static void be32(unsigned char* p, unsigned long v) { p[0] = (unsigned char)(v >> 24); p[1] = (unsigned char)(v >> 16); p[2] = (unsigned char)(v >> 8); p[3] = (unsigned char)v; }
+static void png_chunk(FILE* f, const char* tag, const unsigned char* data, size_t n) {
+    unsigned char h[8];
+    be32(h, (unsigned long)n); memcpy(h + 4, tag, 4);
+    fwrite(h, 8, 1, f);
+    if (n) fwrite(data, n, 1, f);
+    unsigned long c = crc_update(0xffffffffUL, h + 4, 4);
+    c = crc_update(c, data, n) ^ 0xffffffffUL;
+    be32(h, c);
+    fwrite(h, 4, 1, f);
+}
+static int save_png(FILE* f, const TerraFramebuffer* fb) {
+    const size_t w = fb->width, h = fb->height, row = 1 + 3 * w, raw_n = row * h;
+    unsigned char* raw = (unsigned char*)malloc(raw_n);
+    const size_t blocks = (raw_n + 65534) / 65535;
+    unsigned char* z = (unsigned char*)malloc(2 + raw_n + 5 * blocks + 4);
+    if (!raw || !z) return 0;
+    for (size_t y = 0; y < h; ++y) {
+        raw[y * row] = 0;
+        for (size_t x = 0; x < w; ++x) {
+            const float c[3] = { fb->pixels[y * w + x].x, fb->pixels[y * w + x].y, fb->pixels[y * w + x].z };
+            for (int k = 0; k < 3; ++k) { float v = c[k] > 0.f ? c[k] : 0.f; v = v < 1.f ? v : 1.f; raw[y * row + 1 + 3 * x + k] = (unsigned char)(v * 255.f); }
+        }
+    }
+    size_t zn = 0;
+    z[zn++] = 0x78; z[zn++] = 0x01;
+    unsigned long a = 1, b = 0;
+    for (size_t at = 0; at < raw_n; at += 65535) {
+        const size_t n = raw_n - at < 65535 ? raw_n - at : 65535;
+        z[zn++] = at + n == raw_n ? 1 : 0;
+        z[zn++] = (unsigned char)(n & 0xff); z[zn++] = (unsigned char)(n >> 8);
+        z[zn++] = (unsigned char)(~n & 0xff); z[zn++] = (unsigned char)((~n >> 8) & 0xff);
+        memcpy(z + zn, raw + at, n); zn += n;
+        for (size_t i = 0; i < n; ++i) { a = (a + raw[at + i]) % 65521; b = (b + a) % 65521; }
+    }
+    be32(z + zn, (b << 16) | a); zn += 4;
+    static const unsigned char sig[8] = { 0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a };
+    unsigned char ihdr[13];
+    crc_init();
+    fwrite(sig, 8, 1, f);
+    be32(ihdr, (unsigned long)w); be32(ihdr + 4, (unsigned long)h);
+    ihdr[8] = 8; ihdr[9] = 2; ihdr[10] = 0; ihdr[11] = 0; ihdr[12] = 0;
+    png_chunk(f, "IHDR", ihdr, 13);
+    png_chunk(f, "IDAT", z, zn);
+    png_chunk(f, "IEND", NULL, 0);
+    free(raw); free(z);
+    return 1;
+}
+/* Radiance .hdr (what stbi_write_hdr gives satellite, Visualization.cpp:341): RGBE, flat scanlines, top row first. */
+static int save_hdr(FILE* f, const TerraFramebuffer* fb) {
+    fprintf(f, "#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %zu +X %zu\n", fb->height, fb->width);
+    for (size_t i = 0; i < fb->width * fb->height; ++i) {
+        const float c[3] = { fb->pixels[i].x, fb->pixels[i].y, fb->pixels[i].z };
+        const float m = fmaxf(c[0], fmaxf(c[1], c[2]));
+        unsigned char rgbe[4] = { 0, 0, 0, 0 };
+        if (m >= 1e-32f) {
+            int e;
+            const float scale = frexpf(m, &e) * 256.f / m;
+            for (int k = 0; k < 3; ++k) rgbe[k] = (unsigned char)(c[k] > 0.f ? c[k] * scale : 0.f);
+            rgbe[3] = (unsigned char)(e + 128);
+        }
+        fwrite(rgbe, 4, 1, f);
+    }
+    return 1;
+}
 static int save_image(const char* path, const TerraFramebuffer* fb, int hdr_radiance) {
     FILE* f = fopen(path, "wb");
     if (!f) { fprintf(stderr, "terra_headless: cannot write %s\n", path); return 0; }
     const size_t w = fb->width, h = fb->height;
     const char* ext = strrchr(path, '.');
+    if (ext && strcmp(ext, ".png") == 0) { const int ok = save_png(f, fb); fclose(f); return ok; }
+    if (ext && strcmp(ext, ".hdr") == 0) { const int ok = save_hdr(f, fb); fclose(f); return ok; }
     if (ext && strcmp(ext, ".pfm") == 0) {                  /* float RGB, bottom row first, little endian */
         fprintf(f, "PF\n%zu %zu\n-1.0\n", w, h);
         for (size_t y = h; y-- > 0;)
@@ -200,37 +281,137 @@ static int pick(const char* v, const char* const* names, int n, const char* what
     exit(2);
 }
 
+static const char* const integ[] = { "simple", "direct", "mis", "mono", "depth", "normals", "misweights" };
+static const char* const tones[] = { "none", "linear", "reinhard", "filmic", "uncharted2" };
+
+/* ------------------------------------------------------------------ satellite.config
+ * `name = value` lines, '#' comments, blank lines skipped (satellite/src/Config.cpp:170-231); names and value
+ * spellings of satellite/include/Config.hpp:19-117. workers / progressive / accelerator are accepted and have
+ * nothing to drive here. Returns 0 on a malformed value (the reference logs and keeps the default). */
+typedef struct {
+    char obj[1024]; int have_obj;
+    size_t width, height, spp, bounces, tile;
+    int integrator, tonemap, sampler, have_cam, have_up;
+    float jitter, fov, exposure, gamma_, env[3], cam[6], up[3];
+} Settings;
+
+static int parse_f3(const char* v, float* out) {
+    char* end = NULL;
+    out[0] = strtof(v, &end); out[1] = strtof(end, &end); out[2] = strtof(end, &end);
+    while (*end == ' ' || *end == '\t' || *end == '\r') ++end;
+    return *end == '\0';
+}
+
+static int config_set(Settings* S, const char* name, const char* value) {
+    char* end = NULL;
+    if (!strcmp(name, "scene")) {
+        snprintf(S->obj, sizeof S->obj, "%s", value);
+        for (char* c = S->obj; *c; ++c) if (*c == '\\') *c = '/';          /* the shipped config uses Windows separators */
+        S->have_obj = 1; return 1;
+    }
+    if (!strcmp(name, "tile-size")) { const size_t v = strtoul(value, &end, 10); if (*value == '\0' || *end != '\0') return 0; S->tile = v; return 1; }
+    if (!strcmp(name, "bounces")) { const size_t v = strtoul(value, &end, 10); if (*value == '\0' || *end != '\0') return 0; S->bounces = v; return 1; }
+    if (!strcmp(name, "samples")) { const size_t v = strtoul(value, &end, 10); if (*value == '\0' || *end != '\0') return 0; S->spp = v; return 1; }
+    if (!strcmp(name, "width")) { const size_t v = strtoul(value, &end, 10); if (*value == '\0' || *end != '\0') return 0; S->width = v; return 1; }
+    if (!strcmp(name, "height")) { const size_t v = strtoul(value, &end, 10); if (*value == '\0' || *end != '\0') return 0; S->height = v; return 1; }
+    if (!strcmp(name, "gamma")) { const float v = strtof(value, &end); if (*value == '\0' || *end != '\0') return 0; S->gamma_ = v; return 1; }
+    if (!strcmp(name, "exposure")) { const float v = strtof(value, &end); if (*value == '\0' || *end != '\0') return 0; S->exposure = v; return 1; }
+    if (!strcmp(name, "jitter")) { const float v = strtof(value, &end); if (*value == '\0' || *end != '\0') return 0; S->jitter = v; return 1; }
+    if (!strcmp(name, "camfov")) { const float v = strtof(value, &end); if (*value == '\0' || *end != '\0') return 0; S->fov = v; return 1; }
+    float v3[3];
+    if (!strcmp(name, "campos")) { if (!parse_f3(value, v3)) return 0; memcpy(S->cam, v3, sizeof v3); S->have_cam = 1; return 1; }
+    if (!strcmp(name, "camdir")) { if (!parse_f3(value, v3)) return 0; memcpy(S->cam + 3, v3, sizeof v3); S->have_cam = 1; return 1; }
+    if (!strcmp(name, "camup")) { if (!parse_f3(value, v3)) return 0; memcpy(S->up, v3, sizeof v3); S->have_up = 1; return 1; }
+    if (!strcmp(name, "envmap")) { if (!parse_f3(value, v3)) return 0; memcpy(S->env, v3, sizeof v3); return 1; }
+    if (!strcmp(name, "tonemap")) {
+        static const char* const names[] = { "none", "linear", "reinhard", "filmic", "uncharted" };
+        for (int i = 0; i < 5; ++i) if (!strcmp(value, names[i])) { S->tonemap = i; return 1; }
+        return 0;
+    }
+    if (!strcmp(name, "integrator")) {
+        static const char* const names[] = { "simple", "direct", "mis", "debug-mono", "debug-depth", "debug-normals", "debug-mis" };
+        for (int i = 0; i < 7; ++i) if (!strcmp(value, names[i])) { S->integrator = i; return 1; }
+        return 0;
+    }
+    if (!strcmp(name, "sampler")) {
+        static const char* const names[] = { "random", "stratified", "halton" };
+        for (int i = 0; i < 3; ++i) if (!strcmp(value, names[i])) { S->sampler = i; return 1; }
+        return 0;
+    }
+    if (!strcmp(name, "workers") || !strcmp(name, "progressive") || !strcmp(name, "accelerator")) return 1;
+    fprintf(stderr, "terra_headless: config: unknown option '%s'\n", name);
+    return 1;
+}
+
+static int load_config(Settings* S, const char* path) {
+    FILE* f = fopen(path, "r");
+    if (!f) { fprintf(stderr, "terra_headless: cannot read %s\n", path); return 0; }
+    char line[2048];
+    while (fgets(line, sizeof line, f)) {
+        char* p = line;
+        while (*p == ' ' || *p == '\t') ++p;
+        if (*p == '#' || *p == '\n' || *p == '\r' || *p == '\0') continue;
+        char* eq = strchr(p, '=');
+        if (!eq) { fprintf(stderr, "terra_headless: config: unrecognised name=value line: %s", line); continue; }
+        char* name_end = eq;
+        while (name_end > p && (name_end[-1] == ' ' || name_end[-1] == '\t')) --name_end;
+        *name_end = '\0';
+        char* v = eq + 1;
+        while (*v == ' ' || *v == '\t') ++v;
+        size_t n = strlen(v);
+        while (n && (v[n - 1] == '\n' || v[n - 1] == '\r' || v[n - 1] == ' ' || v[n - 1] == '\t')) v[--n] = '\0';
+        if (!config_set(S, p, v)) fprintf(stderr, "terra_headless: config: bad value '%s' for %s (default kept)\n", v, p);
+    }
+    fclose(f);
+    return 1;
+}
+
+static void on_tile(const char* what, size_t x, size_t y, size_t w, size_t h, size_t done, size_t total) {
+    printf("terra_headless: tile %s x %zu y %zu %zux%zu (%zu/%zu)\n", what, x, y, w, h, done, total);
+}
+
 int main(int argc, char** argv) {
-    const char* obj = NULL; const char* out = "terra.pfm";
-    size_t width = 256, height = 256, spp = 16, bounces = 8, tile = 0, passes = 1;
-    int integrator = kTerraIntegratorSimple, tonemap = kTerraTonemappingOperatorNone, dry = 0, have_cam = 0;
-    float jitter = 0.5f, fov = 45.f, exposure = 1.f, gamma_ = 2.2f, env[3] = { 0, 0, 0 }, cam[6] = { 0.5f, 0.5f, -1.4f, 0, 0, 1 };
-    static const char* const integ[] = { "simple", "direct", "mis", "mono", "depth", "normals", "misweights" };
-    static const char* const tones[] = { "none", "linear", "reinhard", "filmic", "uncharted2" };
+    const char* out = "terra.pfm";
+    size_t passes = 1;
+    int dry = 0, progress = 0;
+    Settings S;
+    memset(&S, 0, sizeof S);
+    S.width = 256; S.height = 256; S.spp = 16; S.bounces = 8;
+    S.integrator = kTerraIntegratorSimple; S.tonemap = kTerraTonemappingOperatorNone; S.sampler = kTerraSamplingMethodRandom;
+    S.jitter = 0.5f; S.fov = 45.f; S.exposure = 1.f; S.gamma_ = 2.2f;
+    { const float c[6] = { 0.5f, 0.5f, -1.4f, 0, 0, 1 }; memcpy(S.cam, c, sizeof c); S.up[1] = 1.f; }
     for (int i = 1; i < argc; ++i) {
         const char* a = argv[i];
 #define NEED(n) do { if (i + (n) >= argc) { fprintf(stderr, "terra_headless: %s needs %d value(s)\n", a, (n)); return 2; } } while (0)
-        if (!strcmp(a, "--obj")) { NEED(1); obj = argv[++i]; }
+        if (!strcmp(a, "--obj")) { NEED(1); snprintf(S.obj, sizeof S.obj, "%s", argv[++i]); S.have_obj = 1; }
+        else if (!strcmp(a, "--config")) { NEED(1); if (!load_config(&S, argv[++i])) return 1; }
         else if (!strcmp(a, "--out")) { NEED(1); out = argv[++i]; }
-        else if (!strcmp(a, "--width")) { NEED(1); width = strtoul(argv[++i], NULL, 10); }
-        else if (!strcmp(a, "--height")) { NEED(1); height = strtoul(argv[++i], NULL, 10); }
-        else if (!strcmp(a, "--spp")) { NEED(1); spp = strtoul(argv[++i], NULL, 10); }
-        else if (!strcmp(a, "--bounces")) { NEED(1); bounces = strtoul(argv[++i], NULL, 10); }
-        else if (!strcmp(a, "--tile")) { NEED(1); tile = strtoul(argv[++i], NULL, 10); }
+        else if (!strcmp(a, "--width")) { NEED(1); S.width = strtoul(argv[++i], NULL, 10); }
+        else if (!strcmp(a, "--height")) { NEED(1); S.height = strtoul(argv[++i], NULL, 10); }
+        else if (!strcmp(a, "--spp")) { NEED(1); S.spp = strtoul(argv[++i], NULL, 10); }
+        else if (!strcmp(a, "--bounces")) { NEED(1); S.bounces = strtoul(argv[++i], NULL, 10); }
+        else if (!strcmp(a, "--tile")) { NEED(1); S.tile = strtoul(argv[++i], NULL, 10); }
         else if (!strcmp(a, "--passes")) { NEED(1); passes = strtoul(argv[++i], NULL, 10); }
-        else if (!strcmp(a, "--integrator")) { NEED(1); integrator = pick(argv[++i], integ, 7, "integrator"); }
-        else if (!strcmp(a, "--tonemap")) { NEED(1); tonemap = pick(argv[++i], tones, 5, "tonemap operator"); }
-        else if (!strcmp(a, "--jitter")) { NEED(1); jitter = strtof(argv[++i], NULL); }
-        else if (!strcmp(a, "--fov")) { NEED(1); fov = strtof(argv[++i], NULL); }
-        else if (!strcmp(a, "--exposure")) { NEED(1); exposure = strtof(argv[++i], NULL); }
-        else if (!strcmp(a, "--gamma")) { NEED(1); gamma_ = strtof(argv[++i], NULL); }
-        else if (!strcmp(a, "--env")) { NEED(3); for (int k = 0; k < 3; ++k) env[k] = strtof(argv[++i], NULL); }
-        else if (!strcmp(a, "--camera")) { NEED(6); for (int k = 0; k < 6; ++k) cam[k] = strtof(argv[++i], NULL); have_cam = 1; }
+        else if (!strcmp(a, "--integrator")) { NEED(1); S.integrator = pick(argv[++i], integ, 7, "integrator"); }
+        else if (!strcmp(a, "--tonemap")) { NEED(1); S.tonemap = pick(argv[++i], tones, 5, "tonemap operator"); }
+        else if (!strcmp(a, "--jitter")) { NEED(1); S.jitter = strtof(argv[++i], NULL); }
+        else if (!strcmp(a, "--fov")) { NEED(1); S.fov = strtof(argv[++i], NULL); }
+        else if (!strcmp(a, "--exposure")) { NEED(1); S.exposure = strtof(argv[++i], NULL); }
+        else if (!strcmp(a, "--gamma")) { NEED(1); S.gamma_ = strtof(argv[++i], NULL); }
+        else if (!strcmp(a, "--env")) { NEED(3); for (int k = 0; k < 3; ++k) S.env[k] = strtof(argv[++i], NULL); }
+        else if (!strcmp(a, "--camera")) { NEED(6); for (int k = 0; k < 6; ++k) S.cam[k] = strtof(argv[++i], NULL); S.have_cam = 1; }
+        else if (!strcmp(a, "--progress")) progress = 1;
         else if (!strcmp(a, "--dry-run")) dry = 1;
-        else { fprintf(stderr, "usage: terra_headless [--obj f.obj] [--width W] [--height H] [--spp N] [--bounces N] [--integrator simple|direct|mis|mono|depth|normals|misweights]\n"
-                               "       [--jitter J] [--camera px py pz dx dy dz] [--fov deg] [--tonemap none|linear|reinhard|filmic|uncharted2] [--exposure E] [--gamma G]\n"
-                               "       [--env r g b] [--tile N] [--passes N] [--out image.pfm|.ppm] [--dry-run]\n"); return strcmp(a, "--help") ? 2 : 0; }
+        else { fprintf(stderr, "usage: terra_headless [--config satellite.config] [--obj f.obj] [--width W] [--height H] [--spp N] [--bounces N]\n"
+                               "       [--integrator simple|direct|mis|mono|depth|normals|misweights] [--jitter J] [--camera px py pz dx dy dz] [--fov deg]\n"
+                               "       [--tonemap none|linear|reinhard|filmic|uncharted2] [--exposure E] [--gamma G] [--env r g b] [--tile N] [--passes N]\n"
+                               "       [--progress] [--out image.pfm|.ppm|.png|.hdr] [--dry-run]   (later options override earlier ones)\n"); return strcmp(a, "--help") ? 2 : 0; }
     }
+    const char* obj = S.have_obj ? S.obj : NULL;
+    const size_t width = S.width, height = S.height, spp = S.spp, bounces = S.bounces, tile = S.tile;
+    const int integrator = S.integrator, tonemap = S.tonemap, have_cam = S.have_cam;
+    const float jitter = S.jitter, fov = S.fov, exposure = S.exposure, gamma_ = S.gamma_;
+    float* env = S.env; float* cam = S.cam;
     GroupVec groups = {0}; MtlVec mtls = {0};
     if (obj) { if (!load_obj(obj, &groups, &mtls)) return 1; }
     else builtin_cornell(&groups, &mtls);
@@ -286,7 +467,7 @@ int main(int argc, char** argv) {
     { TerraFloat3 e = { env[0], env[1], env[2] }; terra_attribute_init_constant(&opt->environment_map, &e); }
     opt->tonemapping_operator = (TerraTonemappingOperator)tonemap;
     opt->accelerator = kTerraAcceleratorBVH;
-    opt->sampling_method = kTerraSamplingMethodRandom;
+    opt->sampling_method = (TerraSamplingMethod)S.sampler;
     opt->integrator = (TerraIntegrator)integrator;
     opt->subpixel_jitter = jitter;
     opt->samples_per_pixel = spp;
@@ -302,7 +483,7 @@ int main(int argc, char** argv) {
     }
     camera.position.x = cam[0]; camera.position.y = cam[1]; camera.position.z = cam[2];
     camera.direction.x = cam[3]; camera.direction.y = cam[4]; camera.direction.z = cam[5];
-    camera.up.x = 0; camera.up.y = 1; camera.up.z = 0;
+    camera.up.x = S.up[0]; camera.up.y = S.up[1]; camera.up.z = S.up[2];
     camera.fov = fov;
 
     printf("terra_headless: %zu triangles in %zu objects, %zu materials; %zux%zu, %zu spp x %zu passes, %zu bounces, integrator %s, %s\n",
@@ -318,10 +499,18 @@ int main(int argc, char** argv) {
     if (!terra_framebuffer_create(&fb, width, height)) { fprintf(stderr, "terra_headless: framebuffer %zux%zu\n", width, height); return 1; }
     for (size_t p = 0; p < passes; ++p) {                     /* progressive: results[] accumulate across calls, Terra.c:570-572 */
         if (tile == 0) terra_render(&camera, scene, &fb, 0, 0, width, height);
-        else
+        else {                                                /* the tile grid of Renderer.cpp:316-349, begin / end events as :70-98 */
+            const size_t n_tiles = ((width + tile - 1) / tile) * ((height + tile - 1) / tile);
+            size_t done = 0;
             for (size_t y = 0; y < height; y += tile)
-                for (size_t x = 0; x < width; x += tile)
-                    terra_render(&camera, scene, &fb, x, y, x + tile > width ? width - x : tile, y + tile > height ? height - y : tile);
+                for (size_t x = 0; x < width; x += tile) {
+                    const size_t tw = x + tile > width ? width - x : tile, th = y + tile > height ? height - y : tile;
+                    if (progress) on_tile("begin", x, y, tw, th, done, n_tiles);
+                    terra_render(&camera, scene, &fb, x, y, tw, th);
+                    ++done;
+                    if (progress) on_tile("end", x, y, tw, th, done, n_tiles);
+                }
+        }
     }
     clock_gettime(CLOCK_MONOTONIC, &t2);
     const double commit_s = (t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec);
