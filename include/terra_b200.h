@@ -285,6 +285,7 @@ typedef struct {
     uint64_t h2d_bytes, d2h_bytes;
     uint64_t nodes_visited;      /* only while counting is on (terra_b200_set_counting): 64-byte nodes fetched */
     uint64_t tris_tested;        /*   and triangles tested by the traversal kernel */
+    uint64_t graph_replays;      /* terra_render calls replayed from a CUDA graph (small calls of a shape seen before) */
 } TerraB200Stats;
 
 int  terra_b200_device_count(void);

@@ -19,6 +19,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <thread>
 #include <vector>
 
 #include "tb_internal.h"
@@ -102,6 +103,16 @@ struct TbWave {                // wavefront buffers, `capacity` path slots
     int*     bins;             // 2 x TB_SORT_BINS: counts, then cursors, of the direction binning of the next queue
 };
 
+// What changes between two terra_render calls of the same shape. A call replayed from a CUDA graph reads
+// these from device memory (k_raygen is the only kernel that needs them) so that the graph's kernel arguments
+// stay constant.
+struct TbCallParams {
+    TbCameraFrame cam;
+    int      x, y, fbw, fbh;
+    uint32_t sample_base, pad_;
+    uint64_t seed;
+};
+
 struct TbEventPair { cudaEvent_t a, b; };
 
 struct TbDevice {
@@ -141,6 +152,10 @@ struct TbDevice {
     float       *d_pipe_o3[2], *d_pipe_d3[2];
     TerraB200Hit* d_pipe_hit[2];
     cudaEvent_t  ev_in[2], ev_pack[2], ev_trace[2], ev_out[2];
+    // pageable caller buffers: page-locked bounce buffers, filled / drained by host threads while the GPU works
+    size_t       stage_capacity;
+    float       *h_stage_o3[2], *h_stage_d3[2];
+    TerraB200Hit* h_stage_hit[2];
     // stats
     TerraB200Stats stats;
     std::vector<TbEventPair> ev_pool;
@@ -155,6 +170,14 @@ struct TbDevice {
     int          warp_samples; // at most this many samples of one pixel share a warp (TERRA_B200_WARP_SAMPLES, default 32)
     int          tile_pixels;  // 1: waves walk the region in 8x4 pixel tiles (TERRA_B200_TILE=0 turns it off)
     int          tri_min, refetch_below;
+    // CUDA-graph replay of small terra_render calls (launch-bound: ~45 launches for a 128x128 tile)
+    struct Graph { size_t w, h, spp; uint64_t epoch; cudaGraphExec_t exec; uint64_t launches, paths, last_use; };
+    std::vector<Graph> graphs;
+    std::vector<uint64_t> graph_seen;      // shapes rendered once without a graph (w | h << 20 | spp << 40, xor epoch)
+    uint64_t     graph_epoch, graph_clock;  // epoch: bumped whenever a pointer or scene constant a graph baked in changes
+    size_t       graph_max_paths;           // TERRA_B200_GRAPH_PATHS (0 = never use graphs)
+    bool         capturing;
+    TbCallParams *d_call, *h_call;
     int          sort_rays, sort_bounces;   // TERRA_B200_SORT (0 off, 1 octant, 2 octant + dominant axis) for the first TERRA_B200_SORT_BOUNCES bounces
 };
 
@@ -237,7 +260,12 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
     d->st_in = d->st_out = NULL; d->pipe_capacity = 0;
     d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
+    d->graph_epoch = 1; d->graph_clock = 0; d->capturing = false;
+    d->d_call = tb_alloc<TbCallParams>(1);
+    TB_CUDA(cudaHostAlloc((void**)&d->h_call, sizeof(TbCallParams), cudaHostAllocDefault));
     for (int k = 0; k < 2; ++k) { d->d_pipe_o3[k] = d->d_pipe_d3[k] = NULL; d->d_pipe_hit[k] = NULL; }
+    d->stage_capacity = 0;
+    for (int k = 0; k < 2; ++k) { d->h_stage_o3[k] = d->h_stage_d3[k] = NULL; d->h_stage_hit[k] = NULL; }
     memset(&d->stats, 0, sizeof d->stats);
     d->ev_used = 0;
     d->counting = 0;
@@ -249,6 +277,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
         const char* ws = getenv("TERRA_B200_WARP_SAMPLES"); d->warp_samples = ws ? atoi(ws) : 32;
+        const char* gp = getenv("TERRA_B200_GRAPH_PATHS"); d->graph_max_paths = gp ? (size_t)strtoull(gp, NULL, 10) : ((size_t)1 << 22);
         const char* so = getenv("TERRA_B200_SORT"); d->sort_rays = so ? atoi(so) : 0;
         const char* sb = getenv("TERRA_B200_SORT_BOUNCES"); d->sort_bounces = sb ? atoi(sb) : 2;
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
@@ -289,10 +318,13 @@ extern "C" void tb_device_destroy(TbDevice* d) {
     tb_free(d->d_results); tb_free(d->d_pixels); tb_free(d->d_acc);
     tb_free(d->d_io_o); tb_free(d->d_io_d); tb_free(d->d_io_hit);
     for (int k = 0; k < 2; ++k) { tb_free(d->d_pipe_o3[k]); tb_free(d->d_pipe_d3[k]); tb_free(d->d_pipe_hit[k]); }
+    for (int k = 0; k < 2; ++k) { if (d->h_stage_o3[k]) cudaFreeHost(d->h_stage_o3[k]); if (d->h_stage_d3[k]) cudaFreeHost(d->h_stage_d3[k]); if (d->h_stage_hit[k]) cudaFreeHost(d->h_stage_hit[k]); }
     if (d->st_in) {
         for (int k = 0; k < 2; ++k) { cudaEventDestroy(d->ev_in[k]); cudaEventDestroy(d->ev_pack[k]); cudaEventDestroy(d->ev_trace[k]); cudaEventDestroy(d->ev_out[k]); }
         cudaStreamDestroy(d->st_in); cudaStreamDestroy(d->st_out);
     }
+    for (TbDevice::Graph& g : d->graphs) cudaGraphExecDestroy(g.exec);
+    tb_free(d->d_call); cudaFreeHost(d->h_call);
     for (TbEventPair& e : d->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     cudaEventDestroy(d->ev_call_a);
     cudaEventDestroy(d->ev_call_b);
@@ -314,6 +346,7 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
         terra_log("terra_b200: BVH depth %d exceeds the traversal stack (%d entries)\n", f->stack_bound, TB_STACK_SMEM + TB_STACK_LOCAL);
         abort();
     }
+    d->graph_epoch++;
     tb_scene_free(d);
     d->d_nodes = (float4*)tb_upload(f->nodes, f->n_nodes * 16, d);
     d->d_tris = (float4*)tb_upload(f->tris, f->n_tris * 12, d);
@@ -510,6 +543,7 @@ struct TbRaygenArgs {
     float   jitter;
     float4 *ray_o, *ray_d, *thr, *lo;
     int*    queue;
+    const TbCallParams* call;   // non-NULL: overrides batch.{x,y,fbw,fbh,sample_base,seed} and cam (graph replay)
 };
 
 // Region-linear index -> pixel offset inside the region. Tiled: consecutive indices fill an 8x4 pixel
@@ -580,6 +614,12 @@ __device__ __forceinline__ V3 tb_camera_dir(const TbCameraFrame& cam, int px, in
 }
 
 __global__ void __launch_bounds__(256) k_raygen(TbRaygenArgs a) {
+    if (a.call) {
+        const TbCallParams c = *a.call;
+        a.cam = c.cam;
+        a.batch.x = c.x; a.batch.y = c.y; a.batch.fbw = c.fbw; a.batch.fbh = c.fbh;
+        a.batch.sample_base = c.sample_base; a.batch.seed = c.seed;
+    }
     const int n = a.batch.n_pixels * a.batch.n_samples;
     for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
         int px, py; uint32_t sample;
@@ -1145,10 +1185,10 @@ __global__ void k_bsdf_kat(TbDevScene sc, int object, size_t n, const float* e12
 __global__ void k_counters(int* c, int mode, int value) {
     unsigned long long* rays = (unsigned long long*)(c + 8);
     switch (mode) {
-        case 0: c[0] = 0; c[1] = value; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; break;   // new wave
+        case 0: c[0] = 0; c[1] = value; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)value; break;   // new wave = its first bounce begins
         case 1: c[0] = 0; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)c[1]; break;   // bounce begins
         case 2: c[0] = 0; *rays += (unsigned long long)c[3]; break;                                  // before the visibility trace
-        case 3: c[1] = c[2]; break;                                                                  // bounce ends
+        case 3: c[1] = c[2]; c[0] = 0; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)c[1]; break;   // bounce ends, the next one begins
         case 4: *rays += (unsigned long long)value; c[0] = 0; break;                                 // stand-alone trace of `value` rays
         default: *rays = 0; c[10] = c[11] = c[12] = c[13] = 0; break;
     }
@@ -1312,8 +1352,8 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
 }
 
 static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, bool coherent) {
-    TbEventPair* e = tb_event_pair(d);
-    TB_CUDA(cudaEventRecord(e->a, st));
+    TbEventPair* e = d->capturing ? NULL : tb_event_pair(d);     // a captured launch is timed as part of the whole call only
+    if (e) TB_CUDA(cudaEventRecord(e->a, st));
     TbTraceArgs c = a;
     c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
     c.tri_min = d->tri_min; c.refetch_below = d->refetch_below;
@@ -1322,7 +1362,7 @@ static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, 
     if (kind == TB_K_PACKET && d->counting) kind = TB_K_V2;     // the work counters mean the per-ray walk
     if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind);
     else             tb_launch_trace_kernel<false>(d, st, c, kind);
-    TB_CUDA(cudaEventRecord(e->b, st));
+    if (e) TB_CUDA(cudaEventRecord(e->b, st));
     d->stats.kernel_launches += 1;
 }
 
@@ -1337,13 +1377,14 @@ static TbShadeKernel tb_shade_kernel(int preset, int stage) {
 // All waves of one region: adds `spp` samples per pixel into d_acc (region-linear float4, zeroed by the caller).
 static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* cam, size_t fbw, size_t fbh,
                              size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
-                             uint64_t seed, float4* d_acc) {
+                             uint64_t seed, float4* d_acc, const TbCallParams* d_call = NULL) {
     const size_t npx = w * h;
     const size_t cap = tb_batch_capacity();
     const size_t px_per_wave = npx < cap ? npx : cap;
     size_t s_per_wave = npx < cap ? cap / npx : 1;
     if (s_per_wave > spp) s_per_wave = spp;
     if (s_per_wave < 1) s_per_wave = 1;
+    if (d->wave.capacity < px_per_wave * s_per_wave) d->graph_epoch++;       // the wave buffers move: graphs that baked their addresses are stale
     tb_wave_reserve(&d->wave, px_per_wave * s_per_wave);
     TbWave& wv = d->wave;
     const TbDevScene& sc = d->sc;
@@ -1372,12 +1413,12 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
             TbRaygenArgs rg;
             rg.batch = b; rg.cam = *cam; rg.jitter = sc.jitter;
             rg.ray_o = wv.ray_o; rg.ray_d = wv.ray_d; rg.thr = wv.thr; rg.lo = wv.lo; rg.queue = wv.queue[0];
+            rg.call = d_call;
             k_counters<<<1, 1, 0, st>>>(wv.counters, 0, n_paths);
             k_raygen<<<d->sm_count * 8, 256, 0, st>>>(rg);
             d->stats.kernel_launches += 2;
             int cur = 0;
             for (int bounce = 0; bounce <= last_bounce; ++bounce) {
-                k_counters<<<1, 1, 0, st>>>(wv.counters, 1, 0);
                 TbTraceArgs ta;
                 memset(&ta, 0, sizeof ta);
                 ta.nodes = sc.nodes; ta.tris = sc.tris;
@@ -1387,7 +1428,6 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 ta.matq = wv.matq; ta.matq_count = wv.counters + 4; ta.matq_stride = (int)wv.capacity;
                 ta.emit_prim = 0;
                 tb_launch_trace(d, st, ta, bounce == 0);
-                d->stats.kernel_launches += 1;
                 if (sc.env_lit && last_bounce == sc.bounces && (!env_nee || bounce == 0)) {
                     k_miss<<<d->sm_count * 4, 256, 0, st>>>(sc, wv.queue[cur], wv.counters + 1, wv.ray_d, wv.hit, wv.thr, wv.lo);
                     d->stats.kernel_launches += 1;
@@ -1424,6 +1464,7 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                     tb_shade_kernel(p, 1)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
                     d->stats.kernel_launches += 1;
                 }
+                if (bounce == last_bounce) break;                    // nothing reads the queues of a bounce that does not happen
                 k_counters<<<1, 1, 0, st>>>(wv.counters, 3, 0);
                 d->stats.kernel_launches += 1;
                 if (d->sort_rays && bounce < last_bounce && bounce < d->sort_bounces) {
@@ -1457,12 +1498,67 @@ static void tb_finish_call(TbDevice* d, cudaStream_t st, bool whole_render) {
     tb_drain_events(d);
 }
 
+// Graph of one terra_render call of shape (w, h, spp) on the current scene. The first call of a shape runs
+// directly (a one-off call must not pay for capture + instantiation); the second captures; later ones replay.
+// Everything a graph bakes in — buffer addresses, scene constants, kernel choices — is covered by graph_epoch.
+template <typename Body>
+static TbDevice::Graph* tb_graph_for(TbDevice* d, cudaStream_t st, size_t w, size_t h, size_t spp, Body& body) {
+    ++d->graph_clock;
+    for (TbDevice::Graph& g : d->graphs)
+        if (g.w == w && g.h == h && g.spp == spp && g.epoch == d->graph_epoch) { g.last_use = d->graph_clock; return &g; }
+    const uint64_t tag = ((uint64_t)w | ((uint64_t)h << 20) | ((uint64_t)spp << 40)) ^ (d->graph_epoch * 0x9E3779B97F4A7C15ull);
+    bool seen = false;
+    for (uint64_t t : d->graph_seen) seen = seen || t == tag;
+    if (!seen) {
+        if (d->graph_seen.size() >= 64) d->graph_seen.clear();
+        d->graph_seen.push_back(tag);
+        return NULL;
+    }
+    // drop stale graphs, and the least recently used one beyond 8
+    for (size_t i = 0; i < d->graphs.size();) {
+        if (d->graphs[i].epoch != d->graph_epoch) { cudaGraphExecDestroy(d->graphs[i].exec); d->graphs.erase(d->graphs.begin() + i); }
+        else ++i;
+    }
+    if (d->graphs.size() >= 8) {
+        size_t lru = 0;
+        for (size_t i = 1; i < d->graphs.size(); ++i) if (d->graphs[i].last_use < d->graphs[lru].last_use) lru = i;
+        cudaGraphExecDestroy(d->graphs[lru].exec);
+        d->graphs.erase(d->graphs.begin() + lru);
+    }
+    // buffers must exist before the capture starts (no allocation inside it): size the wave for this shape
+    {
+        const size_t npx = w * h, cap = tb_batch_capacity();
+        const size_t px_per_wave = npx < cap ? npx : cap;
+        size_t s_per_wave = npx < cap ? cap / npx : 1;
+        if (s_per_wave > spp) s_per_wave = spp;
+        if (s_per_wave < 1) s_per_wave = 1;
+        if (d->wave.capacity < px_per_wave * s_per_wave) { d->graph_epoch++; tb_wave_reserve(&d->wave, px_per_wave * s_per_wave); }
+    }
+    const TerraB200Stats before = d->stats;
+    cudaGraph_t graph = NULL;
+    d->capturing = true;
+    TB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    body(d->d_call);
+    TB_CUDA(cudaStreamEndCapture(st, &graph));
+    d->capturing = false;
+    TbDevice::Graph g;
+    g.w = w; g.h = h; g.spp = spp; g.epoch = d->graph_epoch; g.last_use = d->graph_clock;
+    g.launches = d->stats.kernel_launches - before.kernel_launches;
+    g.paths = d->stats.paths_traced - before.paths_traced;
+    d->stats = before;                                     // the capture pass executed nothing
+    TB_CUDA(cudaGraphInstantiate(&g.exec, graph, 0));
+    TB_CUDA(cudaGraphDestroy(graph));
+    d->graphs.push_back(g);
+    return &d->graphs.back();
+}
+
 extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const TerraFramebuffer* fb,
                                  size_t x, size_t y, size_t w, size_t h, size_t spp, uint64_t seed) {
     TB_CUDA(cudaSetDevice(d->index));
     cudaStream_t st = d->stream;
     const size_t npx = w * h;
     if (npx > d->fb_capacity) {
+        d->graph_epoch++;
         tb_free(d->d_results); tb_free(d->d_pixels); tb_free(d->d_acc);
         d->d_results = tb_alloc<TerraRawIntegrationResult>(npx);
         d->d_pixels = tb_alloc<float>(npx * 3);
@@ -1475,16 +1571,35 @@ extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const Te
                               fb->results + y * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
                               w * sizeof(TerraRawIntegrationResult), h, cudaMemcpyHostToDevice, st));
     d->stats.h2d_bytes += npx * sizeof(TerraRawIntegrationResult);
-    TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
-    tb_render_region(d, st, cam, fb->width, fb->height, x, y, w, h, 0, spp, seed, d->d_acc);
-    TbFinalizeArgs fa;
-    fa.acc = d->d_acc;
-    fa.results = d->d_results; fa.results_pitch = w;
-    fa.pixels = d->d_pixels; fa.pixels_pitch = w;
-    fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = d->sc.tonemap;
-    fa.exposure = d->sc.exposure; fa.inv_gamma = d->sc.inv_gamma;
-    k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
-    d->stats.kernel_launches += 1;
+    // ---- the kernels of the call: launched one by one, or — for a small call whose shape has been seen
+    //      before — replayed from a CUDA graph (a 128x128 tile is ~45 launches of a few microseconds each)
+    auto body = [&](const TbCallParams* d_call) {
+        TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
+        tb_render_region(d, st, cam, fb->width, fb->height, x, y, w, h, 0, spp, seed, d->d_acc, d_call);
+        TbFinalizeArgs fa;
+        fa.acc = d->d_acc;
+        fa.results = d->d_results; fa.results_pitch = w;
+        fa.pixels = d->d_pixels; fa.pixels_pitch = w;
+        fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = d->sc.tonemap;
+        fa.exposure = d->sc.exposure; fa.inv_gamma = d->sc.inv_gamma;
+        k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
+        d->stats.kernel_launches += 1;
+    };
+    TbDevice::Graph* g = NULL;
+    if (d->graph_max_paths && npx * spp <= d->graph_max_paths && !d->counting) g = tb_graph_for(d, st, w, h, spp, body);
+    if (g) {
+        TbCallParams* hp = d->h_call;
+        hp->cam = *cam;
+        hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fb->width; hp->fbh = (int)fb->height;
+        hp->sample_base = 0; hp->pad_ = 0; hp->seed = seed;
+        TB_CUDA(cudaMemcpyAsync(d->d_call, hp, sizeof *hp, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaGraphLaunch(g->exec, st));
+        d->stats.kernel_launches += g->launches;
+        d->stats.paths_traced += g->paths;
+        d->stats.graph_replays += 1;
+    } else {
+        body(NULL);
+    }
     TB_CUDA(cudaMemcpy2DAsync(fb->results + y * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
                               d->d_results, w * sizeof(TerraRawIntegrationResult),
                               w * sizeof(TerraRawIntegrationResult), h, cudaMemcpyDeviceToHost, st));
@@ -1501,6 +1616,7 @@ extern "C" void tb_device_render_resident(TbDevice* d, const TbCameraFrame* cam,
     cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
     const size_t npx = w * h;
     if (npx > d->acc_capacity) {
+        d->graph_epoch++;
         tb_free(d->d_acc);
         d->d_acc = tb_alloc<float4>(npx > d->fb_capacity ? npx : d->fb_capacity);
         d->acc_capacity = npx > d->fb_capacity ? npx : d->fb_capacity;
@@ -1590,6 +1706,43 @@ static void tb_pipe_reserve(TbDevice* d, size_t chunk) {
     d->pipe_capacity = chunk;
 }
 
+static bool tb_is_pageable(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return at.type == cudaMemoryTypeUnregistered;
+}
+
+// memcpy on several host threads (one thread moves ~10 GB/s, the PCIe link wants 50)
+static void tb_memcpy_mt(void* dst, const void* src, size_t bytes) {
+    const size_t min_per_thread = (size_t)4 << 20;
+    unsigned hw = std::thread::hardware_concurrency();
+    size_t threads = hw ? hw : 1;
+    if (threads > 16) threads = 16;
+    if (threads > bytes / min_per_thread) threads = bytes / min_per_thread;
+    if (threads <= 1) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> pool;
+    const size_t per = ((bytes + threads - 1) / threads + 63) & ~(size_t)63;
+    for (size_t t = 0; t < threads; ++t) {
+        const size_t lo = t * per, hi = lo + per < bytes ? lo + per : bytes;
+        if (lo >= hi) break;
+        pool.emplace_back([=]() { memcpy((char*)dst + lo, (const char*)src + lo, hi - lo); });
+    }
+    for (std::thread& th : pool) th.join();
+}
+
+static void tb_stage_reserve(TbDevice* d, size_t chunk) {
+    if (chunk <= d->stage_capacity) return;
+    for (int k = 0; k < 2; ++k) {
+        if (d->h_stage_o3[k]) cudaFreeHost(d->h_stage_o3[k]);
+        if (d->h_stage_d3[k]) cudaFreeHost(d->h_stage_d3[k]);
+        if (d->h_stage_hit[k]) cudaFreeHost(d->h_stage_hit[k]);
+        TB_CUDA(cudaHostAlloc((void**)&d->h_stage_o3[k], chunk * 12, cudaHostAllocDefault));
+        TB_CUDA(cudaHostAlloc((void**)&d->h_stage_d3[k], chunk * 12, cudaHostAllocDefault));
+        TB_CUDA(cudaHostAlloc((void**)&d->h_stage_hit[k], chunk * sizeof(TerraB200Hit), cudaHostAllocDefault));
+    }
+    d->stage_capacity = chunk;
+}
+
 extern "C" void tb_device_trace_host(TbDevice* d, size_t n, const float* origins, const float* dirs, TerraB200Hit* out) {
     TB_CUDA(cudaSetDevice(d->index));
     if (n == 0) return;
@@ -1599,13 +1752,36 @@ extern "C" void tb_device_trace_host(TbDevice* d, size_t n, const float* origins
     if (chunk > n) chunk = n;
     tb_io_reserve(d, chunk);
     tb_pipe_reserve(d, chunk);
+    // Pageable caller memory: a cudaMemcpyAsync from it is staged by the driver through one small buffer and
+    // blocks the calling thread (~6 GB/s, no overlap). Large pageable batches go through the library's own
+    // page-locked bounce buffers instead, filled and drained by host threads while the GPU works on the
+    // previous chunk. Small batches are not worth the extra copy.
+    size_t staging_min = (size_t)1 << 18;                               // TERRA_B200_STAGING_MIN (rays; 0 = never stage)
+    if (const char* e = getenv("TERRA_B200_STAGING_MIN")) { staging_min = (size_t)strtoull(e, NULL, 10); if (!staging_min) staging_min = ~(size_t)0; }
+    const bool staged = n >= staging_min &&
+                        (tb_is_pageable(origins) || tb_is_pageable(dirs) || tb_is_pageable(out));
+    if (staged) tb_stage_reserve(d, chunk);
     size_t k = 0;
+    size_t pending_at[2] = { 0, 0 }, pending_m[2] = { 0, 0 };           // staged: hits waiting in h_stage_hit[slot]
     for (size_t at = 0; at < n; at += chunk, ++k) {
         const size_t m = n - at < chunk ? n - at : chunk;
         const int slot = (int)(k & 1);
+        const float* src_o = origins + 3 * at;
+        const float* src_d = dirs + 3 * at;
+        TerraB200Hit* dst_hit = out + at;
+        if (staged) {
+            if (k >= 2) {                                                 // chunk k-2 has come back: hand it to the caller, slot is free
+                TB_CUDA(cudaEventSynchronize(d->ev_out[slot]));
+                tb_memcpy_mt(out + pending_at[slot], d->h_stage_hit[slot], pending_m[slot] * sizeof(TerraB200Hit));
+            }
+            tb_memcpy_mt(d->h_stage_o3[slot], src_o, m * 12);
+            tb_memcpy_mt(d->h_stage_d3[slot], src_d, m * 12);
+            src_o = d->h_stage_o3[slot]; src_d = d->h_stage_d3[slot]; dst_hit = d->h_stage_hit[slot];
+            pending_at[slot] = at; pending_m[slot] = m;
+        }
         if (k >= 2) TB_CUDA(cudaStreamWaitEvent(d->st_in, d->ev_pack[slot], 0));       // chunk k-2 has been packed: its raw input is free
-        TB_CUDA(cudaMemcpyAsync(d->d_pipe_o3[slot], origins + 3 * at, m * 12, cudaMemcpyHostToDevice, d->st_in));
-        TB_CUDA(cudaMemcpyAsync(d->d_pipe_d3[slot], dirs + 3 * at, m * 12, cudaMemcpyHostToDevice, d->st_in));
+        TB_CUDA(cudaMemcpyAsync(d->d_pipe_o3[slot], src_o, m * 12, cudaMemcpyHostToDevice, d->st_in));
+        TB_CUDA(cudaMemcpyAsync(d->d_pipe_d3[slot], src_d, m * 12, cudaMemcpyHostToDevice, d->st_in));
         TB_CUDA(cudaEventRecord(d->ev_in[slot], d->st_in));
         TB_CUDA(cudaStreamWaitEvent(st, d->ev_in[slot], 0));
         k_pack_rays<<<d->sm_count * 8, 256, 0, st>>>(m, d->d_pipe_o3[slot], d->d_pipe_d3[slot], d->d_io_o, d->d_io_d);
@@ -1615,10 +1791,18 @@ extern "C" void tb_device_trace_host(TbDevice* d, size_t n, const float* origins
         tb_trace_generic(d, st, m, d->d_io_o, d->d_io_d, (float4*)d->d_pipe_hit[slot]);
         TB_CUDA(cudaEventRecord(d->ev_trace[slot], st));
         TB_CUDA(cudaStreamWaitEvent(d->st_out, d->ev_trace[slot], 0));
-        TB_CUDA(cudaMemcpyAsync(out + at, d->d_pipe_hit[slot], m * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, d->st_out));
+        TB_CUDA(cudaMemcpyAsync(dst_hit, d->d_pipe_hit[slot], m * sizeof(TerraB200Hit), cudaMemcpyDeviceToHost, d->st_out));
         TB_CUDA(cudaEventRecord(d->ev_out[slot], d->st_out));
         d->stats.h2d_bytes += m * 24;
         d->stats.d2h_bytes += m * sizeof(TerraB200Hit);
+    }
+    if (staged) {                                                         // the last one or two chunks, oldest first
+        const size_t first = k >= 2 ? k - 2 : 0;
+        for (size_t j = first; j < k; ++j) {
+            const int slot = (int)(j & 1);
+            TB_CUDA(cudaEventSynchronize(d->ev_out[slot]));
+            tb_memcpy_mt(out + pending_at[slot], d->h_stage_hit[slot], pending_m[slot] * sizeof(TerraB200Hit));
+        }
     }
     TB_CUDA(cudaStreamSynchronize(d->st_out));
     tb_finish_call(d, st, false);
@@ -1723,7 +1907,7 @@ extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
     *out = d->stats;
 }
 
-extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; }
+extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; d->graph_epoch++; }
 // Builds TbDevDist2D over `f` (ny rows of nx, device) into freshly allocated device arrays.
 static void tb_dist2d_build(TbDevice* d, cudaStream_t st, const float* d_f, int nx, int ny, float** cdf_out, float** rows_out,
                             float** marg_out, TbDevDist2D* out) {
@@ -1749,6 +1933,7 @@ static void tb_dist2d_build(TbDevice* d, cudaStream_t st, const float* d_f, int 
 // the environment is not a lat-long texture.
 extern "C" void tb_device_set_env_lit(TbDevice* d, int on) {
     TB_CUDA(cudaSetDevice(d->index));
+    d->graph_epoch++;
     d->sc.env_lit = on ? 1 : 0;
     d->sc.env_nee = 0;
     tb_free(d->d_env_f); tb_free(d->d_env_cdf); tb_free(d->d_env_rows); tb_free(d->d_env_marg);

@@ -97,7 +97,15 @@ def test_pipelined_host_batches_equal_one_shot(api, scenes, gpu, monkeypatch):
         ph.array.view(np.uint8)[:] = 0xff
         got = s.trace_rays(po.array, pd.array, out=ph.array)
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), chunk
+        # pageable caller buffers: straight from them (driver-staged copies) ...
+        monkeypatch.setenv("TERRA_B200_STAGING_MIN", "0")
         assert np.array_equal(s.trace_rays(o, d).view(np.uint32), want.view(np.uint32)), chunk
+        # ... and through the library's page-locked bounce buffers (the path large pageable batches take)
+        monkeypatch.setenv("TERRA_B200_STAGING_MIN", "1")
+        assert np.array_equal(s.trace_rays(o, d).view(np.uint32), want.view(np.uint32)), chunk
+        mixed = s.trace_rays(po.array, d, out=ph.array)                  # page-locked and pageable mixed
+        assert np.array_equal(mixed.view(np.uint32), want.view(np.uint32)), chunk
+        monkeypatch.delenv("TERRA_B200_STAGING_MIN")
         assert np.array_equal(s.trace_rays(po.array[:777], pd.array[:777]).view(np.uint32), want[:777].view(np.uint32))
     st = s.stats()
     assert st.h2d_bytes > 0 and st.d2h_bytes > 0

@@ -483,6 +483,40 @@ def test_async_tile_job_cancel_and_two_jobs_on_one_scene(api, scenes, gpu):
     s.destroy()
 
 
+def test_graph_replay_equals_direct_launches(api, scenes, gpu, monkeypatch):
+    """Small terra_render calls of a shape seen before are replayed from a CUDA graph (the per-call values —
+    region origin, framebuffer size, seed, camera — reach k_raygen through device memory). Same bytes as the
+    kernel-by-kernel launches: tiles of two shapes, three passes, the camera moving between passes, MIS
+    integrator (visibility launches inside the graph), results accumulating across calls."""
+    w, h, tile = 72, 48, 32            # 32x32 tiles plus ragged 8-wide / 16-high edge tiles: four shapes
+    outs, replays, launches = [], [], []
+    for graph_paths in ("0", None):
+        if graph_paths is None:
+            monkeypatch.delenv("TERRA_B200_GRAPH_PATHS", raising=False)
+        else:
+            monkeypatch.setenv("TERRA_B200_GRAPH_PATHS", graph_paths)
+        s, cam = scenes.cornell(gpu, spp=4, integrator=api.INTEGRATOR_DIRECT_MIS, bounces=3)
+        gpu.terra_b200_set_seed(s.h, 9)
+        fb = api.Framebuffer()
+        assert gpu.terra_framebuffer_create(C.byref(fb), w, h)
+        gpu.terra_framebuffer_clear(C.byref(fb))
+        for p in range(3):
+            cam.position.x = 0.5 + 0.02 * p
+            for y in range(0, h, tile):
+                for x in range(0, w, tile):
+                    gpu.terra_render(C.byref(cam), s.h, C.byref(fb), x, y, min(tile, w - x), min(tile, h - y))
+        res, pix = _fb_arrays(fb, w, h)
+        st = s.stats()
+        outs.append((res, pix)); replays.append(st.graph_replays); launches.append(st.kernel_launches)
+        gpu.terra_framebuffer_destroy(C.byref(fb))
+        s.destroy()
+    assert replays[0] == 0 and replays[1] >= 6, replays          # 18 calls, 4 shapes: first direct, second captures, rest replay
+    assert launches[0] == launches[1]                             # the same kernels ran
+    assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
+    assert np.array_equal(outs[0][1].view(np.uint32), outs[1][1].view(np.uint32))
+    assert (outs[1][0][..., 3].view(np.int32) == 12).all()
+
+
 def test_stratified_rounds_spp_like_the_reference(api, scenes, gpu):
     """sampling_method only changes spp: cur = strata^2; while (spp > cur) cur *= cur (Terra.c:519-527)."""
     s, cam = scenes.cornell(gpu, spp=5)
