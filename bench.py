@@ -321,7 +321,9 @@ def run_render_arm(args):
     if world == 1:
         fb = api.Framebuffer()
         assert lib.terra_framebuffer_create(C.byref(fb), w, h)
-        ms_e2e, _ = timed(lambda: lib.terra_render(C.byref(cam), s.h, C.byref(fb), 0, 0, w, h), max(1, args.steps // 2), 1)
+        # warm-up >= 3 calls (the contract's W): the first call of a shape sizes buffers, the second may capture a CUDA graph
+        e2e_steps = args.steps if w * h * spp <= (1 << 22) else max(1, args.steps // 2)
+        ms_e2e, _ = timed(lambda: lib.terra_render(C.byref(cam), s.h, C.byref(fb), 0, 0, w, h), e2e_steps, max(1, min(3, args.warmup)))
         h2d, d2h = w * h * 16 + 40, w * h * 28
     else:
         def e2e_step():
@@ -330,7 +332,7 @@ def run_render_arm(args):
             r.render(spp)
             if rank == 0:
                 r.to_host()
-        ms_e2e, _ = timed(e2e_step, max(1, args.steps // 2), 1)
+        ms_e2e, _ = timed(e2e_step, max(1, args.steps // 2), max(1, min(3, args.warmup)))
         h2d, d2h = w * h * 16 + 40, w * h * 28
 
     # ---- work counters for the roofline: one small counted frame (never inside a timed region)

@@ -8,6 +8,9 @@
 //   k_shade       [K3+K4] surface, integrator, BSDF sample/pdf/eval, Russian roulette, next ray
 //                                               Terra.c:1726-1764, 1039-1097, 1339-1587; TerraPresets.c
 //   k_accumulate / k_finalize [K6]              Terra.c:569-630, 1815-1828
+//   k_miss        env-lit extension             Terra.c:1056 restored; tb_distribution.cuh: Terra.c:760-846 on the device
+// Host side of this file: wave loop (tb_render_region), CUDA-graph replay of small calls (tb_graph_for),
+// pipelined host ray batches (tb_device_trace_host), uploads, statistics.
 // Compiled with -fmad=false: the reference's x86-64 build has no FMA contraction and the primary
 // closest-hit parity is bit-exact only if every mul/add rounds separately.
 // No tensor cores: there is no dense contraction anywhere on this path.
