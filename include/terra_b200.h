@@ -360,6 +360,11 @@ void        terra_b200_job_wait(HTerraB200Job job);      /* block until every ti
 void        terra_b200_job_cancel(HTerraB200Job job);    /* skip tiles not started yet; returns once the running one ends */
 void        terra_b200_job_release(HTerraB200Job job);   /* wait, then free the handle */
 
+/* Render calls of at most max_paths (pixel, sample) pairs whose shape (width, height, spp) repeats are replayed
+ * from a CUDA graph instead of being launched kernel by kernel (same results; default 4M paths, environment
+ * TERRA_B200_GRAPH_PATHS; 0 = never). Per-kernel trace timings in TerraB200Stats are not taken on replayed calls. */
+void        terra_b200_set_graph_paths(HTerraScene scene, size_t max_paths);
+
 /* Page-locked host memory for large ray batches (and anything else handed to the entry points below):
  * copies from / to it run at PCIe speed and overlap the kernels. NULL when no CUDA device is visible.
  * Framebuffers made by terra_framebuffer_create are page-locked already. */

@@ -661,6 +661,7 @@ extern "C" void terra_b200_distribution_2d_sample(HTerraScene h, const float* f,
     std::lock_guard<std::mutex> guard(s->lock);
     tb_device_distribution_2d_sample(s->dev, f, nx, ny, n, e1, e2, out4);
 }
+extern "C" void terra_b200_set_graph_paths(HTerraScene h, size_t max_paths) { tb_device_set_graph_paths(committed(h, "terra_b200_set_graph_paths")->dev, max_paths); }
 extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;

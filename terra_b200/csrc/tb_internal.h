@@ -144,6 +144,7 @@ void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 void      tb_device_set_env_lit(TbDevice* dev, int on);
+void      tb_device_set_graph_paths(TbDevice* dev, size_t max_paths);
 void      tb_device_distribution_2d_sample(TbDevice* dev, const float* f, size_t nx, size_t ny, size_t n,
                                            const float* e1, const float* e2, float* out4);
 int       tb_cuda_device_count(void);

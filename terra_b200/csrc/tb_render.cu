@@ -114,6 +114,7 @@ struct TbCallParams {
     int      x, y, fbw, fbh;
     uint32_t sample_base, pad_;
     uint64_t seed;
+    void*    results;           // device-resident calls: the caller's full-framebuffer results array (k_finalize)
 };
 
 struct TbEventPair { cudaEvent_t a, b; };
@@ -174,7 +175,7 @@ struct TbDevice {
     int          tile_pixels;  // 1: waves walk the region in 8x4 pixel tiles (TERRA_B200_TILE=0 turns it off)
     int          tri_min, refetch_below;
     // CUDA-graph replay of small terra_render calls (launch-bound: ~45 launches for a 128x128 tile)
-    struct Graph { size_t w, h, spp; uint64_t epoch; cudaGraphExec_t exec; uint64_t launches, paths, last_use; };
+    struct Graph { size_t w, h, spp; int kind; uint64_t epoch; cudaGraphExec_t exec; uint64_t launches, paths, last_use; };
     std::vector<Graph> graphs;
     std::vector<uint64_t> graph_seen;      // shapes rendered once without a graph (w | h << 20 | spp << 40, xor epoch)
     uint64_t     graph_epoch, graph_clock;  // epoch: bumped whenever a pointer or scene constant a graph baked in changes
@@ -1129,8 +1130,14 @@ struct TbFinalizeArgs {
     float* pixels; size_t pixels_pitch;                         // may be NULL
     int w, h, spp, tonemap;
     float exposure, inv_gamma;
+    const TbCallParams* call;  // non-NULL (graph replay of a device-resident call): results / pitch / region origin come from here
 };
 __global__ void __launch_bounds__(256) k_finalize(TbFinalizeArgs a) {
+    if (a.call) {
+        const TbCallParams c = *a.call;
+        a.results = (TerraRawIntegrationResult*)c.results + (size_t)c.y * (size_t)c.fbw + (size_t)c.x;
+        a.results_pitch = (size_t)c.fbw;
+    }
     const int n = a.w * a.h;
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const int i = p / a.w, j = p - i * a.w;
@@ -1505,11 +1512,11 @@ static void tb_finish_call(TbDevice* d, cudaStream_t st, bool whole_render) {
 // directly (a one-off call must not pay for capture + instantiation); the second captures; later ones replay.
 // Everything a graph bakes in — buffer addresses, scene constants, kernel choices — is covered by graph_epoch.
 template <typename Body>
-static TbDevice::Graph* tb_graph_for(TbDevice* d, cudaStream_t st, size_t w, size_t h, size_t spp, Body& body) {
+static TbDevice::Graph* tb_graph_for(TbDevice* d, cudaStream_t st, size_t w, size_t h, size_t spp, int kind, Body& body) {   // kind: 0 terra_render, 1 device-resident
     ++d->graph_clock;
     for (TbDevice::Graph& g : d->graphs)
-        if (g.w == w && g.h == h && g.spp == spp && g.epoch == d->graph_epoch) { g.last_use = d->graph_clock; return &g; }
-    const uint64_t tag = ((uint64_t)w | ((uint64_t)h << 20) | ((uint64_t)spp << 40)) ^ (d->graph_epoch * 0x9E3779B97F4A7C15ull);
+        if (g.w == w && g.h == h && g.spp == spp && g.kind == kind && g.epoch == d->graph_epoch) { g.last_use = d->graph_clock; return &g; }
+    const uint64_t tag = ((uint64_t)w | ((uint64_t)h << 20) | ((uint64_t)spp << 40) | ((uint64_t)kind << 63)) ^ (d->graph_epoch * 0x9E3779B97F4A7C15ull);
     bool seen = false;
     for (uint64_t t : d->graph_seen) seen = seen || t == tag;
     if (!seen) {
@@ -1545,7 +1552,7 @@ static TbDevice::Graph* tb_graph_for(TbDevice* d, cudaStream_t st, size_t w, siz
     TB_CUDA(cudaStreamEndCapture(st, &graph));
     d->capturing = false;
     TbDevice::Graph g;
-    g.w = w; g.h = h; g.spp = spp; g.epoch = d->graph_epoch; g.last_use = d->graph_clock;
+    g.w = w; g.h = h; g.spp = spp; g.kind = kind; g.epoch = d->graph_epoch; g.last_use = d->graph_clock;
     g.launches = d->stats.kernel_launches - before.kernel_launches;
     g.paths = d->stats.paths_traced - before.paths_traced;
     d->stats = before;                                     // the capture pass executed nothing
@@ -1585,16 +1592,17 @@ extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const Te
         fa.pixels = d->d_pixels; fa.pixels_pitch = w;
         fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = d->sc.tonemap;
         fa.exposure = d->sc.exposure; fa.inv_gamma = d->sc.inv_gamma;
+        fa.call = NULL;
         k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
         d->stats.kernel_launches += 1;
     };
     TbDevice::Graph* g = NULL;
-    if (d->graph_max_paths && npx * spp <= d->graph_max_paths && !d->counting) g = tb_graph_for(d, st, w, h, spp, body);
+    if (d->graph_max_paths && npx * spp <= d->graph_max_paths && !d->counting) g = tb_graph_for(d, st, w, h, spp, 0, body);
     if (g) {
         TbCallParams* hp = d->h_call;
         hp->cam = *cam;
         hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fb->width; hp->fbh = (int)fb->height;
-        hp->sample_base = 0; hp->pad_ = 0; hp->seed = seed;
+        hp->sample_base = 0; hp->pad_ = 0; hp->seed = seed; hp->results = NULL;
         TB_CUDA(cudaMemcpyAsync(d->d_call, hp, sizeof *hp, cudaMemcpyHostToDevice, st));
         TB_CUDA(cudaGraphLaunch(g->exec, st));
         d->stats.kernel_launches += g->launches;
@@ -1626,15 +1634,33 @@ extern "C" void tb_device_render_resident(TbDevice* d, const TbCameraFrame* cam,
         if (d->fb_capacity < npx) { tb_free(d->d_results); tb_free(d->d_pixels); d->d_results = NULL; d->d_pixels = NULL; d->fb_capacity = 0; }
     }
     TB_CUDA(cudaEventRecord(d->ev_call_a, st));
-    TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
-    tb_render_region(d, st, cam, fbw, fbh, x, y, w, h, sample_base, spp, seed, d->d_acc);
-    TbFinalizeArgs fa;
-    fa.acc = d->d_acc;
-    fa.results = (TerraRawIntegrationResult*)d_results + y * fbw + x; fa.results_pitch = fbw;
-    fa.pixels = NULL; fa.pixels_pitch = 0;
-    fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = 0; fa.exposure = 1.f; fa.inv_gamma = 1.f;
-    k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
-    d->stats.kernel_launches += 1;
+    auto body = [&](const TbCallParams* d_call) {
+        TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
+        tb_render_region(d, st, cam, fbw, fbh, x, y, w, h, sample_base, spp, seed, d->d_acc, d_call);
+        TbFinalizeArgs fa;
+        fa.acc = d->d_acc;
+        fa.results = (TerraRawIntegrationResult*)d_results + y * fbw + x; fa.results_pitch = fbw;
+        fa.pixels = NULL; fa.pixels_pitch = 0;
+        fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = 0; fa.exposure = 1.f; fa.inv_gamma = 1.f;
+        fa.call = d_call;
+        k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
+        d->stats.kernel_launches += 1;
+    };
+    TbDevice::Graph* g = NULL;
+    if (d->graph_max_paths && npx * spp <= d->graph_max_paths && !d->counting) g = tb_graph_for(d, st, w, h, spp, 1, body);
+    if (g) {
+        TbCallParams* hp = d->h_call;
+        hp->cam = *cam;
+        hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fbw; hp->fbh = (int)fbh;
+        hp->sample_base = (uint32_t)sample_base; hp->pad_ = 0; hp->seed = seed; hp->results = d_results;
+        TB_CUDA(cudaMemcpyAsync(d->d_call, hp, sizeof *hp, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaGraphLaunch(g->exec, st));
+        d->stats.kernel_launches += g->launches;
+        d->stats.paths_traced += g->paths;
+        d->stats.graph_replays += 1;
+    } else {
+        body(NULL);
+    }
     tb_finish_call(d, st, true);
 }
 
@@ -1911,6 +1937,7 @@ extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
 }
 
 extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; d->graph_epoch++; }
+extern "C" void tb_device_set_graph_paths(TbDevice* d, size_t max_paths) { d->graph_max_paths = max_paths; }
 // Builds TbDevDist2D over `f` (ny rows of nx, device) into freshly allocated device arrays.
 static void tb_dist2d_build(TbDevice* d, cudaStream_t st, const float* d_f, int nx, int ny, float** cdf_out, float** rows_out,
                             float** marg_out, TbDevDist2D* out) {

@@ -598,4 +598,7 @@ def test_sample_split_and_row_split_equal_single_render(api, scenes, gpu):
     summed = render(parts)
     assert (summed["samples"] == spp).all()
     assert np.allclose(summed["acc"], whole["acc"], rtol=1e-5, atol=1e-6)
+    # the bands / sample ranges repeat one shape: those calls were replayed from a CUDA graph whose region origin,
+    # sample base and results pointer came through device memory — and still reproduced the single render above
+    assert s.stats().graph_replays >= 4
     s.destroy()
