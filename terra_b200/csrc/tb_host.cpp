@@ -267,6 +267,8 @@ struct TbScene {
     int               stack_bound;
     int               bvh_mode;
     float             commit_ms[4];   // last commit: tree build, flatten, quantise, upload
+    const TerraTexture* env_tex;      // environment texture of the last upload (NULL: constant environment)
+    const void*       env_pixels;
     TbDevice*         dev;
     uint64_t          seed;
     bool              seed_fixed;
@@ -304,6 +306,7 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     s->stack_bound = 0;
     s->bvh_mode = -1;
     memset(s->commit_ms, 0, sizeof s->commit_ms);
+    s->env_tex = NULL; s->env_pixels = NULL;
     s->dev = NULL;
     s->seed = 0;
     s->seed_fixed = false;
@@ -447,7 +450,13 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
 
     TbTextureTable table;
     TbDevAttr env = classify_attribute(&s->opts.environment_map, &table, "environment_map");
-    if (dirty_accelerator || s->dirty_lights) {
+    // An options-only commit keeps the device copy of the scene; a NEW environment texture is not in it yet
+    // (the environment is texture 0 of the table), so that takes the upload path as well.
+    const TerraTexture* env_tex = table.list.empty() ? NULL : table.list[0];
+    const void* env_pixels = env_tex ? env_tex->pixels : NULL;
+    const bool new_env_texture = env_tex != NULL && (env_tex != s->env_tex || env_pixels != s->env_pixels);
+    s->env_tex = env_tex; s->env_pixels = env_pixels;
+    if (dirty_accelerator || s->dirty_lights || new_env_texture) {
         typedef std::chrono::steady_clock Clock;
         auto ms_since = [](Clock::time_point t0) { return std::chrono::duration<float, std::milli>(Clock::now() - t0).count(); };
         Clock::time_point t0 = Clock::now();

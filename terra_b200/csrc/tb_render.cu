@@ -181,6 +181,7 @@ struct TbDevice {
     uint64_t     graph_epoch, graph_clock;  // epoch: bumped whenever a pointer or scene constant a graph baked in changes
     size_t       graph_max_paths;           // TERRA_B200_GRAPH_PATHS (0 = never use graphs)
     bool         capturing;
+    int          env_mode;                  // what terra_b200_set_env_lit asked for (0 / 1 / 2), re-applied at every commit
     TbCallParams *d_call, *h_call;
     int          sort_rays, sort_bounces;   // TERRA_B200_SORT (0 off, 1 octant, 2 octant + dominant axis) for the first TERRA_B200_SORT_BOUNCES bounces
 };
@@ -264,7 +265,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
     d->st_in = d->st_out = NULL; d->pipe_capacity = 0;
     d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
-    d->graph_epoch = 1; d->graph_clock = 0; d->capturing = false;
+    d->graph_epoch = 1; d->graph_clock = 0; d->capturing = false; d->env_mode = 0;
     d->d_call = tb_alloc<TbCallParams>(1);
     TB_CUDA(cudaHostAlloc((void**)&d->h_call, sizeof(TbCallParams), cudaHostAllocDefault));
     for (int k = 0; k < 2; ++k) { d->d_pipe_o3[k] = d->d_pipe_d3[k] = NULL; d->d_pipe_hit[k] = NULL; }
@@ -397,6 +398,7 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
     for (size_t i = 0; i < f->n_objects; ++i) sc.preset_mask |= 1 << f->materials[i].preset;
 }
 
+extern "C" void tb_device_set_env_lit(TbDevice* d, int on);
 extern "C" void tb_device_set_options(TbDevice* d, const TerraSceneOptions* o, const TbDevAttr* env) {
     TbDevScene& sc = d->sc;
     sc.env = *env;
@@ -407,6 +409,8 @@ extern "C" void tb_device_set_options(TbDevice* d, const TerraSceneOptions* o, c
     sc.exposure = o->manual_exposure;
     sc.gamma = o->gamma;
     sc.inv_gamma = 1.f / o->gamma;                      // `1.f / scene->opts.gamma`, Terra.c:582
+    d->graph_epoch++;                                   // graphs bake the scene constants in
+    if (d->env_mode == 2) tb_device_set_env_lit(d, 2);  // the importance map belongs to the environment of THIS commit
 }
 
 // ==================================================================================== K2: closest hit
@@ -1964,6 +1968,7 @@ static void tb_dist2d_build(TbDevice* d, cudaStream_t st, const float* d_f, int 
 extern "C" void tb_device_set_env_lit(TbDevice* d, int on) {
     TB_CUDA(cudaSetDevice(d->index));
     d->graph_epoch++;
+    d->env_mode = on;
     d->sc.env_lit = on ? 1 : 0;
     d->sc.env_nee = 0;
     tb_free(d->d_env_f); tb_free(d->d_env_cdf); tb_free(d->d_env_rows); tb_free(d->d_env_marg);

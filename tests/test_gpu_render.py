@@ -303,6 +303,32 @@ def test_env_importance_sampling_same_image_less_noise(api, scenes, gpu, integra
     assert np.allclose(nee[sky].mean(axis=0), brute[0][sky].mean(axis=0), rtol=0.02)
 
 
+def test_env_mode_2_survives_a_recommit(api, scenes, gpu):
+    """The extension mode is a property of the scene, not of one upload: after a re-commit with other options the
+    importance map is rebuilt for the environment of that commit and mode 2 renders what a fresh scene renders."""
+    w, h = 32, 20
+
+    def run(s, cam):
+        gpu.terra_b200_set_seed(s.h, 5)
+        return s.render(cam, w, h)[0]["acc"].copy()
+
+    s, cam = _open_scene(api, scenes, gpu, api.INTEGRATOR_DIRECT, 4, bounces=2)
+    gpu.terra_b200_set_env_lit(s.h, 2)
+    a = run(s, cam)
+    s.options().bounces = 3
+    s.commit()
+    b = run(s, cam)
+    s.destroy()
+    s2, cam2 = _open_scene(api, scenes, gpu, api.INTEGRATOR_DIRECT, 4, bounces=3)
+    gpu.terra_b200_set_env_lit(s2.h, 2)
+    want = run(s2, cam2)
+    gpu.terra_b200_set_env_lit(s2.h, 1)
+    brute = run(s2, cam2)
+    s2.destroy()
+    assert np.array_equal(b.view(np.uint32), want.view(np.uint32))
+    assert not np.array_equal(a, b) and not np.array_equal(want, brute)
+
+
 def test_env_mode_2_without_latlong_environment_is_mode_1(api, scenes, gpu):
     """A constant environment has no map to sample: mode 2 renders exactly what mode 1 renders."""
     w, h = 32, 20
@@ -515,6 +541,58 @@ def test_graph_replay_equals_direct_launches(api, scenes, gpu, monkeypatch):
     assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
     assert np.array_equal(outs[0][1].view(np.uint32), outs[1][1].view(np.uint32))
     assert (outs[1][0][..., 3].view(np.int32) == 12).all()
+
+
+def test_graph_cache_is_invalidated_by_commit_and_extension_switches(api, scenes, gpu):
+    """A captured graph bakes in scene constants and buffer addresses. After anything that changes them — a
+    re-commit with other options, the env-lit switch, a bigger call that moves the wave buffers — calls of the
+    old shape must render the NEW state: each is compared, bit for bit, with a fresh scene that never held a graph
+    for another state."""
+    w, h = 32, 32
+
+    def frames(s, cam, n):
+        out = []
+        for k in range(n):
+            gpu.terra_b200_set_seed(s.h, 77)
+            out.append(s.render(cam, w, h)[0]["acc"].copy())
+        return out
+
+    def fresh(bounces, integrator, env_lit=0):
+        s, cam = scenes.cornell(gpu, spp=4, bounces=bounces, integrator=integrator)
+        s.const_attr(s.options().environment_map, (0.3, 0.4, 0.5))
+        s.commit()
+        if env_lit:
+            gpu.terra_b200_set_env_lit(s.h, env_lit)
+        gpu.terra_b200_set_graph_paths(s.h, 0)                 # kernel by kernel: the yardstick
+        ref = frames(s, cam, 1)[0]
+        s.destroy()
+        return ref
+
+    s, cam = scenes.cornell(gpu, spp=4, bounces=2, integrator=api.INTEGRATOR_SIMPLE)
+    s.const_attr(s.options().environment_map, (0.3, 0.4, 0.5))
+    s.commit()
+    a = frames(s, cam, 4)                                       # direct, capture + replay, replay, replay
+    want = fresh(2, api.INTEGRATOR_SIMPLE)
+    assert all(np.array_equal(x.view(np.uint32), want.view(np.uint32)) for x in a)
+    assert s.stats().graph_replays >= 2
+    # 1. re-commit with other options
+    o = s.options()
+    o.bounces, o.integrator = 5, api.INTEGRATOR_DIRECT
+    s.commit()
+    b = frames(s, cam, 3)
+    want = fresh(5, api.INTEGRATOR_DIRECT)
+    assert all(np.array_equal(x.view(np.uint32), want.view(np.uint32)) for x in b)
+    # 2. extension switch
+    gpu.terra_b200_set_env_lit(s.h, 1)
+    c = frames(s, cam, 3)
+    want = fresh(5, api.INTEGRATOR_DIRECT, env_lit=1)
+    assert all(np.array_equal(x.view(np.uint32), want.view(np.uint32)) for x in c)
+    assert not np.array_equal(c[0], b[0])
+    # 3. a bigger call in between (wave and staging buffers are reallocated), then the old shape again
+    s.render(cam, 160, 128)
+    d = frames(s, cam, 3)
+    assert all(np.array_equal(x.view(np.uint32), want.view(np.uint32)) for x in d)
+    s.destroy()
 
 
 def test_stratified_rounds_spp_like_the_reference(api, scenes, gpu):
