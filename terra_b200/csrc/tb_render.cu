@@ -53,6 +53,10 @@ extern "C" void terra_log(const char* fmt, ...);
 #ifndef TB_SHADE_MIN_BLOCKS
 #define TB_SHADE_MIN_BLOCKS    1            // resident CTAs per SM the shade kernels are compiled for (register cap)
 #endif
+#ifndef TB_SHADE_MIN_BLOCKS_LIGHT
+#define TB_SHADE_MIN_BLOCKS_LIGHT TB_SHADE_MIN_BLOCKS      // the same for the two light presets (Diffuse, GGX), A/B builds
+#endif
+#define TB_SHADE_MINB(PRESET) (((PRESET) == 0 || (PRESET) == 2) ? TB_SHADE_MIN_BLOCKS_LIGHT : TB_SHADE_MIN_BLOCKS)
 #define TB_QUEUE_SENTINEL     0x7fffffff
 
 // ------------------------------------------------------------------------------------ RNG
@@ -838,7 +842,7 @@ __device__ __forceinline__ V3 tb_integrate_debug(const TbDevScene& sc, int integ
 #include "tb_distribution.cuh"
 
 template <int PRESET, int STAGE>
-__global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MIN_BLOCKS) k_shade(TbShadeArgs a) {
+__global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_shade(TbShadeArgs a) {
     const int count = *a.q_count;
     const int stride = gridDim.x * blockDim.x;
     const int rounds = (count + stride - 1) / stride;
