@@ -256,7 +256,7 @@ class Scene:
     def __init__(self, lib: TerraLib):
         self.lib = lib
         self.h = lib.terra_scene_create()
-        self.objects_base = None          # &objects[0]; stable while <= 64 objects
+        self.objects_base = None          # &objects[0]
         self.n_objects = 0
         self._keep = []                   # textures etc. referenced by raw pointer from attributes
         self.preset_overrides = dict(Scene.default_preset_overrides)   # name -> init function (tests plug the oracle's in)
@@ -279,8 +279,9 @@ class Scene:
         props = np.ascontiguousarray(props, dtype=np.float32)
         optr = self.lib.terra_scene_add_object(self.h, n)
         obj = optr.contents
-        if self.objects_base is None:
-            self.objects_base = C.addressof(obj)
+        # &objects[0]: the array moves when it grows past its capacity (64, 128, ...), so follow it on every add
+        # (and fill an object in before adding the next one: earlier Object references dangle after a move)
+        self.objects_base = C.addressof(obj) - self.n_objects * C.sizeof(Object)
         assert obj.triangles_count == n
         C.memmove(obj.triangles, _ptr(tris), tris.nbytes)
         C.memmove(obj.properties, _ptr(props), props.nbytes)

@@ -114,6 +114,31 @@ def test_pipelined_host_batches_equal_one_shot(api, scenes, gpu, monkeypatch):
     s.destroy()
 
 
+def test_two_hundred_objects_and_the_object_limit(api, scenes, gpu, oracle, bvh_mode):
+    """The leaf packing gives an object 8 bits (TerraBVH.c:155): 200 objects (beyond the reference's 64
+    preallocated slots, Q14) trace bit-exactly against the oracle's walk of the reference tree, object ids
+    above 127 included."""
+    rng = np.random.default_rng(17)
+    s = api.Scene(gpu)
+    for k in range(200):
+        c = rng.uniform(-20, 20, 3).astype(np.float32)
+        tris = (c + rng.uniform(-1.5, 1.5, (3 + k % 4, 3, 3))).astype(np.float32)
+        s.set_diffuse(s.add_object(tris), (0.5, 0.5, 0.5))
+    s.set_options()
+    s.commit()
+    assert s.n_objects == 200
+    o, d = cases.rays_for(s, api, scenes, 20_000)
+    got = s.trace_rays(o, d)
+    osc = api.OracleScene(oracle, s)
+    want = osc.trace_rays(o, d)
+    osc.destroy()
+    assert (want["t"] >= 0).mean() > 0.02
+    assert_hits(got, want, exact_ids=(bvh_mode == 0))
+    hit = got["t"] >= 0
+    assert (got["prim"][hit] & 0xff).max() > 127
+    s.destroy()
+
+
 def test_medium_scene_vs_oracle(api, scenes, gpu, oracle):
     """100k-triangle sphere field (config C2's geometry) and a 200k-triangle terrain: 200k incoherent
     rays against the oracle's canonical walk over the same tree, plus primary hits at 320x180."""
