@@ -360,6 +360,13 @@ void        terra_b200_job_wait(HTerraB200Job job);      /* block until every ti
 void        terra_b200_job_cancel(HTerraB200Job job);    /* skip tiles not started yet; returns once the running one ends */
 void        terra_b200_job_release(HTerraB200Job job);   /* wait, then free the handle */
 
+/* Re-fit instead of rebuild (the "refit" half of replacing terra_bvh_create, src/TerraBVH.c:128-244): after editing
+ * vertex positions / normals / texcoords of the committed objects IN PLACE (same objects, same triangle counts),
+ * every box of the tree is recomputed bottom-up on the GPU and the nodes are re-quantised; light triangle areas are
+ * refreshed. Closest hits afterwards are those of a fresh commit of the edited geometry (t, u, v bit-identical).
+ * Not for the reference tree (TERRA_B200_BVH_REFERENCE). Returns the device time of the refit kernels, ms. */
+float       terra_b200_refit(HTerraScene scene);
+
 /* Render calls of at most max_paths (pixel, sample) pairs whose shape (width, height, spp) repeats are replayed
  * from a CUDA graph instead of being launched kernel by kernel (same results; default 4M paths, environment
  * TERRA_B200_GRAPH_PATHS; 0 = never). Per-kernel trace timings in TerraB200Stats are not taken on replayed calls. */

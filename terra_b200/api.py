@@ -177,6 +177,7 @@ class TerraLib:
             sig("terra_b200_job_release", None, _vp)
             sig("terra_b200_distribution_2d_sample", None, _vp, _vp, _sz, _sz, _sz, _vp, _vp, _vp)
             sig("terra_b200_set_graph_paths", None, _vp, _sz)
+            sig("terra_b200_refit", C.c_float, _vp)
             sig("terra_b200_host_alloc", _vp, _sz)
             sig("terra_b200_host_free", None, _vp)
             sig("terra_b200_commit_ms", None, _vp, C.POINTER(C.c_float))

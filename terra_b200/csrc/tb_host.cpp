@@ -670,6 +670,44 @@ extern "C" void terra_b200_distribution_2d_sample(HTerraScene h, const float* f,
     std::lock_guard<std::mutex> guard(s->lock);
     tb_device_distribution_2d_sample(s->dev, f, nx, ny, n, e1, e2, out4);
 }
+// Re-fit the committed tree to vertex data edited in place (SURVEY §8f N1 "build / refit"): same objects, same
+// triangle counts, any new positions / normals / texcoords. Light areas are refreshed the way commit computes them
+// (Terra.c:208-215). The tree keeps its topology, so quality degrades with large motion; results do not.
+extern "C" float terra_b200_refit(HTerraScene h) {
+    TbScene* s = committed(h, "terra_b200_refit");
+    std::lock_guard<std::mutex> guard(s->lock);
+    if (s->dirty_objects) tb_fatal("terra_b200_refit: objects were added or cleared since the last commit (commit instead)");
+    if (s->bvh_mode == TB_BVH_REFERENCE) tb_fatal("terra_b200_refit: the reference tree's boxes carry its builder's +1e-4 merges and cannot be re-fitted (use the sah3 or lbvh tree)");
+    size_t total = 0;
+    std::vector<uint32_t> base(s->objects_pop);
+    for (size_t i = 0; i < s->objects_pop; ++i) { base[i] = (uint32_t)total; total += s->objects[i].triangles_count; }
+    static_assert(sizeof(TerraTriangle) == 36 && sizeof(TerraTriangleProperties) == 60, "record sizes the refit kernels assume");
+    std::vector<const float*> tris(s->objects_pop), props(s->objects_pop);
+    for (size_t i = 0; i < s->objects_pop; ++i) { tris[i] = (const float*)s->objects[i].triangles; props[i] = (const float*)s->objects[i].properties; }
+    std::vector<TbDevLight> lights(s->lights.size());
+    std::vector<float> light_area;
+    for (size_t l = 0; l < s->lights.size(); ++l) {
+        const size_t obj = s->lights[l].object;
+        float area = 0;
+        for (size_t j = 0; j < s->objects[obj].triangles_count; ++j) {
+            const float a = triangle_area(&s->objects[obj].triangles[j]);
+            s->lights[l].triangle_area[j] = a;
+            area += a;
+        }
+        V2 mid = { 0.5f, 0.5f };
+        s->lights[l].power = abi3(vmul(host_attr_eval(&s->objects[obj].material.emissive, mid), area * TB_PI));
+        s->lights[l].area = area;
+        lights[l].object = (int32_t)obj;
+        lights[l].tri_count = (uint32_t)s->objects[obj].triangles_count;
+        lights[l].tri_base = (uint32_t)light_area.size();
+        lights[l].area = area;
+        light_area.insert(light_area.end(), s->lights[l].triangle_area.begin(), s->lights[l].triangle_area.end());
+    }
+    float ms = 0.f;
+    tb_device_refit(s->dev, tris.data(), props.data(), base.data(), s->objects_pop, lights.data(), lights.size(),
+                    light_area.data(), light_area.size(), &ms);
+    return ms;
+}
 extern "C" void terra_b200_set_graph_paths(HTerraScene h, size_t max_paths) { tb_device_set_graph_paths(committed(h, "terra_b200_set_graph_paths")->dev, max_paths); }
 extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {

@@ -145,6 +145,8 @@ void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 void      tb_device_set_env_lit(TbDevice* dev, int on);
 void      tb_device_set_graph_paths(TbDevice* dev, size_t max_paths);
+void      tb_device_refit(TbDevice* dev, const float* const* obj_tris, const float* const* obj_props, const uint32_t* obj_base, size_t n_objects,
+                          const TbDevLight* lights, size_t n_lights, const float* light_area, size_t n_light_tris, float* ms_out);
 void      tb_device_distribution_2d_sample(TbDevice* dev, const float* f, size_t nx, size_t ny, size_t n,
                                            const float* e1, const float* e2, float* out4);
 int       tb_cuda_device_count(void);

@@ -1934,6 +1934,171 @@ extern "C" double tb_device_probe_bandwidth(int device_index, size_t bytes, int 
     return moved / (best * 1e-3) / 1e9;
 }
 
+// ==================================================================================== refit
+// Vertex positions (and normals / texcoords) edited in place, same topology: the tree keeps its shape and every
+// box is re-fitted on the GPU, bottom-up, then re-quantised — no rebuild, no flatten. The boxes are what a fresh
+// sah3 build gives for the same tree (a child box = exact union of its padded triangle boxes, min / max only), so
+// closest hits stay bit-identical to a fresh commit of the edited geometry.
+//   k_refit_gather    rank-ordered triangle / property records <- the objects' raw arrays (prim id rides in tris[].w)
+//   k_refit_parents   parent index + number of inner children per node (once per refit: the tree is immutable)
+//   k_refit_fit       one thread per node without inner children starts, the last child to arrive continues upwards
+//   k_refit_quantise  the host quantiser's arithmetic (double, outward rounding + one cell) per node
+__global__ void __launch_bounds__(256) k_refit_gather(const float* __restrict__ raw_tris, const float* __restrict__ raw_props,
+                                                      const uint32_t* __restrict__ obj_base, float4* tris, float4* props, int n_tris) {
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_tris; r += gridDim.x * blockDim.x) {
+        const float4 a = tris[(size_t)r * 3], b = tris[(size_t)r * 3 + 1], c = tris[(size_t)r * 3 + 2];
+        const uint32_t prim = __float_as_uint(a.w);
+        const size_t src = (size_t)obj_base[prim & 0xffu] + (prim >> 8);
+        const float* t = raw_tris + src * 9;
+        tris[(size_t)r * 3]     = make_float4(t[0], t[1], t[2], a.w);
+        tris[(size_t)r * 3 + 1] = make_float4(t[3], t[4], t[5], b.w);
+        tris[(size_t)r * 3 + 2] = make_float4(t[6], t[7], t[8], c.w);
+        const float* p = raw_props + src * 15;
+        float* q = (float*)(props + (size_t)r * 4);
+#pragma unroll
+        for (int k = 0; k < 15; ++k) q[k] = p[k];
+    }
+}
+__global__ void __launch_bounds__(256) k_refit_parents(const float4* __restrict__ nodes, int n_nodes, int* parent, int* need, int* arrive) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += gridDim.x * blockDim.x) {
+        const float4 q3 = nodes[(size_t)i * 4 + 3];
+        const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
+        need[i] = (r0 >= 0 ? 1 : 0) + (r1 >= 0 ? 1 : 0);
+        arrive[i] = 0;
+        if (r0 >= 0) parent[r0] = i;
+        if (r1 >= 0) parent[r1] = i;
+        if (i == 0) parent[0] = -1;
+    }
+}
+__device__ __forceinline__ float tb_pad_lo(float v) { return v - (1e-4f + 2e-6f * fabsf(v)); }   // tb_bvh.cpp pad_lo / pad_hi
+__device__ __forceinline__ float tb_pad_hi(float v) { return v + (1e-4f + 2e-6f * fabsf(v)); }
+__device__ __forceinline__ void tb_refit_child(const float4* nodes, const float4* tris, int ref, float* lo, float* hi) {
+    if (ref < 0) {
+        const float4* tp = tris + (size_t)(~ref) * 3;
+        const float4 a = __ldcg(tp), b = __ldcg(tp + 1), c = __ldcg(tp + 2);
+        const float xs[3][3] = { { a.x, b.x, c.x }, { a.y, b.y, c.y }, { a.z, b.z, c.z } };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float l = xs[k][0] < xs[k][1] ? xs[k][0] : xs[k][1]; if (xs[k][2] < l) l = xs[k][2];
+            float h = xs[k][0] > xs[k][1] ? xs[k][0] : xs[k][1]; if (xs[k][2] > h) h = xs[k][2];
+            lo[k] = tb_pad_lo(l); hi[k] = tb_pad_hi(h);
+        }
+    } else {
+        const float4* np = nodes + (size_t)ref * 4;
+        const float4 q0 = __ldcg(np), q1 = __ldcg(np + 1), q2 = __ldcg(np + 2);
+        lo[0] = fminf(q0.x, q1.z); lo[1] = fminf(q0.y, q1.w); lo[2] = fminf(q0.z, q2.x);
+        hi[0] = fmaxf(q0.w, q2.y); hi[1] = fmaxf(q1.x, q2.z); hi[2] = fmaxf(q1.y, q2.w);
+    }
+}
+__global__ void __launch_bounds__(256) k_refit_fit(float4* nodes, const float4* __restrict__ tris, const int* __restrict__ parent,
+                                                   const int* __restrict__ need, int* arrive, int n_nodes) {
+    const int i0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i0 >= n_nodes || need[i0] != 0) return;
+    int i = i0;
+    while (true) {
+        const float4 q3 = __ldcg(nodes + (size_t)i * 4 + 3);
+        float lo0[3], hi0[3], lo1[3], hi1[3];
+        tb_refit_child(nodes, tris, __float_as_int(q3.x), lo0, hi0);
+        tb_refit_child(nodes, tris, __float_as_int(q3.y), lo1, hi1);
+        __stcg(nodes + (size_t)i * 4,     make_float4(lo0[0], lo0[1], lo0[2], hi0[0]));
+        __stcg(nodes + (size_t)i * 4 + 1, make_float4(hi0[1], hi0[2], lo1[0], lo1[1]));
+        __stcg(nodes + (size_t)i * 4 + 2, make_float4(lo1[2], hi1[0], hi1[1], hi1[2]));
+        __threadfence();
+        const int p = parent[i];
+        if (p < 0) return;
+        if (atomicAdd(&arrive[p], 1) + 1 < need[p]) return;        // the other inner child is still on its way: it continues
+        __threadfence();
+        i = p;
+    }
+}
+__global__ void __launch_bounds__(256) k_refit_quantise(const float4* __restrict__ nodes, uint4* qnodes, int n_nodes,
+                                                        float l0, float l1, float l2, float c0, float c1, float c2) {
+    const double gl[3] = { (double)l0, (double)l1, (double)l2 }, gc[3] = { (double)c0, (double)c1, (double)c2 };
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += gridDim.x * blockDim.x) {
+        const float4 q0 = nodes[(size_t)i * 4], q1 = nodes[(size_t)i * 4 + 1], q2 = nodes[(size_t)i * 4 + 2], q3 = nodes[(size_t)i * 4 + 3];
+        const float q[12] = { q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w };
+        uint32_t g[12];
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double l = gl[k], cell = gc[k];
+                long long a = (long long)floor((q[6 * c + k] - l) / cell);
+                while (a > 0 && l + a * cell > q[6 * c + k]) --a;
+                a -= 1;
+                long long b = (long long)ceil((q[6 * c + 3 + k] - l) / cell);
+                while (b < 65535 && l + b * cell < q[6 * c + 3 + k]) ++b;
+                b += 1;
+                if (a < 0) a = 0;
+                if (b > 65535) b = 65535;
+                g[6 * c + k] = (uint32_t)a; g[6 * c + 3 + k] = (uint32_t)b;
+            }
+        uint4 w0, w1;
+        w0.x = g[0] | (g[1] << 16); w0.y = g[2] | (g[3] << 16); w0.z = g[4] | (g[5] << 16); w0.w = g[6] | (g[7] << 16);
+        w1.x = g[8] | (g[9] << 16); w1.y = g[10] | (g[11] << 16); w1.z = __float_as_uint(q3.x); w1.w = __float_as_uint(q3.y);
+        qnodes[(size_t)i * 2] = w0; qnodes[(size_t)i * 2 + 1] = w1;
+    }
+}
+
+// raw_tris: 9 floats per triangle, objects concatenated; raw_props: 15 floats per triangle; obj_base[o] = first
+// triangle of object o in those arrays. lights / light_area: the refreshed light table (same sizes as at commit).
+extern "C" void tb_device_refit(TbDevice* d, const float* const* obj_tris, const float* const* obj_props, const uint32_t* obj_base, size_t n_objects,
+                                const TbDevLight* lights, size_t n_lights, const float* light_area, size_t n_light_tris, float* ms_out) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    const int n_tris = d->sc.n_tris, n_nodes = d->sc.n_nodes;
+    cudaEvent_t e0, e1;
+    TB_CUDA(cudaEventCreate(&e0)); TB_CUDA(cudaEventCreate(&e1));
+    // the objects' own arrays go up as they are (object o at triangle offset obj_base[o]): no host-side gather
+    float* d_raw_t = tb_alloc<float>((size_t)n_tris * 9);
+    float* d_raw_p = tb_alloc<float>((size_t)n_tris * 15);
+    for (size_t o = 0; o < n_objects; ++o) {
+        const size_t cnt = (o + 1 < n_objects ? obj_base[o + 1] : (uint32_t)n_tris) - obj_base[o];
+        TB_CUDA(cudaMemcpyAsync(d_raw_t + (size_t)obj_base[o] * 9, obj_tris[o], cnt * 36, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(d_raw_p + (size_t)obj_base[o] * 15, obj_props[o], cnt * 60, cudaMemcpyHostToDevice, st));
+        d->stats.h2d_bytes += cnt * 96;
+    }
+    uint32_t* d_base = tb_upload(obj_base, n_objects, d);
+    int* d_parent = tb_alloc<int>((size_t)n_nodes);
+    int* d_need = tb_alloc<int>((size_t)n_nodes);
+    int* d_arrive = tb_alloc<int>((size_t)n_nodes);
+    TB_CUDA(cudaEventRecord(e0, st));
+    k_refit_gather<<<d->sm_count * 8, 256, 0, st>>>(d_raw_t, d_raw_p, d_base, d->d_tris, d->d_props, n_tris);
+    k_refit_parents<<<d->sm_count * 8, 256, 0, st>>>(d->d_nodes, n_nodes, d_parent, d_need, d_arrive);
+    k_refit_fit<<<(n_nodes + 255) / 256, 256, 0, st>>>(d->d_nodes, d->d_tris, d_parent, d_need, d_arrive, n_nodes);
+    d->stats.kernel_launches += 3;
+    if (d->d_qnodes) {
+        // the grid of the quantised nodes covers the scene box, i.e. the root's two child boxes (tb_bvh_quantize)
+        float root[12];
+        TB_CUDA(cudaMemcpyAsync(root, d->d_nodes, sizeof root, cudaMemcpyDeviceToHost, st));
+        TB_CUDA(cudaStreamSynchronize(st));
+        for (int k = 0; k < 3; ++k) {
+            const double lo = root[k] < root[6 + k] ? root[k] : root[6 + k];
+            const double hi = root[3 + k] > root[9 + k] ? root[3 + k] : root[9 + k];
+            double ext = hi - lo;
+            if (!(ext > 0)) ext = 1.0;
+            const double pad = ext * 1e-3;
+            d->grid_lo[k] = (float)(lo - pad);
+            d->grid_cell[k] = (float)((ext + 2 * pad) / 65535.0);
+        }
+        k_refit_quantise<<<d->sm_count * 8, 256, 0, st>>>(d->d_nodes, d->d_qnodes, n_nodes, d->grid_lo[0], d->grid_lo[1], d->grid_lo[2],
+                                                          d->grid_cell[0], d->grid_cell[1], d->grid_cell[2]);
+        d->stats.kernel_launches += 1;
+        tb_free(d->d_qnodes4); d->d_qnodes4 = NULL;             // the 4-wide A/B tree is not refitted
+    }
+    TB_CUDA(cudaEventRecord(e1, st));
+    if (n_lights) {
+        TB_CUDA(cudaMemcpyAsync(d->d_lights, lights, n_lights * sizeof(TbDevLight), cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(d->d_light_area, light_area, n_light_tris * sizeof(float), cudaMemcpyHostToDevice, st));
+    }
+    TB_CUDA(cudaStreamSynchronize(st));
+    TB_CUDA(cudaGetLastError());
+    if (ms_out) TB_CUDA(cudaEventElapsedTime(ms_out, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    tb_free(d_raw_t); tb_free(d_raw_p); tb_free(d_base); tb_free(d_parent); tb_free(d_need); tb_free(d_arrive);
+    d->graph_epoch++;                                            // the grid constants are kernel arguments of captured graphs
+}
+
 extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
     TB_CUDA(cudaSetDevice(d->index));
     unsigned long long c[3] = { 0, 0, 0 };

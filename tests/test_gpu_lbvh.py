@@ -99,3 +99,61 @@ def test_lbvh_hits_equal_sah3_hits_on_a_medium_terrain(api, scenes, gpu):
         assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), f
     assert (a["prim"] != b["prim"]).mean() < 0.01
     assert (a["t"] >= 0).mean() > 0.2
+
+
+# ----------------------------------------------------------------------------- refit (the other half of row N1)
+@pytest.mark.parametrize("mode", [1, 2], ids=["sah3_tree", "gpu_lbvh_tree"])
+def test_refit_gives_the_hits_of_a_fresh_commit(api, scenes, gpu, oracle, mode):
+    """terra_b200_refit after editing vertices in place: the tree keeps its topology, every box is re-fitted on
+    the GPU and re-quantised. Closest hits must be those of a fresh commit of the edited geometry (t bit-identical,
+    ids modulo exact-t ties, u / v bit-identical where the ids agree) and of the oracle's reference walk; a refit
+    with nothing moved changes nothing; renders (light areas refreshed) agree with the fresh scene's."""
+    import ctypes as C
+    import cases
+    gpu.terra_b200_set_bvh_mode(mode)
+    try:
+        s, cam, wh = cases.build(scenes, gpu, "field")
+        o, d = cases.rays_for(s, api, scenes, 30_000)
+        before = s.trace_rays(o, d)
+        assert gpu.terra_b200_refit(s.h) >= 0.0
+        assert np.array_equal(s.trace_rays(o, d).view(np.uint32), before.view(np.uint32))
+        objs = (api.Object * s.n_objects).from_address(s.objects_base)
+        copies = []
+        for k in range(s.n_objects):
+            n = objs[k].triangles_count
+            v = np.ctypeslib.as_array(C.cast(objs[k].triangles, C.POINTER(C.c_float)), (n, 3, 3))
+            v += (0.8 * np.sin(0.9 * v[..., [2, 0, 1]] + 0.5)).astype(np.float32)       # a smooth deformation, in place
+            pr = np.ctypeslib.as_array(C.cast(objs[k].properties, C.POINTER(C.c_float)), (n, 15))
+            copies.append((v.copy(), pr[:, :9].reshape(n, 3, 3).copy(), pr[:, 9:].reshape(n, 3, 2).copy()))
+        ms = gpu.terra_b200_refit(s.h)
+        got = s.trace_rays(o, d)
+        fresh = api.Scene(gpu)
+        for k, (v, nrm, tex) in enumerate(copies):
+            obj = fresh.add_object(v, nrm, tex)
+            C.memmove(C.byref(obj.material), C.byref(objs[k].material), C.sizeof(api.Material))
+        C.memmove(C.byref(fresh.options()), C.byref(s.options()), C.sizeof(api.SceneOptions))
+        fresh.commit()
+        want = fresh.trace_rays(o, d)
+        print(f"refit of {sum(c[0].shape[0] for c in copies)} triangles: {ms:.3f} ms on the device")
+        assert (bits(got["t"]) != bits(before["t"])).mean() > 0.05           # the geometry really moved
+        assert np.array_equal(bits(got["t"]), bits(want["t"]))
+        assert (got["prim"] != want["prim"]).mean() < 0.01
+        same = got["prim"] == want["prim"]
+        assert np.array_equal(bits(got["u"][same]), bits(want["u"][same])) and np.array_equal(bits(got["v"][same]), bits(want["v"][same]))
+        osc = api.OracleScene(oracle, fresh)
+        ref_walk = osc.trace_rays(o[:3000], d[:3000])
+        osc.destroy()
+        assert np.array_equal(bits(got["t"][:3000]), bits(ref_walk["t"]))
+        # shading after a refit: same seed, same camera rays; the two trees may order exact-t ties differently, nothing else
+        gpu.terra_b200_set_seed(s.h, 3); gpu.terra_b200_set_seed(fresh.h, 3)
+        a = s.render(cam, 64, 40)[0]["acc"]
+        b = fresh.render(cam, 64, 40)[0]["acc"]
+        assert np.isfinite(a).all() and (a.reshape(-1, 3) != b.reshape(-1, 3)).any(axis=1).mean() < 0.02
+        fresh.destroy()
+        s.destroy()
+    finally:
+        gpu.terra_b200_set_bvh_mode(1)
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
