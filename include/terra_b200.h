@@ -286,6 +286,12 @@ typedef struct {
     uint64_t nodes_visited;      /* only while counting is on (terra_b200_set_counting): 64-byte nodes fetched */
     uint64_t tris_tested;        /*   and triangles tested by the traversal kernel */
     uint64_t graph_replays;      /* terra_render calls replayed from a CUDA graph (small calls of a shape seen before) */
+    /* The camera-ray launches alone (they run the packet kernel; everything else — bounce, visibility and API rays —
+     * is the difference to the totals above): one roofline per kernel. */
+    uint64_t coherent_rays;
+    double   coherent_kernel_ms;
+    uint64_t coherent_kernel_launches;
+    uint64_t coherent_nodes_visited, coherent_tris_tested;
 } TerraB200Stats;
 
 int  terra_b200_device_count(void);

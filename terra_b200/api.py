@@ -96,7 +96,9 @@ class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64), ("paths_traced", C.c_uint64),
                 ("trace_kernel_ms", C.c_double), ("trace_kernel_launches", C.c_uint64),
                 ("render_ms", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
-                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64), ("graph_replays", C.c_uint64)]
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64), ("graph_replays", C.c_uint64),
+                ("coherent_rays", C.c_uint64), ("coherent_kernel_ms", C.c_double), ("coherent_kernel_launches", C.c_uint64),
+                ("coherent_nodes_visited", C.c_uint64), ("coherent_tris_tested", C.c_uint64)]
 
 
 HIT_DTYPE = np.dtype([("t", "<f4"), ("prim", "<u4"), ("u", "<f4"), ("v", "<f4")])

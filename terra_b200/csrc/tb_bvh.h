@@ -19,11 +19,6 @@ struct TbQuantBvh {
     float grid_lo[3], grid_cell[3];
 };
 void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out);
-struct TbQuantBvh4 {
-    std::vector<uint32_t> nodes;              // 16 words per 4-wide node (tb_trace_v5.cuh)
-    int stack_bound;
-};
-void tb_bvh_collapse4(const TbFlatBvh& flat, const TbQuantBvh& grid, TbQuantBvh4* out);
 
 void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
 // Conventional binned-SAH tree over x, y and z in the same node format (see tb_bvh.cpp).

@@ -524,17 +524,9 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         up.exact_boxes = s->bvh_mode == TB_BVH_REFERENCE ? 1 : 0;
         t0 = Clock::now();
         TbQuantBvh quant;
-        TbQuantBvh4 quant4;
         if (!up.exact_boxes) {
             tb_bvh_quantize(flat, &quant);
             up.qnodes = quant.nodes.data();
-            const char* ik = getenv("TERRA_B200_INCOHERENT"); const char* tk = getenv("TERRA_B200_TRACE");
-            if ((ik && strcmp(ik, "v5") == 0) || (tk && strcmp(tk, "v5") == 0)) {      // the 4-wide tree is an A/B option only
-                tb_bvh_collapse4(flat, quant, &quant4);
-                up.qnodes4 = quant4.nodes.data();
-                up.n_nodes4 = quant4.nodes.size() / 16;
-                up.stack_bound4 = quant4.stack_bound;
-            }
             memcpy(up.grid_lo, quant.grid_lo, sizeof up.grid_lo);
             memcpy(up.grid_cell, quant.grid_cell, sizeof up.grid_cell);
         }

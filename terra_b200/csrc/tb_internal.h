@@ -115,9 +115,6 @@ struct TbFlatScene {          // host staging of everything the device needs
     TbDevAttr            env;
     int                  stack_bound;
     const uint32_t*      qnodes;          // 8 words per node, or NULL (reference tree: float boxes only)
-    const uint32_t*      qnodes4;         // 16 words per 4-wide node (tb_trace_v5.cuh), or NULL
-    size_t               n_nodes4;
-    int                  stack_bound4;
     float                grid_lo[3], grid_cell[3];
     int                  exact_boxes;     // 1: reference tree -> reference box arithmetic in k_trace (tb_trace.cuh)
 };

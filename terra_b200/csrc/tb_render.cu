@@ -43,7 +43,9 @@ extern "C" void terra_log(const char* fmt, ...);
 
 // ------------------------------------------------------------------------------------ tunables
 #define TB_TRACE_THREADS      128          // threads per trace CTA
+#ifndef TB_TRACE_CTAS_PER_SM
 #define TB_TRACE_CTAS_PER_SM  8            // persistent grid = SMs x this
+#endif
 #define TB_STACK_SMEM         16           // traversal stack entries held in shared memory ...
 #define TB_STACK_LOCAL        112          // ... deeper entries spill to local memory
 #define TB_TRI_MIN            8            // rounds kernel: parked leaves needed before a triangle round
@@ -51,13 +53,13 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_REFETCH_BELOW      20           // dynamic fetch: refill the warp when fewer lanes are busy
 #define TB_SHADE_THREADS      256
 #ifndef TB_SHADE_MIN_BLOCKS
-#define TB_SHADE_MIN_BLOCKS    1            // resident CTAs per SM the shade kernels are compiled for (register cap)
+#define TB_SHADE_MIN_BLOCKS    1            // resident CTAs per SM the direct / debug shade kernels are compiled for (register cap)
 #endif
-#ifndef TB_SHADE_MIN_BLOCKS_LIGHT
-#define TB_SHADE_MIN_BLOCKS_LIGHT TB_SHADE_MIN_BLOCKS      // the same for the two light presets (Diffuse, GGX), A/B builds
+#ifndef TB_SHADE_MIN_BLOCKS_SIMPLE
+#define TB_SHADE_MIN_BLOCKS_SIMPLE 3        // ... and the simple-integrator ones (<= 85 registers)
 #endif
-#define TB_SHADE_MINB(PRESET) (((PRESET) == 0 || (PRESET) == 2) ? TB_SHADE_MIN_BLOCKS_LIGHT : TB_SHADE_MIN_BLOCKS)
 #define TB_QUEUE_SENTINEL     0x7fffffff
+#define TB_V6_OPT_DEFAULT      1            // k_trace_v6 control options (tb_trace_v6.cuh): bit 0 second pop, bit 1 second parking slot
 
 // ------------------------------------------------------------------------------------ RNG
 // Counter-based: splitmix64 over (path key, dimension). The reference draws BSDF/RR numbers from
@@ -91,7 +93,6 @@ enum {  // dimensions per bounce (16 reserved)
 };
 
 // ------------------------------------------------------------------------------------ device state
-#define TB_SORT_BINS 32          // direction bins of the optional queue reordering (k_bin_count / k_bin_scatter)
 
 struct TbWave {                // wavefront buffers, `capacity` path slots
     size_t   capacity;
@@ -107,7 +108,6 @@ struct TbWave {                // wavefront buffers, `capacity` path slots
     int*     matq;             // TB_PRESET_COUNT x capacity: slots binned by preset after the trace
     int*     auxq;             // aux ray ids to trace
     int*     counters;         // [0] fetch cursor, [1] queue count cur, [2] next, [3] aux count, [4..7] matq counts
-    int*     bins;             // 2 x TB_SORT_BINS: counts, then cursors, of the direction binning of the next queue
 };
 
 // What changes between two terra_render calls of the same shape. A call replayed from a CUDA graph reads
@@ -121,7 +121,7 @@ struct TbCallParams {
     void*    results;           // device-resident calls: the caller's full-framebuffer results array (k_finalize)
 };
 
-struct TbEventPair { cudaEvent_t a, b; };
+struct TbEventPair { cudaEvent_t a, b; int coherent; };
 
 struct TbDevice {
     int          index;
@@ -131,8 +131,6 @@ struct TbDevice {
     // owned device memory
     float4 *d_nodes, *d_tris, *d_props;
     uint4*  d_qnodes;
-    uint4*  d_qnodes4;       // 4-wide quantised nodes (tb_trace_v5.cuh)
-    int     stack_bound4;
     float   grid_lo[3], grid_cell[3];
     TbDevMaterial* d_mats;
     TbDevTexture*  d_texs;
@@ -168,11 +166,12 @@ struct TbDevice {
     TerraB200Stats stats;
     std::vector<TbEventPair> ev_pool;
     size_t       ev_used;
-    cudaEvent_t  ev_call_a, ev_call_b;
+    cudaEvent_t  ev_call_a, ev_call_b, ev_legacy;
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
-    int          v4_opt;            // k_trace_v4 OPT bits (tb_trace_v4.cuh)
+    int          v6_opt;            // k_trace_v6 OPT bits (tb_trace_v6.cuh)
+    int          fused_raygen;      // 1: camera rays are generated inside the packet kernel (no k_raygen, no ray arrays for bounce 0)
     int          coherent_kind;     // TB_K_* used for camera-ray launches when trace_kind is auto
     int          incoherent_kind;   // TB_K_* used for incoherent launches when trace_kind is auto
     int          warp_samples; // at most this many samples of one pixel share a warp (TERRA_B200_WARP_SAMPLES, default 32)
@@ -187,7 +186,6 @@ struct TbDevice {
     bool         capturing;
     int          env_mode;                  // what terra_b200_set_env_lit asked for (0 / 1 / 2), re-applied at every commit
     TbCallParams *d_call, *h_call;
-    int          sort_rays, sort_bounces;   // TERRA_B200_SORT (0 off, 1 octant, 2 octant + dominant axis) for the first TERRA_B200_SORT_BOUNCES bounces
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -218,7 +216,7 @@ extern "C" int tb_cuda_device_count(void) {
 static void tb_wave_free(TbWave* w) {
     tb_free(w->ray_o); tb_free(w->ray_d); tb_free(w->thr); tb_free(w->lo); tb_free(w->hit);
     tb_free(w->aux_o); tb_free(w->aux_d); tb_free(w->aux_hit);
-    tb_free(w->queue[0]); tb_free(w->queue[1]); tb_free(w->matq); tb_free(w->auxq); tb_free(w->bins);
+    tb_free(w->queue[0]); tb_free(w->queue[1]); tb_free(w->matq); tb_free(w->auxq);
     int* counters = w->counters;                 // lives as long as the device (holds the ray statistics)
     memset(w, 0, sizeof *w);
     w->counters = counters;
@@ -239,7 +237,6 @@ static void tb_wave_reserve(TbWave* w, size_t capacity) {
     w->queue[1] = tb_alloc<int>(capacity);
     w->matq = tb_alloc<int>(capacity * TB_PRESET_COUNT);
     w->auxq = tb_alloc<int>(capacity * 3);
-    w->bins = tb_alloc<int>(2 * TB_SORT_BINS);
 }
 
 extern "C" TbDevice* tb_device_create(int device_index) {
@@ -259,12 +256,12 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     memset(&d->sc, 0, sizeof d->sc);
     d->d_nodes = d->d_tris = d->d_props = NULL;
-    d->d_qnodes = NULL; d->d_qnodes4 = NULL; d->stack_bound4 = 0;
+    d->d_qnodes = NULL;
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
     d->stack_bound = 0;
     memset(&d->wave, 0, sizeof d->wave);
-    d->wave.counters = tb_alloc<int>(16);
-    TB_CUDA(cudaMemset(d->wave.counters, 0, 16 * sizeof(int)));
+    d->wave.counters = tb_alloc<int>(32);
+    TB_CUDA(cudaMemset(d->wave.counters, 0, 32 * sizeof(int)));
     d->fb_capacity = 0; d->d_results = NULL; d->d_pixels = NULL; d->d_acc = NULL; d->acc_capacity = 0;
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
     d->st_in = d->st_out = NULL; d->pipe_capacity = 0;
@@ -280,34 +277,36 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->counting = 0;
     d->exact_boxes = 0;
     {
-        const char* e = getenv("TERRA_B200_TRACE");
-        static const char* names[] = { "auto", "v1", "v2", "v3", "v3q", "quant", "ld128", "v4", "v4q", "packet", "v5" };
-        d->trace_kind = 0;
+        // A/B switches (profiles/ records what each one measured): TERRA_B200_TRACE forces one kernel for every
+        // launch; TERRA_B200_INCOHERENT / TERRA_B200_COHERENT choose it for bounce / visibility / API rays and for
+        // camera rays. walk = per-ray while-while (the work counters' kernel), v4 = rounds kernel of round 1,
+        // v6 = rounds kernel with sign-selected planes (tb_trace_v6.cuh), packet = one warp per 32-ray packet.
+        static const char* names[] = { "auto", "walk", "v4", "v6", "packet" };
+        auto kind_of = [&](const char* env, int dflt) {
+            const char* e = getenv(env);
+            for (int k = 0; e && k < 5; ++k) if (strcmp(e, names[k]) == 0) return k;
+            return dflt;
+        };
+        d->trace_kind = kind_of("TERRA_B200_TRACE", 0);
+        d->incoherent_kind = kind_of("TERRA_B200_INCOHERENT", 3);
+        d->coherent_kind = kind_of("TERRA_B200_COHERENT", 4);
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
         const char* ws = getenv("TERRA_B200_WARP_SAMPLES"); d->warp_samples = ws ? atoi(ws) : 32;
         const char* gp = getenv("TERRA_B200_GRAPH_PATHS"); d->graph_max_paths = gp ? (size_t)strtoull(gp, NULL, 10) : ((size_t)1 << 22);
-        const char* so = getenv("TERRA_B200_SORT"); d->sort_rays = so ? atoi(so) : 0;
-        const char* sb = getenv("TERRA_B200_SORT_BOUNCES"); d->sort_bounces = sb ? atoi(sb) : 2;
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
-        for (int k = 0; e && k < 11; ++k) if (strcmp(e, names[k]) == 0) d->trace_kind = k;
-        const char* vo = getenv("TERRA_B200_V4_OPT"); d->v4_opt = vo ? (atoi(vo) & 3) : 3;       // measured on B200: 256-bit loads +1.7 %, single pop +10 % (C3 1M)
-        const char* ik = getenv("TERRA_B200_INCOHERENT");      // kernel for bounce / visibility / API rays (A/B runs)
-        d->incoherent_kind = 8;                                 // TB_K_V4Q
-        for (int k = 1; ik && k < 11; ++k) if (strcmp(ik, names[k]) == 0) d->incoherent_kind = k;
-        const char* ck = getenv("TERRA_B200_COHERENT");         // kernel for camera rays (A/B runs)
-        d->coherent_kind = 9;                                   // TB_K_PACKET
-        for (int k = 1; ck && k < 10; ++k) if (strcmp(ck, names[k]) == 0) d->coherent_kind = k;
+        const char* vo = getenv("TERRA_B200_V6_OPT"); d->v6_opt = vo ? atoi(vo) : TB_V6_OPT_DEFAULT;
+        const char* fr = getenv("TERRA_B200_FUSED_RAYGEN"); d->fused_raygen = fr ? atoi(fr) : 1;
     }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
+    TB_CUDA(cudaEventCreateWithFlags(&d->ev_legacy, cudaEventDisableTiming));
     return d;
 }
 
 static void tb_scene_free(TbDevice* d) {
     tb_free(d->d_nodes); tb_free(d->d_tris); tb_free(d->d_props); tb_free(d->d_mats); tb_free(d->d_texs);
     tb_free(d->d_qnodes); d->d_qnodes = NULL;
-    tb_free(d->d_qnodes4); d->d_qnodes4 = NULL;
     tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
     for (void* p : d->tex_pixels) tb_free(p);
     d->tex_pixels.clear();
@@ -337,6 +336,7 @@ extern "C" void tb_device_destroy(TbDevice* d) {
     for (TbEventPair& e : d->ev_pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     cudaEventDestroy(d->ev_call_a);
     cudaEventDestroy(d->ev_call_b);
+    cudaEventDestroy(d->ev_legacy);
     cudaStreamDestroy(d->stream);
     delete d;
 }
@@ -361,10 +361,6 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
     d->d_tris = (float4*)tb_upload(f->tris, f->n_tris * 12, d);
     if (f->qnodes) {
         d->d_qnodes = (uint4*)tb_upload(f->qnodes, f->n_nodes * 8, d);
-        if (f->qnodes4 && f->stack_bound4 <= TB_STACK_SMEM + TB_STACK_LOCAL) {
-            d->d_qnodes4 = (uint4*)tb_upload(f->qnodes4, f->n_nodes4 * 16, d);
-            d->stack_bound4 = f->stack_bound4;
-        }
         memcpy(d->grid_lo, f->grid_lo, sizeof d->grid_lo);
         memcpy(d->grid_cell, f->grid_cell, sizeof d->grid_cell);
     }
@@ -525,17 +521,11 @@ struct TbTraceArgs {
     int           emit_prim;    // 1: write object|tri<<8 (API), 0: write rank (wavefront)
     unsigned long long* visit_counters;   // COUNT variant only: [0] nodes fetched, [1] triangles tested
     const uint4*  qnodes;       // quantised 32-byte nodes (tb_trace.cuh), or NULL
-    const uint4*  qnodes4;      // quantised 64-byte 4-wide nodes (tb_trace_v5.cuh), or NULL
     float         grid_lo[3], grid_cell[3];
-    int           tri_min, refetch_below;   // rounds kernel tunables (tb_trace_v3.cuh)
+    int           tri_min, refetch_below;   // rounds kernels: parked leaves needed for a triangle round; refill below this many live lanes
+    int           stack_smem;               // k_trace_v6: stack entries per lane held in (dynamic) shared memory
+    float4*       lo;                       // fused ray generation: zeroed for the paths that leave the scene (k_trace_packet<.., GEN>)
 };
-
-#include "tb_trace_v1.cuh"
-#include "tb_trace.cuh"
-#include "tb_trace_v3.cuh"
-#include "tb_trace_v4.cuh"
-#include "tb_trace_v5.cuh"
-#include "tb_trace_packet.cuh"
 
 // ==================================================================================== K1: ray generation
 struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot = s_local * n_pixels + p_local
@@ -549,13 +539,21 @@ struct TbBatch {               // which (pixel, sample) pairs a wave holds: slot
     int      sub;              // tiled: samples of one pixel that share a warp (power of two dividing n_samples, <= 32)
 };
 
-struct TbRaygenArgs {
-    TbBatch batch;
-    TbCameraFrame cam;
+// Everything a camera ray is a function of. The packet kernel and the first shade pass derive the ray from the
+// slot index with this instead of reading it back from HBM (`on`), k_raygen writes it out for the kernels that
+// cannot (work-counting walk, A/B kernels).
+struct TbGenArgs {
+    TbBatch batch;              // wave shape; x, y, fbw, fbh, sample_base and seed are NOT read on the device (see call)
     float   jitter;
+    int     on;                 // 0: rays come from the ray arrays
+    const TbCallParams* call;   // what differs between two calls of one shape — region origin, framebuffer size, seed, camera —
+                                // in device memory, so that the arguments of a kernel captured in a CUDA graph never change
+};
+
+struct TbRaygenArgs {
+    TbGenArgs gen;
     float4 *ray_o, *ray_d, *thr, *lo;
     int*    queue;
-    const TbCallParams* call;   // non-NULL: overrides batch.{x,y,fbw,fbh,sample_base,seed} and cam (graph replay)
 };
 
 // Region-linear index -> pixel offset inside the region. Tiled: consecutive indices fill an 8x4 pixel
@@ -586,7 +584,8 @@ __device__ __forceinline__ int tb_slot_of(const TbBatch& b, int p_local, int s_l
     return s_local * b.n_pixels + p_local;
 }
 
-__device__ __forceinline__ void tb_slot_to_pixel(const TbBatch& b, int slot, int* px, int* py, uint32_t* sample) {
+// -> pixel offset inside the region and sample index relative to the call's sample_base
+__device__ __forceinline__ void tb_slot_to_pixel(const TbBatch& b, int slot, int* rx_out, int* ry_out, uint32_t* sample) {
     int s_local, p_local;
     if (b.tiled) {
         const int sub = b.sub, P = 32 / sub, sg = b.n_samples / sub;
@@ -598,12 +597,8 @@ __device__ __forceinline__ void tb_slot_to_pixel(const TbBatch& b, int slot, int
         s_local = slot / b.n_pixels;
         p_local = slot - s_local * b.n_pixels;
     }
-    const int pr = b.p0 + p_local;
-    int rx, ry;
-    tb_region_pixel(b, pr, &rx, &ry);
-    *py = b.y + ry;
-    *px = b.x + rx;
-    *sample = b.sample_base + (uint32_t)(b.s0 + s_local);
+    tb_region_pixel(b, b.p0 + p_local, rx_out, ry_out);
+    *sample = (uint32_t)(b.s0 + s_local);
 }
 
 // terra_camera_perspective_sample + terra_transformf3 + terra_ray (Terra.c:555-560, 1783-1799)
@@ -625,22 +620,50 @@ __device__ __forceinline__ V3 tb_camera_dir(const TbCameraFrame& cam, int px, in
     return mtransform(rot, dir);
 }
 
-__global__ void __launch_bounds__(256) k_raygen(TbRaygenArgs a) {
-    if (a.call) {
-        const TbCallParams c = *a.call;
-        a.cam = c.cam;
-        a.batch.x = c.x; a.batch.y = c.y; a.batch.fbw = c.fbw; a.batch.fbh = c.fbh;
-        a.batch.sample_base = c.sample_base; a.batch.seed = c.seed;
+// The per-call values are loaded where a ray is generated, with volatile loads: hoisted out of a persistent
+// kernel's loop they would pin ~25 registers for the whole kernel (the line stays in L1).
+__device__ __forceinline__ float tb_ldv(const float* p) { float v; asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p)); return v; }
+__device__ __forceinline__ int tb_ldv(const int* p) { int v; asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p)); return v; }
+__device__ __forceinline__ uint32_t tb_ldv(const uint32_t* p) { uint32_t v; asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p)); return v; }
+__device__ __forceinline__ uint64_t tb_ldv(const uint64_t* p) { unsigned long long v; asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(v) : "l"(p)); return (uint64_t)v; }
+
+// Camera ray of wave slot `slot` (Terra.c:553-560): direction, origin (the camera position), and the path key that
+// rides in the .w lanes of the ray records.
+__device__ __forceinline__ V3 tb_gen_ray(const TbGenArgs& g, int slot, uint64_t* key_out, V3* origin_out) {
+    const TbCallParams* c = g.call;
+    int rx, ry; uint32_t s_rel;
+    tb_slot_to_pixel(g.batch, slot, &rx, &ry, &s_rel);
+    const int px = tb_ldv(&c->x) + rx, py = tb_ldv(&c->y) + ry;
+    const int fbw = tb_ldv(&c->fbw), fbh = tb_ldv(&c->fbh);
+    const uint32_t sample = tb_ldv(&c->sample_base) + s_rel;
+    const uint64_t key = tb_path_key(tb_ldv(&c->seed), (uint32_t)(py * fbw + px), sample);
+    const float r1 = tb_randf_pcg(key, TB_DIM_JITTER_X), r2 = tb_randf_pcg(key, TB_DIM_JITTER_Y);
+    TbCameraFrame cam;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) cam.rot[i][j] = tb_ldv(&c->cam.rot[i][j]);
+        cam.pos[i] = tb_ldv(&c->cam.pos[i]);
     }
-    const int n = a.batch.n_pixels * a.batch.n_samples;
+    cam.tan_half_fov = tb_ldv(&c->cam.tan_half_fov);
+    *key_out = key;
+    *origin_out = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
+    return tb_camera_dir(cam, px, py, fbw, fbh, g.jitter, r1, r2);
+}
+
+#include "tb_trace.cuh"
+#include "tb_trace_v4.cuh"
+#include "tb_trace_v6.cuh"
+#include "tb_trace_packet.cuh"
+
+// ==================================================================================== K1: ray generation kernel
+__global__ void __launch_bounds__(256) k_raygen(TbRaygenArgs a) {
+    const int n = a.gen.batch.n_pixels * a.gen.batch.n_samples;
     for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
-        int px, py; uint32_t sample;
-        tb_slot_to_pixel(a.batch, slot, &px, &py, &sample);
-        const uint64_t key = tb_path_key(a.batch.seed, (uint32_t)(py * a.batch.fbw + px), sample);
-        const float r1 = tb_randf_pcg(key, TB_DIM_JITTER_X), r2 = tb_randf_pcg(key, TB_DIM_JITTER_Y);
-        const V3 d = tb_camera_dir(a.cam, px, py, a.batch.fbw, a.batch.fbh, a.jitter, r1, r2);
+        uint64_t key; V3 o;
+        const V3 d = tb_gen_ray(a.gen, slot, &key, &o);
         // the path key rides in the .w lanes of the ray so later stages need no extra array
-        a.ray_o[slot] = make_float4(a.cam.pos[0], a.cam.pos[1], a.cam.pos[2], __uint_as_float((uint32_t)key));
+        a.ray_o[slot] = make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)key));
         a.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float((uint32_t)(key >> 32)));
         a.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
         a.lo[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -671,7 +694,11 @@ __global__ void __launch_bounds__(256) k_pack_rays(size_t n, const float* o3, co
 // c*v + b*u + a*(1-u-v), attributes evaluated, skewed tangent frame built.
 struct TbHitInfo { int rank, object, preset; V3 a, b, c; V2 texcoord; };
 
-__device__ __forceinline__ TbSurface tb_surface_init(const TbDevScene& sc, int rank, V3 point, TbHitInfo* info) {
+// `tag` = object | preset << 8: the trace kernels leave it in the .z lane of a wavefront hit record (the intersector's
+// u, v are not used by shading), so the material record is requested together with the triangle, not after it.
+__device__ __forceinline__ TbSurface tb_surface_init(const TbDevScene& sc, int rank, int tag, V3 point, TbHitInfo* info) {
+    const TbDevMaterial* m = sc.materials + (tag & 0xff);
+    const int cnt = m->attr_count;
     const float4* tp = sc.tris + (size_t)rank * 3;
     const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
     const float4* pp = sc.props + (size_t)rank * 4;
@@ -679,7 +706,6 @@ __device__ __forceinline__ TbSurface tb_surface_init(const TbDevScene& sc, int r
     const V3 a = v3(ta.x, ta.y, ta.z), b = v3(tb.x, tb.y, tb.z), c = v3(tc.x, tc.y, tc.z);
     const V3 na = v3(p0.x, p0.y, p0.z), nb = v3(p0.w, p1.x, p1.y), nc = v3(p1.z, p1.w, p2.x);
     const V2 t_a = { p2.y, p2.z }, t_b = { p2.w, p3.x }, t_c = { p3.y, p3.z };
-    const int tag = __float_as_int(tb.w);
     info->rank = rank; info->object = tag & 0xff; info->preset = (tag >> 8) & 0xff;
     info->a = a; info->b = b; info->c = c;
 
@@ -696,8 +722,6 @@ __device__ __forceinline__ TbSurface tb_surface_init(const TbDevScene& sc, int r
     tex.x = (t_c.x * uy + t_b.x * ux) + t_a.x * uw;
     tex.y = (t_c.y * uy + t_b.y * ux) + t_a.y * uw;
     info->texcoord = tex;
-    const TbDevMaterial* m = sc.materials + info->object;
-    const int cnt = m->attr_count;
     s.a0 = cnt > 0 ? tb_attr_eval(m->attr[0], sc.textures, tex, point) : v3s(0.f);
     s.a1 = cnt > 1 ? tb_attr_eval(m->attr[1], sc.textures, tex, point) : v3s(0.f);
     s.a2 = cnt > 2 ? tb_attr_eval(m->attr[2], sc.textures, tex, point) : v3s(0.f);
@@ -724,6 +748,8 @@ struct TbShadeArgs {
     int*  aux_count;
     int   bounce;
     int   env_base;            // aux id of slot s's environment visibility ray = env_base + s
+    TbGenArgs gen;             // gen.on (first bounce after a fused-raygen trace): the ray is derived from the slot, throughput is 1,
+                               // and the radiance is stored, not added (nothing initialised the path state of a path that hit)
 };
 
 // Warp-aggregated append; every lane of the warp must call it (full mask).
@@ -739,7 +765,7 @@ __device__ __forceinline__ int tb_append(int* counter, bool pred) {
 
 // One explicit light sample: terra_scene_pick_light + terra_light_pick_triangle +
 // terra_light_sample_triangle (Terra.c:1592-1621, 1662-1697), randoms as at :1370-1388.
-struct TbLightSample { int light, tri; uint32_t rank; V3 pos, norm; float tri_area; };
+struct TbLightSample { int light, tri, object; uint32_t rank; V3 pos, norm; float tri_area; };
 
 __device__ __forceinline__ TbLightSample tb_sample_light(const TbDevScene& sc, uint64_t key, uint32_t dim0) {
     TbLightSample ls;
@@ -751,7 +777,7 @@ __device__ __forceinline__ TbLightSample tb_sample_light(const TbDevScene& sc, u
     const float e_tri = tb_randf_libc(key, dim0 + TB_DIM_TRI_PICK);
     long long ti = (long long)(e_tri * (float)L.tri_count);
     if (ti > (long long)L.tri_count - 1) ti = (long long)L.tri_count - 1;
-    ls.light = (int)li; ls.tri = (int)ti;
+    ls.light = (int)li; ls.tri = (int)ti; ls.object = L.object;
     ls.rank = sc.light_tri_rank[L.tri_base + ti];
     ls.tri_area = sc.light_tri_area[L.tri_base + ti];
     const float e1 = tb_randf_libc(key, dim0 + TB_DIM_LIGHT_U), e2 = tb_randf_libc(key, dim0 + TB_DIM_LIGHT_V);
@@ -822,7 +848,7 @@ __device__ __forceinline__ V3 tb_integrate_debug(const TbDevScene& sc, int integ
             const V3 bo = tb_offset_origin(tb_surface_ray_origin(s, point), wi);
             const V3 bpoint = vadd(bo, vmul(wi, bh.x));
             TbHitInfo binfo;
-            const TbSurface bsurf = tb_surface_init(sc, __float_as_int(bh.y), bpoint, &binfo);
+            const TbSurface bsurf = tb_surface_init(sc, __float_as_int(bh.y), __float_as_int(bh.z), bpoint, &binfo);
             if (binfo.object == sc.lights[ls.light].object) {
                 const float NoW = vdot(bsurf.n, vneg(wi));
                 if (NoW > 0) {
@@ -841,12 +867,18 @@ __device__ __forceinline__ V3 tb_integrate_debug(const TbDevScene& sc, int integ
 
 #include "tb_distribution.cuh"
 
-template <int PRESET, int STAGE>
-__global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_shade(TbShadeArgs a) {
+// MODE: the integrator family the kernel is compiled for — 0 simple (Terra.c:1339-1347), 1 direct / direct MIS
+// (:1349-1587, plus the explicit environment samples of env-lit mode 2), 2 the debug views (:1140-1337). One kernel
+// for all of them carried the registers of the MIS path (104-118, two CTAs per SM) through the simple integrator
+// every benchmark runs: ncu r1w showed it latency-bound at a quarter of the SM's warps.
+enum { TB_SHADE_SIMPLE = 0, TB_SHADE_DIRECT = 1, TB_SHADE_DEBUG = 2 };
+template <int PRESET, int STAGE, int MODE>
+__global__ void __launch_bounds__(TB_SHADE_THREADS, MODE == TB_SHADE_SIMPLE ? TB_SHADE_MIN_BLOCKS_SIMPLE : TB_SHADE_MIN_BLOCKS) k_shade(TbShadeArgs a) {
     const int count = *a.q_count;
     const int stride = gridDim.x * blockDim.x;
     const int rounds = (count + stride - 1) / stride;
     const TbDevScene& sc = a.sc;
+    const bool first = a.gen.on != 0;
     for (int it = 0; it < rounds; ++it) {
         const int i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         const bool valid = i < count;
@@ -856,7 +888,14 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
         float4 o4 = make_float4(0, 0, 0, 0), d4 = o4;
         if (valid) {
             slot = a.q[i];
-            o4 = a.ray_o[slot]; d4 = a.ray_d[slot];
+            if (first) {
+                uint64_t k0; V3 go;
+                const V3 gd = tb_gen_ray(a.gen, slot, &k0, &go);
+                o4 = make_float4(go.x, go.y, go.z, __uint_as_float((uint32_t)k0));
+                d4 = make_float4(gd.x, gd.y, gd.z, __uint_as_float((uint32_t)(k0 >> 32)));
+            } else {
+                o4 = a.ray_o[slot]; d4 = a.ray_d[slot];
+            }
             const float4 h4 = a.hit[slot];
             const uint64_t key = ((uint64_t)__float_as_uint(d4.w) << 32) | __float_as_uint(o4.w);
             const uint32_t dim0 = 2u + (uint32_t)a.bounce * TB_DIMS_PER_BOUNCE;
@@ -864,13 +903,13 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
             const V3 ro = tb_offset_origin(v3(o4.x, o4.y, o4.z), d);
             const V3 point = vadd(ro, vmul(d, h4.x));                        // terra_ray_pos, TerraGeometry.c:9-12
             TbHitInfo info;
-            TbSurface s = tb_surface_init(sc, __float_as_int(h4.y), point, &info);
+            TbSurface s = tb_surface_init(sc, __float_as_int(h4.y), __float_as_int(h4.z), point, &info);
             const V3 wo = vneg(d);
             const int integ = sc.integrator;
-            const bool dbg_mis = integ == kTerraIntegratorDebugMisWeights;            // bounce 0 only (host loop)
-            const bool direct = integ == kTerraIntegratorDirect || integ == kTerraIntegratorDirectMis || dbg_mis;
-            const bool mis = integ == kTerraIntegratorDirectMis || dbg_mis;
-            const bool debug = integ > kTerraIntegratorDirectMis;
+            const bool debug = MODE == TB_SHADE_DEBUG;
+            const bool dbg_mis = debug && integ == kTerraIntegratorDebugMisWeights;   // bounce 0 only (host loop)
+            const bool direct = MODE == TB_SHADE_DIRECT || dbg_mis;
+            const bool mis = (MODE == TB_SHADE_DIRECT && integ == kTerraIntegratorDirectMis) || dbg_mis;
 
             const bool env_nee = sc.env_nee && direct && !dbg_mis;                    // extension: explicit environment samples
             if (STAGE == 0) {
@@ -895,8 +934,8 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
                 }
             } else {
                 // ---- terra_integrate (Terra.c:1099-1138)
-                const float4 t4 = a.thr[slot];
-                V3 thr = v3(t4.x, t4.y, t4.z);
+                V3 thr = v3s(1.f);
+                if (!first) { const float4 t4 = a.thr[slot]; thr = v3(t4.x, t4.y, t4.z); }
                 V3 Lo = v3s(0.f);
                 if (debug) {
                     Lo = tb_integrate_debug(sc, integ, s, info, point, v3(o4.x, o4.y, o4.z), wo, thr, key, dim0, a.aux_hit + (size_t)slot * 2, PRESET);
@@ -920,7 +959,7 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
                                 const V3 lo_ = tb_offset_origin(tb_surface_ray_origin(s, point), wi);
                                 const V3 lpoint = vadd(lo_, vmul(wi, ah.x));
                                 TbHitInfo linfo;
-                                const TbSurface lsurf = tb_surface_init(sc, (int)ls.rank, lpoint, &linfo);
+                                const TbSurface lsurf = tb_surface_init(sc, (int)ls.rank, ls.object, lpoint, &linfo);
                                 const float light_pdf = vsqlen(p_to_light) / fabsf(cosl * ls.tri_area);
                                 if (!mis) {                                    // :1417-1422
                                     const V3 f = tb_bsdf_eval(PRESET, s, wi, wo);
@@ -948,7 +987,7 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
                                 const V3 bo = tb_offset_origin(tb_surface_ray_origin(s, point), wi2);
                                 const V3 bpoint = vadd(bo, vmul(wi2, bh.x));
                                 TbHitInfo binfo;
-                                const TbSurface bsurf = tb_surface_init(sc, __float_as_int(bh.y), bpoint, &binfo);
+                                const TbSurface bsurf = tb_surface_init(sc, __float_as_int(bh.y), __float_as_int(bh.z), bpoint, &binfo);
                                 if (binfo.object == sc.lights[ls.light].object) {
                                     const float NoW = vdot(bsurf.n, vneg(wi2));
                                     if (NoW > 0) {
@@ -999,7 +1038,9 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
                     }
                     Lo = vpoint(Lo, thr);
                 }
-                if (Lo.x != 0.f || Lo.y != 0.f || Lo.z != 0.f) {
+                if (first) {
+                    a.lo[slot] = make_float4(Lo.x, Lo.y, Lo.z, 0.f);                            // Lo = 0 + radiance
+                } else if (Lo.x != 0.f || Lo.y != 0.f || Lo.z != 0.f) {
                     const float4 l4 = a.lo[slot];
                     a.lo[slot] = make_float4(l4.x + Lo.x, l4.y + Lo.y, l4.z + Lo.z, 0.f);   // Lo = Lo + radiance, :1063
                 }
@@ -1063,12 +1104,20 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, TB_SHADE_MINB(PRESET)) k_sha
 // terra_attribute_eval(&environment_map, &ray.direction, ...): the direction is the lat-long lookup's
 // argument, and what a 2-D texture callback would read as its uv.
 __global__ void __launch_bounds__(256) k_miss(TbDevScene sc, const int* q, const int* q_count, const float4* ray_d,
-                                               const float4* hit, const float4* thr, float4* lo) {
+                                               const float4* hit, const float4* thr, float4* lo, TbGenArgs gen) {
     const int count = *q_count;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const int slot = q[i];
+        const int slot = q ? q[i] : i;
         if (hit[slot].x >= 0.f) continue;
-        const float4 d4 = ray_d[slot], t4 = thr[slot], l4 = lo[slot];
+        float4 d4, t4 = make_float4(1.f, 1.f, 1.f, 0.f);
+        if (gen.on) {                   // first bounce after a fused-raygen trace (the packet kernel zeroed lo of these paths)
+            uint64_t k0; V3 go;
+            const V3 gd = tb_gen_ray(gen, slot, &k0, &go);
+            d4 = make_float4(gd.x, gd.y, gd.z, 0.f);
+        } else {
+            d4 = ray_d[slot]; t4 = thr[slot];
+        }
+        const float4 l4 = lo[slot];
         const V3 d = v3(d4.x, d4.y, d4.z);
         V2 uv; uv.x = d.x; uv.y = d.y;
         const V3 env = tb_attr_eval(sc.env, sc.textures, uv, d);
@@ -1200,69 +1249,21 @@ __global__ void k_bsdf_kat(TbDevScene sc, int object, size_t n, const float* e12
 // ==================================================================================== host-side launchers
 // counters layout (ints): [0] trace fetch cursor  [1] live paths this bounce  [2] live paths next bounce
 // [3] visibility rays  [4..7] per-preset hit counts  [8..9] u64 rays traced (statistics)
+// [10..13] u64 nodes fetched, triangles tested by the incoherent-ray launches (counting variants only)
+// [14..15] u64 camera rays  [16..19] u64 nodes, triangles of the camera-ray launches
+#define TB_COUNTER_INTS 32
 __global__ void k_counters(int* c, int mode, int value) {
     unsigned long long* rays = (unsigned long long*)(c + 8);
+    unsigned long long* cam_rays = (unsigned long long*)(c + 14);
     switch (mode) {
-        case 0: c[0] = 0; c[1] = value; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)value; break;   // new wave = its first bounce begins
+        case 0: c[0] = 0; c[1] = value; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0;            // new wave = its first bounce begins
+                *rays += (unsigned long long)value; *cam_rays += (unsigned long long)value; break;
         case 1: c[0] = 0; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)c[1]; break;   // bounce begins
         case 2: c[0] = 0; *rays += (unsigned long long)c[3]; break;                                  // before the visibility trace
         case 3: c[1] = c[2]; c[0] = 0; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)c[1]; break;   // bounce ends, the next one begins
         case 4: *rays += (unsigned long long)value; c[0] = 0; break;                                 // stand-alone trace of `value` rays
-        default: *rays = 0; c[10] = c[11] = c[12] = c[13] = 0; break;
-    }
-}
-
-// ---- direction binning of the next bounce's queue (TERRA_B200_SORT=1|2; A/B option, off by default)
-// The rays a shade pass emits sit in the queue in slot order: a warp of the next trace launch gets 32 rays
-// leaving (nearly) one point in 32 unrelated directions. Reordering the queue ids — the rays stay where they
-// are — so that a warp's rays share their direction octant (mode 1) or octant and dominant axis (mode 2)
-// makes the lanes agree on near / far children. Two passes over the ids: histogram, then scatter at
-// warp-aggregated cursors. Results do not depend on the order of the queue.
-__device__ __forceinline__ int tb_dir_bin(float4 d, int mode) {
-    int key = (d.x < 0.f ? 1 : 0) | (d.y < 0.f ? 2 : 0) | (d.z < 0.f ? 4 : 0);
-    if (mode >= 2) {
-        const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-        const int major = ax >= ay ? (ax >= az ? 0 : 2) : (ay >= az ? 1 : 2);
-        key |= major << 3;
-    }
-    return key;
-}
-__global__ void __launch_bounds__(256) k_bin_count(const int* __restrict__ q, const int* __restrict__ q_count,
-                                                   const float4* __restrict__ ray_d, int mode, int* __restrict__ bins) {
-    __shared__ int s_bins[TB_SORT_BINS];
-    if (threadIdx.x < TB_SORT_BINS) s_bins[threadIdx.x] = 0;
-    __syncthreads();
-    const int count = *q_count;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
-        atomicAdd(&s_bins[tb_dir_bin(ray_d[q[i]], mode)], 1);
-    __syncthreads();
-    if (threadIdx.x < TB_SORT_BINS && s_bins[threadIdx.x]) atomicAdd(&bins[threadIdx.x], s_bins[threadIdx.x]);
-}
-__global__ void __launch_bounds__(256) k_bin_scatter(const int* __restrict__ q, const int* __restrict__ q_count,
-                                                     const float4* __restrict__ ray_d, int mode, int* __restrict__ bins,
-                                                     int* __restrict__ out) {
-    __shared__ int s_base[TB_SORT_BINS];
-    if (threadIdx.x == 0) {
-        int acc = 0;
-        for (int b = 0; b < TB_SORT_BINS; ++b) { s_base[b] = acc; acc += bins[b]; }
-    }
-    __syncthreads();
-    int* cursors = bins + TB_SORT_BINS;
-    const int count = *q_count;
-    const int stride = gridDim.x * blockDim.x;
-    const int rounds = (count + stride - 1) / stride;
-    const unsigned lane = threadIdx.x & 31u;
-    for (int it = 0; it < rounds; ++it) {
-        const int i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
-        const bool valid = i < count;
-        int slot = 0, key = TB_SORT_BINS;                 // invalid lanes share a dummy key
-        if (valid) { slot = q[i]; key = tb_dir_bin(ray_d[slot], mode); }
-        const unsigned peers = __match_any_sync(0xffffffffu, key);
-        const int leader = __ffs(peers) - 1;
-        int base = 0;
-        if (valid && (int)lane == leader) base = atomicAdd(&cursors[key], __popc(peers));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (valid) out[s_base[key] + base + __popc(peers & ((1u << lane) - 1u))] = slot;
+        case 5: *rays += (unsigned long long)value; *cam_rays += (unsigned long long)value; c[0] = 0; break;   // ... of camera rays
+        default: for (int k = 8; k < 20; ++k) c[k] = 0; break;
     }
 }
 
@@ -1274,128 +1275,147 @@ static size_t tb_batch_capacity() {
     return cap;
 }
 
-static TbEventPair* tb_event_pair(TbDevice* d) {
+static TbEventPair* tb_event_pair(TbDevice* d, int coherent) {
     if (d->ev_used == d->ev_pool.size()) {
         TbEventPair e;
         TB_CUDA(cudaEventCreate(&e.a));
         TB_CUDA(cudaEventCreate(&e.b));
+        e.coherent = 0;
         d->ev_pool.push_back(e);
     }
+    d->ev_pool[d->ev_used].coherent = coherent;
     return &d->ev_pool[d->ev_used++];
 }
 
-// Sum the device times of the trace launches recorded since the last drain. Stream must be idle.
+// Sum the device times of the trace launches recorded since the last drain, per kind of launch (camera rays /
+// everything else: they run different kernels with different roofs). Stream must be idle.
 static void tb_drain_events(TbDevice* d) {
     for (size_t i = 0; i < d->ev_used; ++i) {
         float ms = 0.f;
         TB_CUDA(cudaEventElapsedTime(&ms, d->ev_pool[i].a, d->ev_pool[i].b));
         d->stats.trace_kernel_ms += ms;
         d->stats.trace_kernel_launches += 1;
+        if (d->ev_pool[i].coherent) { d->stats.coherent_kernel_ms += ms; d->stats.coherent_kernel_launches += 1; }
     }
     d->ev_used = 0;
 }
 
-// Which closest-hit kernel a launch uses. Measured on B200 (profiles/): camera rays are coherent and
-// instruction-bound, where the while-while kernel over 64-byte float nodes is fastest (10.5 Grays/s on C2);
-// bounce / visibility / API rays are incoherent and bound by L1 wavefronts AND by issue slots at 7 of 32
-// lanes, where the rounds kernel over 32-byte quantised nodes is fastest (3.9 vs 2.8 Grays/s on C3).
-// TERRA_B200_TRACE=v1|v2|v3|v3q|quant|ld128 forces one kernel for every launch (A/B runs).
-enum { TB_K_AUTO = 0, TB_K_V1, TB_K_V2, TB_K_V3, TB_K_V3Q, TB_K_QUANT, TB_K_LD128, TB_K_V4, TB_K_V4Q, TB_K_PACKET, TB_K_V5 };
+// Which closest-hit kernel a launch uses (measured on B200, profiles/): camera rays are coherent — one warp walks
+// the tree once for its 32 rays (k_trace_packet); bounce / visibility / API rays are incoherent — per-lane rays in
+// warp-synchronous rounds over 32-byte quantised nodes (k_trace_v6; k_trace_v4 = round 1's version, kept while
+// the two are measured side by side). The work counters of SURVEY §8(d) mean the per-ray walk: a counting
+// camera launch runs k_trace<COUNT> (a packet would count the union over its 32 rays).
+enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V4, TB_K_V6, TB_K_PACKET };
 
 template <bool COUNT>
-static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind) {
+static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind, const TbGenArgs* gen) {
     const int grid = d->sm_count * TB_TRACE_CTAS_PER_SM;
-    const bool have_q = d->d_qnodes != NULL;
-    if (have_q) {
+    const bool exact = d->exact_boxes != 0;
+    if (d->d_qnodes) {
         c.qnodes = d->d_qnodes;
         memcpy(c.grid_lo, d->grid_lo, sizeof c.grid_lo);
         memcpy(c.grid_cell, d->grid_cell, sizeof c.grid_cell);
     }
-    if (kind == TB_K_V1) { k_trace_v1<COUNT><<<grid, TB_TRACE_THREADS, 0, st>>>(c); return; }
-    if (kind == TB_K_V5) {            // 4-wide tree; the work counters and the reference tree stay on the binary kernels
-        if (!COUNT && d->d_qnodes4 && !d->exact_boxes) {
-            c.qnodes4 = d->d_qnodes4;
-            if (d->stack_bound4 > TB_V5_DEPTH) k_trace_v5<true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-            else                               k_trace_v5<false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+    if (kind == TB_K_PACKET && !COUNT) {
+        TbGenArgs g;
+        memset(&g, 0, sizeof g);
+        if (gen) {
+            g = *gen;
+            if (exact) k_trace_packet<true, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c, g);
+            else       k_trace_packet<false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c, g);
+        } else {
+            if (exact) k_trace_packet<true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c, g);
+            else       k_trace_packet<false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c, g);
+        }
+        return;
+    }
+    if (kind == TB_K_PACKET || kind == TB_K_WALK) {
+        if (exact) k_trace<COUNT, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else       k_trace<COUNT, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        return;
+    }
+    if (kind == TB_K_V6) {
+        static const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
+        int rows = d->stack_bound > 1 ? d->stack_bound : 1;
+        if (forced > 0 && forced < rows) rows = forced;
+        const bool spill = rows > TB_V6_MAX_SMEM_DEPTH || rows < d->stack_bound;
+        if (rows > TB_V6_MAX_SMEM_DEPTH) rows = TB_V6_SPILL_SMEM_DEPTH;
+        c.stack_smem = rows;
+        const size_t smem = (size_t)(rows + 2) * TB_TRACE_THREADS * 8;
+#define TB_V6_LAUNCH(CNT, EX, SP, OP) k_trace_v6<CNT, EX, SP, OP><<<grid, TB_TRACE_THREADS, smem, st>>>(c)
+        if (COUNT || exact) {           // counting and the reference tree run the default control options
+            if (exact) { if (spill) TB_V6_LAUNCH(COUNT, true, true, TB_V6_OPT_DEFAULT); else TB_V6_LAUNCH(COUNT, true, false, TB_V6_OPT_DEFAULT); }
+            else       { if (spill) TB_V6_LAUNCH(COUNT, false, true, TB_V6_OPT_DEFAULT); else TB_V6_LAUNCH(COUNT, false, false, TB_V6_OPT_DEFAULT); }
             return;
         }
-        kind = TB_K_V4Q;
-    }
-    if (kind == TB_K_PACKET && !COUNT) {
-        static const int occ = getenv("TERRA_B200_PACKET_OCC") ? atoi(getenv("TERRA_B200_PACKET_OCC")) : 8;
-        if (d->exact_boxes)  k_trace_packet<true, 8><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else if (occ == 12)  k_trace_packet<false, 12><<<d->sm_count * 12, TB_TRACE_THREADS, 0, st>>>(c);
-        else if (occ == 10)  k_trace_packet<false, 10><<<d->sm_count * 10, TB_TRACE_THREADS, 0, st>>>(c);
-        else                 k_trace_packet<false, 8><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        return;
-    }
-    const bool spill = d->stack_bound > TB_V4_DEPTH;
-    if (kind == TB_K_V4 || kind == TB_K_V4Q) {
-        const bool q = kind == TB_K_V4Q && have_q && !d->exact_boxes;
-        if (d->exact_boxes) {
-            if (spill) k_trace_v4<COUNT, true, false, true, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-            else       k_trace_v4<COUNT, true, false, false, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        } else if (q) {
-            const int opt = COUNT ? 0 : d->v4_opt;
-            switch (opt * 2 + (spill ? 1 : 0)) {
-                case 0: k_trace_v4<COUNT, false, true, false, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                case 1: k_trace_v4<COUNT, false, true, true, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                case 2: k_trace_v4<false, false, true, false, 1><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                case 3: k_trace_v4<false, false, true, true, 1><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                case 4: k_trace_v4<false, false, true, false, 2><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                case 5: k_trace_v4<false, false, true, true, 2><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                case 6: k_trace_v4<false, false, true, false, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-                default: k_trace_v4<false, false, true, true, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-            }
-        } else {
-            if (spill) k_trace_v4<COUNT, false, false, true, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-            else       k_trace_v4<COUNT, false, false, false, 0><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        switch ((d->v6_opt & 3) * 2 + (spill ? 1 : 0)) {
+            case 0: TB_V6_LAUNCH(false, false, false, 0); break;
+            case 1: TB_V6_LAUNCH(false, false, true, 0); break;
+            case 2: TB_V6_LAUNCH(false, false, false, 1); break;
+            case 3: TB_V6_LAUNCH(false, false, true, 1); break;
+            case 4: TB_V6_LAUNCH(false, false, false, 2); break;
+            case 5: TB_V6_LAUNCH(false, false, true, 2); break;
+            case 6: TB_V6_LAUNCH(false, false, false, 3); break;
+            default: TB_V6_LAUNCH(false, false, true, 3); break;
         }
+#undef TB_V6_LAUNCH
         return;
     }
-    if (d->exact_boxes) {           // reference tree: the reference's own box arithmetic, float nodes
-        if (kind == TB_K_V3 || kind == TB_K_V3Q) k_trace_v3<COUNT, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else k_trace<COUNT, true, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        return;
-    }
-    switch (kind) {
-        case TB_K_V3:    k_trace_v3<COUNT, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-        case TB_K_V3Q:   if (have_q) { k_trace_v3<COUNT, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break; }
-                         k_trace_v3<COUNT, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-        case TB_K_QUANT: if (have_q) { k_trace<COUNT, false, false, true><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break; }
-                         k_trace<COUNT, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-        case TB_K_LD128: k_trace<COUNT, false, false, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
-        default:         k_trace<COUNT, false, true, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c); break;
+    // TB_K_V4
+    const bool spill = d->stack_bound > TB_V4_DEPTH;
+    if (exact) {
+        if (spill) k_trace_v4<COUNT, true, false, true, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else       k_trace_v4<COUNT, true, false, false, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+    } else {
+        if (spill) k_trace_v4<COUNT, false, true, true, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        else       k_trace_v4<COUNT, false, true, false, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
     }
 }
 
-static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, bool coherent) {
-    TbEventPair* e = d->capturing ? NULL : tb_event_pair(d);     // a captured launch is timed as part of the whole call only
-    if (e) TB_CUDA(cudaEventRecord(e->a, st));
-    TbTraceArgs c = a;
-    c.visit_counters = (unsigned long long*)(d->wave.counters + 10);
-    c.tri_min = d->tri_min; c.refetch_below = d->refetch_below;
+// Kernel a launch of this kind will run (TB_K_*), after the A/B overrides.
+static int tb_trace_kind(const TbDevice* d, bool coherent) {
     int kind = d->trace_kind;
     if (kind == TB_K_AUTO) kind = coherent ? d->coherent_kind : d->incoherent_kind;
-    if (kind == TB_K_PACKET && d->counting) kind = TB_K_V2;     // the work counters mean the per-ray walk
-    if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind);
-    else             tb_launch_trace_kernel<false>(d, st, c, kind);
+    if (kind == TB_K_AUTO) kind = coherent ? TB_K_PACKET : TB_K_V6;
+    return kind;
+}
+
+static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, bool coherent, const TbGenArgs* gen = NULL) {
+    TbEventPair* e = d->capturing ? NULL : tb_event_pair(d, coherent ? 1 : 0);     // a captured launch is timed as part of the whole call only
+    if (e) TB_CUDA(cudaEventRecord(e->a, st));
+    TbTraceArgs c = a;
+    c.visit_counters = (unsigned long long*)(d->wave.counters + (coherent ? 16 : 10));
+    c.tri_min = d->tri_min; c.refetch_below = d->refetch_below;
+    const int kind = tb_trace_kind(d, coherent);
+    if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind, NULL);
+    else             tb_launch_trace_kernel<false>(d, st, c, kind, gen);
     if (e) TB_CUDA(cudaEventRecord(e->b, st));
     d->stats.kernel_launches += 1;
 }
 
+// Camera rays can be generated inside the trace kernel when that kernel is the packet kernel.
+static bool tb_fused_raygen(const TbDevice* d) {
+    return d->fused_raygen && !d->counting && tb_trace_kind(d, true) == TB_K_PACKET;
+}
+
 typedef void (*TbShadeKernel)(TbShadeArgs);
-static TbShadeKernel tb_shade_kernel(int preset, int stage) {
-    static const TbShadeKernel table[TB_PRESET_COUNT][2] = {
-        { k_shade<0, 0>, k_shade<0, 1> }, { k_shade<1, 0>, k_shade<1, 1> },
-        { k_shade<2, 0>, k_shade<2, 1> }, { k_shade<3, 0>, k_shade<3, 1> } };
-    return table[preset][stage];
+static TbShadeKernel tb_shade_kernel(int preset, int stage, int mode) {
+    static const TbShadeKernel simple[TB_PRESET_COUNT] = {
+        k_shade<0, 1, TB_SHADE_SIMPLE>, k_shade<1, 1, TB_SHADE_SIMPLE>, k_shade<2, 1, TB_SHADE_SIMPLE>, k_shade<3, 1, TB_SHADE_SIMPLE> };
+    static const TbShadeKernel direct[TB_PRESET_COUNT][2] = {
+        { k_shade<0, 0, TB_SHADE_DIRECT>, k_shade<0, 1, TB_SHADE_DIRECT> }, { k_shade<1, 0, TB_SHADE_DIRECT>, k_shade<1, 1, TB_SHADE_DIRECT> },
+        { k_shade<2, 0, TB_SHADE_DIRECT>, k_shade<2, 1, TB_SHADE_DIRECT> }, { k_shade<3, 0, TB_SHADE_DIRECT>, k_shade<3, 1, TB_SHADE_DIRECT> } };
+    static const TbShadeKernel debug[TB_PRESET_COUNT][2] = {
+        { k_shade<0, 0, TB_SHADE_DEBUG>, k_shade<0, 1, TB_SHADE_DEBUG> }, { k_shade<1, 0, TB_SHADE_DEBUG>, k_shade<1, 1, TB_SHADE_DEBUG> },
+        { k_shade<2, 0, TB_SHADE_DEBUG>, k_shade<2, 1, TB_SHADE_DEBUG> }, { k_shade<3, 0, TB_SHADE_DEBUG>, k_shade<3, 1, TB_SHADE_DEBUG> } };
+    if (mode == TB_SHADE_SIMPLE) return simple[preset];
+    return mode == TB_SHADE_DIRECT ? direct[preset][stage] : debug[preset][stage];
 }
 
 // All waves of one region: adds `spp` samples per pixel into d_acc (region-linear float4, zeroed by the caller).
-static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* cam, size_t fbw, size_t fbh,
-                             size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
-                             uint64_t seed, float4* d_acc, const TbCallParams* d_call = NULL) {
+// Region origin, framebuffer size, sample base, seed and camera reach the kernels through d->d_call (tb_set_call),
+// so the same launches serve a direct call and a CUDA-graph replay.
+static void tb_render_region(TbDevice* d, cudaStream_t st, size_t w, size_t h, size_t spp, float4* d_acc) {
     const size_t npx = w * h;
     const size_t cap = tb_batch_capacity();
     const size_t px_per_wave = npx < cap ? npx : cap;
@@ -1406,48 +1426,57 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
     tb_wave_reserve(&d->wave, px_per_wave * s_per_wave);
     TbWave& wv = d->wave;
     const TbDevScene& sc = d->sc;
-    const bool direct = sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis ||
-                        sc.integrator == kTerraIntegratorDebugMisWeights;
-    const bool env_nee = sc.env_nee && (sc.integrator == kTerraIntegratorDirect || sc.integrator == kTerraIntegratorDirectMis);
     if (sc.integrator < 0 || sc.integrator > kTerraIntegratorDebugMisWeights) {
         terra_log("terra_b200: unknown integrator %d\n", sc.integrator);      // assert(false), Terra.c:1134
         abort();
     }
+    const int mode = sc.integrator == kTerraIntegratorSimple ? TB_SHADE_SIMPLE
+                   : sc.integrator <= kTerraIntegratorDirectMis ? TB_SHADE_DIRECT : TB_SHADE_DEBUG;
+    const bool direct = mode == TB_SHADE_DIRECT || sc.integrator == kTerraIntegratorDebugMisWeights;
+    const bool env_nee = sc.env_nee && mode == TB_SHADE_DIRECT;
     // debug views (Terra.c:1140-1337) contribute at bounce 0 only: one trace + one shade per wave
-    const int last_bounce = sc.integrator > kTerraIntegratorDirectMis ? 0 : sc.bounces;
-    const int shade_grid = d->sm_count * 4;
+    const int last_bounce = mode == TB_SHADE_DEBUG ? 0 : sc.bounces;
+    const bool fused = tb_fused_raygen(d);
     for (size_t p0 = 0; p0 < npx; p0 += px_per_wave) {
         const size_t np = npx - p0 < px_per_wave ? npx - p0 : px_per_wave;
         for (size_t s0 = 0; s0 < spp; s0 += s_per_wave) {
             const size_t ns = spp - s0 < s_per_wave ? spp - s0 : s_per_wave;
-            TbBatch b;
-            b.x = (int)x; b.y = (int)y; b.w = (int)w; b.h = (int)h; b.fbw = (int)fbw; b.fbh = (int)fbh;
+            TbGenArgs gen;
+            memset(&gen, 0, sizeof gen);
+            TbBatch& b = gen.batch;
+            b.w = (int)w; b.h = (int)h;
             b.p0 = (int)p0; b.n_pixels = (int)np; b.s0 = (int)s0; b.n_samples = (int)ns;
-            b.sample_base = (uint32_t)sample_base; b.seed = seed;
             b.tiled = (d->tile_pixels && w % 8 == 0 && h % 4 == 0 && np % 32 == 0 && p0 % 32 == 0) ? 1 : 0;
             b.sub = 1;
             while (b.sub < 32 && b.sub < d->warp_samples && ns % (size_t)(b.sub * 2) == 0) b.sub *= 2;
+            gen.jitter = sc.jitter; gen.on = 1; gen.call = d->d_call;
             const int n_paths = (int)(np * ns);
-            TbRaygenArgs rg;
-            rg.batch = b; rg.cam = *cam; rg.jitter = sc.jitter;
-            rg.ray_o = wv.ray_o; rg.ray_d = wv.ray_d; rg.thr = wv.thr; rg.lo = wv.lo; rg.queue = wv.queue[0];
-            rg.call = d_call;
             k_counters<<<1, 1, 0, st>>>(wv.counters, 0, n_paths);
-            k_raygen<<<d->sm_count * 8, 256, 0, st>>>(rg);
-            d->stats.kernel_launches += 2;
+            d->stats.kernel_launches += 1;
+            if (!fused) {
+                TbRaygenArgs rg;
+                rg.gen = gen;
+                rg.ray_o = wv.ray_o; rg.ray_d = wv.ray_d; rg.thr = wv.thr; rg.lo = wv.lo; rg.queue = wv.queue[0];
+                k_raygen<<<d->sm_count * 8, 256, 0, st>>>(rg);
+                d->stats.kernel_launches += 1;
+            }
             int cur = 0;
             for (int bounce = 0; bounce <= last_bounce; ++bounce) {
+                const bool implicit = fused && bounce == 0;          // this bounce's rays exist in no array: they are functions of the slot
+                TbGenArgs off = gen;
+                off.on = 0;
                 TbTraceArgs ta;
                 memset(&ta, 0, sizeof ta);
                 ta.nodes = sc.nodes; ta.tris = sc.tris;
                 ta.ray_o = wv.ray_o; ta.ray_d = wv.ray_d;
-                ta.queue = wv.queue[cur]; ta.count_ptr = wv.counters + 1; ta.cursor = wv.counters;
-                ta.hit_out = wv.hit;
+                ta.queue = implicit ? NULL : wv.queue[cur]; ta.count_ptr = wv.counters + 1; ta.cursor = wv.counters;
+                ta.hit_out = wv.hit; ta.lo = wv.lo;
                 ta.matq = wv.matq; ta.matq_count = wv.counters + 4; ta.matq_stride = (int)wv.capacity;
                 ta.emit_prim = 0;
-                tb_launch_trace(d, st, ta, bounce == 0);
+                tb_launch_trace(d, st, ta, bounce == 0, implicit ? &gen : NULL);
                 if (sc.env_lit && last_bounce == sc.bounces && (!env_nee || bounce == 0)) {
-                    k_miss<<<d->sm_count * 4, 256, 0, st>>>(sc, wv.queue[cur], wv.counters + 1, wv.ray_d, wv.hit, wv.thr, wv.lo);
+                    k_miss<<<d->sm_count * 4, 256, 0, st>>>(sc, implicit ? NULL : wv.queue[cur], wv.counters + 1, wv.ray_d, wv.hit, wv.thr, wv.lo,
+                                                            implicit ? gen : off);
                     d->stats.kernel_launches += 1;
                 }
                 TbShadeArgs sa;
@@ -1458,11 +1487,17 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 sa.auxq = wv.auxq; sa.aux_count = wv.counters + 3;
                 sa.bounce = bounce;
                 sa.env_base = (int)(2 * wv.capacity);
+                sa.gen = implicit ? gen : off;
+                // enough CTAs for the queue when it is short, a grid-stride loop when it is long
+                const int shade_cap = d->sm_count * 8;
+                int shade_grid = (int)((np * ns + TB_SHADE_THREADS - 1) / TB_SHADE_THREADS);
+                if (shade_grid > shade_cap) shade_grid = shade_cap;
+                if (shade_grid < 1) shade_grid = 1;
                 if (direct && (sc.n_lights > 0 || env_nee)) {
                     for (int p = 0; p < TB_PRESET_COUNT; ++p) {
                         if (!(sc.preset_mask & (1 << p))) continue;
                         sa.q = wv.matq + (size_t)p * wv.capacity; sa.q_count = wv.counters + 4 + p;
-                        tb_shade_kernel(p, 0)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
+                        tb_shade_kernel(p, 0, mode)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
                         d->stats.kernel_launches += 1;
                     }
                     k_counters<<<1, 1, 0, st>>>(wv.counters, 2, 0);
@@ -1479,28 +1514,32 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, const TbCameraFrame* 
                 for (int p = 0; p < TB_PRESET_COUNT; ++p) {
                     if (!(sc.preset_mask & (1 << p))) continue;
                     sa.q = wv.matq + (size_t)p * wv.capacity; sa.q_count = wv.counters + 4 + p;
-                    tb_shade_kernel(p, 1)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
+                    tb_shade_kernel(p, 1, mode)<<<shade_grid, TB_SHADE_THREADS, 0, st>>>(sa);
                     d->stats.kernel_launches += 1;
                 }
                 if (bounce == last_bounce) break;                    // nothing reads the queues of a bounce that does not happen
                 k_counters<<<1, 1, 0, st>>>(wv.counters, 3, 0);
                 d->stats.kernel_launches += 1;
-                if (d->sort_rays && bounce < last_bounce && bounce < d->sort_bounces) {
-                    // next queue (queue[cur^1], count in counters[1]) -> queue[cur] in direction bins; no flip
-                    TB_CUDA(cudaMemsetAsync(wv.bins, 0, 2 * TB_SORT_BINS * sizeof(int), st));
-                    k_bin_count<<<d->sm_count * 4, 256, 0, st>>>(wv.queue[cur ^ 1], wv.counters + 1, wv.ray_d, d->sort_rays, wv.bins);
-                    k_bin_scatter<<<d->sm_count * 4, 256, 0, st>>>(wv.queue[cur ^ 1], wv.counters + 1, wv.ray_d, d->sort_rays, wv.bins, wv.queue[cur]);
-                    d->stats.kernel_launches += 2;
-                } else {
-                    cur ^= 1;
-                }
+                cur ^= 1;
             }
-            k_accumulate<<<d->sm_count * 4, 256, 0, st>>>(b, wv.lo, d_acc);
+            k_accumulate<<<d->sm_count * 4, 256, 0, st>>>(gen.batch, wv.lo, d_acc);
             d->stats.kernel_launches += 1;
             d->stats.paths_traced += (uint64_t)n_paths;
         }
     }
     TB_CUDA(cudaGetLastError());
+}
+
+// The per-call values of a render call, written to device memory before its kernels (direct launches and graph
+// replays alike). h_call is page-locked and reused: the calls are synchronous, so the copy has run before the next one.
+static void tb_set_call(TbDevice* d, cudaStream_t st, const TbCameraFrame* cam, size_t fbw, size_t fbh, size_t x, size_t y,
+                        size_t sample_base, uint64_t seed, void* d_results) {
+    TbCallParams* hp = d->h_call;
+    memset(hp, 0, sizeof *hp);
+    hp->cam = *cam;
+    hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fbw; hp->fbh = (int)fbh;
+    hp->sample_base = (uint32_t)sample_base; hp->seed = seed; hp->results = d_results;
+    TB_CUDA(cudaMemcpyAsync(d->d_call, hp, sizeof *hp, cudaMemcpyHostToDevice, st));
 }
 
 // ==================================================================================== entry points
@@ -1556,7 +1595,7 @@ static TbDevice::Graph* tb_graph_for(TbDevice* d, cudaStream_t st, size_t w, siz
     cudaGraph_t graph = NULL;
     d->capturing = true;
     TB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    body(d->d_call);
+    body();
     TB_CUDA(cudaStreamEndCapture(st, &graph));
     d->capturing = false;
     TbDevice::Graph g;
@@ -1570,6 +1609,24 @@ static TbDevice::Graph* tb_graph_for(TbDevice* d, cudaStream_t st, size_t w, siz
     return &d->graphs.back();
 }
 
+// d_acc is shared by both render entry points: one capacity, never shrunk.
+static void tb_acc_reserve(TbDevice* d, size_t npx) {
+    if (npx <= d->acc_capacity) return;
+    d->graph_epoch++;
+    tb_free(d->d_acc);
+    d->d_acc = tb_alloc<float4>(npx);
+    d->acc_capacity = npx;
+}
+
+// A caller that passes no stream works on the legacy default stream: order this library's own (non-blocking)
+// stream after whatever the caller has queued there, so that e.g. a memset of the results array is seen.
+static cudaStream_t tb_call_stream(TbDevice* d, void* stream) {
+    if (stream) return (cudaStream_t)stream;
+    TB_CUDA(cudaEventRecord(d->ev_legacy, cudaStreamLegacy));
+    TB_CUDA(cudaStreamWaitEvent(d->stream, d->ev_legacy, 0));
+    return d->stream;
+}
+
 extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const TerraFramebuffer* fb,
                                  size_t x, size_t y, size_t w, size_t h, size_t spp, uint64_t seed) {
     TB_CUDA(cudaSetDevice(d->index));
@@ -1577,12 +1634,12 @@ extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const Te
     const size_t npx = w * h;
     if (npx > d->fb_capacity) {
         d->graph_epoch++;
-        tb_free(d->d_results); tb_free(d->d_pixels); tb_free(d->d_acc);
+        tb_free(d->d_results); tb_free(d->d_pixels);
         d->d_results = tb_alloc<TerraRawIntegrationResult>(npx);
         d->d_pixels = tb_alloc<float>(npx * 3);
-        d->d_acc = tb_alloc<float4>(npx);
         d->fb_capacity = npx;
     }
+    tb_acc_reserve(d, npx);
     TB_CUDA(cudaEventRecord(d->ev_call_a, st));
     // progressive accumulation: the caller's results[] are the state (Terra.c:570-572), so they go up first
     TB_CUDA(cudaMemcpy2DAsync(d->d_results, w * sizeof(TerraRawIntegrationResult),
@@ -1591,9 +1648,9 @@ extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const Te
     d->stats.h2d_bytes += npx * sizeof(TerraRawIntegrationResult);
     // ---- the kernels of the call: launched one by one, or — for a small call whose shape has been seen
     //      before — replayed from a CUDA graph (a 128x128 tile is ~45 launches of a few microseconds each)
-    auto body = [&](const TbCallParams* d_call) {
+    auto body = [&]() {
         TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
-        tb_render_region(d, st, cam, fb->width, fb->height, x, y, w, h, 0, spp, seed, d->d_acc, d_call);
+        tb_render_region(d, st, w, h, spp, d->d_acc);
         TbFinalizeArgs fa;
         fa.acc = d->d_acc;
         fa.results = d->d_results; fa.results_pitch = w;
@@ -1606,18 +1663,14 @@ extern "C" void tb_device_render(TbDevice* d, const TbCameraFrame* cam, const Te
     };
     TbDevice::Graph* g = NULL;
     if (d->graph_max_paths && npx * spp <= d->graph_max_paths && !d->counting) g = tb_graph_for(d, st, w, h, spp, 0, body);
+    tb_set_call(d, st, cam, fb->width, fb->height, x, y, 0, seed, NULL);
     if (g) {
-        TbCallParams* hp = d->h_call;
-        hp->cam = *cam;
-        hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fb->width; hp->fbh = (int)fb->height;
-        hp->sample_base = 0; hp->pad_ = 0; hp->seed = seed; hp->results = NULL;
-        TB_CUDA(cudaMemcpyAsync(d->d_call, hp, sizeof *hp, cudaMemcpyHostToDevice, st));
         TB_CUDA(cudaGraphLaunch(g->exec, st));
         d->stats.kernel_launches += g->launches;
         d->stats.paths_traced += g->paths;
         d->stats.graph_replays += 1;
     } else {
-        body(NULL);
+        body();
     }
     TB_CUDA(cudaMemcpy2DAsync(fb->results + y * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
                               d->d_results, w * sizeof(TerraRawIntegrationResult),
@@ -1632,49 +1685,39 @@ extern "C" void tb_device_render_resident(TbDevice* d, const TbCameraFrame* cam,
                                           size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
                                           uint64_t seed, void* d_results, void* stream) {
     TB_CUDA(cudaSetDevice(d->index));
-    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    cudaStream_t st = tb_call_stream(d, stream);
     const size_t npx = w * h;
-    if (npx > d->acc_capacity) {
-        d->graph_epoch++;
-        tb_free(d->d_acc);
-        d->d_acc = tb_alloc<float4>(npx > d->fb_capacity ? npx : d->fb_capacity);
-        d->acc_capacity = npx > d->fb_capacity ? npx : d->fb_capacity;
-        if (d->fb_capacity < npx) { tb_free(d->d_results); tb_free(d->d_pixels); d->d_results = NULL; d->d_pixels = NULL; d->fb_capacity = 0; }
-    }
+    tb_acc_reserve(d, npx);
     TB_CUDA(cudaEventRecord(d->ev_call_a, st));
-    auto body = [&](const TbCallParams* d_call) {
+    auto body = [&]() {
         TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
-        tb_render_region(d, st, cam, fbw, fbh, x, y, w, h, sample_base, spp, seed, d->d_acc, d_call);
+        tb_render_region(d, st, w, h, spp, d->d_acc);
         TbFinalizeArgs fa;
         fa.acc = d->d_acc;
-        fa.results = (TerraRawIntegrationResult*)d_results + y * fbw + x; fa.results_pitch = fbw;
+        fa.results = NULL; fa.results_pitch = 0;              // region origin, pitch and the results pointer come from d_call
         fa.pixels = NULL; fa.pixels_pitch = 0;
         fa.w = (int)w; fa.h = (int)h; fa.spp = (int)spp; fa.tonemap = 0; fa.exposure = 1.f; fa.inv_gamma = 1.f;
-        fa.call = d_call;
+        fa.call = d->d_call;
         k_finalize<<<d->sm_count * 4, 256, 0, st>>>(fa);
         d->stats.kernel_launches += 1;
     };
     TbDevice::Graph* g = NULL;
     if (d->graph_max_paths && npx * spp <= d->graph_max_paths && !d->counting) g = tb_graph_for(d, st, w, h, spp, 1, body);
+    tb_set_call(d, st, cam, fbw, fbh, x, y, sample_base, seed, d_results);
     if (g) {
-        TbCallParams* hp = d->h_call;
-        hp->cam = *cam;
-        hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fbw; hp->fbh = (int)fbh;
-        hp->sample_base = (uint32_t)sample_base; hp->pad_ = 0; hp->seed = seed; hp->results = d_results;
-        TB_CUDA(cudaMemcpyAsync(d->d_call, hp, sizeof *hp, cudaMemcpyHostToDevice, st));
         TB_CUDA(cudaGraphLaunch(g->exec, st));
         d->stats.kernel_launches += g->launches;
         d->stats.paths_traced += g->paths;
         d->stats.graph_replays += 1;
     } else {
-        body(NULL);
+        body();
     }
     tb_finish_call(d, st, true);
 }
 
 extern "C" void tb_device_resolve(TbDevice* d, size_t fbw, size_t fbh, const void* d_results, void* d_pixels, void* stream) {
     TB_CUDA(cudaSetDevice(d->index));
-    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    cudaStream_t st = tb_call_stream(d, stream);
     k_resolve<<<d->sm_count * 4, 256, 0, st>>>((const TerraRawIntegrationResult*)d_results, (float*)d_pixels, fbw * fbh,
                                                d->sc.tonemap, d->sc.exposure, d->sc.inv_gamma);
     d->stats.kernel_launches += 1;
@@ -1682,7 +1725,7 @@ extern "C" void tb_device_resolve(TbDevice* d, size_t fbw, size_t fbh, const voi
 }
 
 static void tb_trace_generic(TbDevice* d, cudaStream_t st, size_t n, const float4* d_o, const float4* d_d, float4* d_hit, bool coherent = false) {
-    k_counters<<<1, 1, 0, st>>>(d->wave.counters, 4, (int)n);
+    k_counters<<<1, 1, 0, st>>>(d->wave.counters, coherent ? 5 : 4, (int)n);
     TbTraceArgs ta;
     memset(&ta, 0, sizeof ta);
     ta.nodes = d->sc.nodes; ta.tris = d->sc.tris;
@@ -1705,7 +1748,7 @@ static void tb_io_reserve(TbDevice* d, size_t n) {
 
 extern "C" void tb_device_trace_resident(TbDevice* d, size_t n, const void* d_o, const void* d_d, void* d_hits, void* stream) {
     TB_CUDA(cudaSetDevice(d->index));
-    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    cudaStream_t st = tb_call_stream(d, stream);
     const size_t chunk = (size_t)1 << 30;
     for (size_t at = 0; at < n; at += chunk) {
         const size_t m = n - at < chunk ? n - at : chunk;
@@ -2034,8 +2077,8 @@ __global__ void __launch_bounds__(256) k_refit_quantise(const float4* __restrict
                 g[6 * c + k] = (uint32_t)a; g[6 * c + 3 + k] = (uint32_t)b;
             }
         uint4 w0, w1;
-        w0.x = g[0] | (g[1] << 16); w0.y = g[2] | (g[3] << 16); w0.z = g[4] | (g[5] << 16); w0.w = g[6] | (g[7] << 16);
-        w1.x = g[8] | (g[9] << 16); w1.y = g[10] | (g[11] << 16); w1.z = __float_as_uint(q3.x); w1.w = __float_as_uint(q3.y);
+        w0.x = g[0] | (g[3] << 16); w0.y = g[1] | (g[4] << 16); w0.z = g[2] | (g[5] << 16); w0.w = g[6] | (g[9] << 16);
+        w1.x = g[7] | (g[10] << 16); w1.y = g[8] | (g[11] << 16); w1.z = __float_as_uint(q3.x); w1.w = __float_as_uint(q3.y);
         qnodes[(size_t)i * 2] = w0; qnodes[(size_t)i * 2 + 1] = w1;
     }
 }
@@ -2084,7 +2127,6 @@ extern "C" void tb_device_refit(TbDevice* d, const float* const* obj_tris, const
         k_refit_quantise<<<d->sm_count * 8, 256, 0, st>>>(d->d_nodes, d->d_qnodes, n_nodes, d->grid_lo[0], d->grid_lo[1], d->grid_lo[2],
                                                           d->grid_cell[0], d->grid_cell[1], d->grid_cell[2]);
         d->stats.kernel_launches += 1;
-        tb_free(d->d_qnodes4); d->d_qnodes4 = NULL;             // the 4-wide A/B tree is not refitted
     }
     TB_CUDA(cudaEventRecord(e1, st));
     if (n_lights) {
@@ -2101,11 +2143,14 @@ extern "C" void tb_device_refit(TbDevice* d, const float* const* obj_tris, const
 
 extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
     TB_CUDA(cudaSetDevice(d->index));
-    unsigned long long c[3] = { 0, 0, 0 };
+    unsigned long long c[6] = { 0, 0, 0, 0, 0, 0 };          // rays, nodes, tris (incoherent launches); camera rays, nodes, tris
     TB_CUDA(cudaMemcpy(c, d->wave.counters + 8, sizeof c, cudaMemcpyDeviceToHost));
     d->stats.rays_traced = c[0];
-    d->stats.nodes_visited = c[1];
-    d->stats.tris_tested = c[2];
+    d->stats.nodes_visited = c[1] + c[4];
+    d->stats.tris_tested = c[2] + c[5];
+    d->stats.coherent_rays = c[3];
+    d->stats.coherent_nodes_visited = c[4];
+    d->stats.coherent_tris_tested = c[5];
     *out = d->stats;
 }
 

@@ -66,14 +66,13 @@ __device__ __forceinline__ void tb_load_node256(const float4* np, float4& q0, fl
                  : "=f"(q2.x), "=f"(q2.y), "=f"(q2.z), "=f"(q2.w), "=f"(q3.x), "=f"(q3.y), "=f"(q3.z), "=f"(q3.w) : "l"(np + 2));
 }
 
-// ---- quantised nodes (QUANT): 32 bytes = 2 x 128-bit requests instead of 4.
-// An experiment, OFF by default (TERRA_B200_TRACE=quant): on incoherent rays k_trace fetches 66 G records/s,
-// the same rate at which terra_b200_probe_bandwidth gathers random 64-byte records (65 G/s), so halving the
-// 16-byte requests per node looked promising. Measured: no gain on incoherent rays (2.82 vs 2.85 Grays/s)
-// and -7 % on the C2 frame (12 extra PRMTs per node, slightly larger boxes). Kept for the record.
-// Layout (tb_bvh.cpp, tb_bvh_quantize): child boxes on a 16-bit grid over the padded scene box,
-//   word0 = min0.x | min0.y << 16   word1 = min0.z | max0.x << 16   word2 = max0.y | max0.z << 16
-//   word3 = min1.x | min1.y << 16   word4 = min1.z | max1.x << 16   word5 = max1.y | max1.z << 16
+// ---- quantised nodes: 32 bytes = ONE 256-bit request per node visit (a divergent warp pays one L1 wavefront
+// per lane per load instruction), used by the rounds kernels for every tree but the reference's.
+// Layout (tb_bvh.cpp, tb_bvh_quantize): child boxes on a 16-bit grid over the padded scene box, the two planes
+// of one axis share a word — so that a per-ray byte-permute selector picks the NEAR or the FAR plane of the
+// axis straight out of the word (tb_trace_v6.cuh):
+//   word0 = min0.x | max0.x << 16   word1 = min0.y | max0.y << 16   word2 = min0.z | max0.z << 16
+//   word3 = min1.x | max1.x << 16   word4 = min1.y | max1.y << 16   word5 = min1.z | max1.z << 16
 //   word6 = ref0                    word7 = ref1
 // mins rounded down and maxes up, then widened by one more cell, so the decoded box always CONTAINS the
 // float box (the triangle test, which decides id/t/u/v, is untouched). Decode is folded into the slab
@@ -93,8 +92,9 @@ __device__ __forceinline__ float tb_qlo(unsigned w) { return __uint_as_float(__b
 __device__ __forceinline__ float tb_qhi(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)); }
 
 #define TB_REF_DONE ((int)0x80000000)             /* not a valid ~rank (rank < 2^31 - 1) nor a node index */
+#define TB_REF_POP  ((int)0x80000001)             /* rounds kernels: the lane must pop its stack next round */
 
-template <bool COUNT, bool EXACT, bool LD256, bool QUANT>
+template <bool COUNT, bool EXACT>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace(TbTraceArgs a) {
     __shared__ int   s_ref[TB_STACK_SMEM][TB_TRACE_THREADS];
     __shared__ float s_tmin[TB_STACK_SMEM][TB_TRACE_THREADS];
@@ -153,8 +153,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                     const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
                     const V3 d = v3(d4.x, d4.y, d4.z);
                     r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
-                    if (QUANT) fr = tb_quant_ray(r, d, a.grid_lo, a.grid_cell);
-                    else if (!EXACT) fr = tb_fast_ray(r, d);
+                    if (!EXACT) fr = tb_fast_ray(r, d);
                     cur = 0; sp = 0;
                     best_rank = -1; best_t = FLT_MAX; cull_t = FLT_MAX;
                 }
@@ -169,17 +168,10 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                 int ref0, ref1;
                 float tmin0, tmin1;
                 bool hit0, hit1;
-                if (QUANT) {
-                    const uint4* np = a.qnodes + (size_t)cur * 2;
-                    const uint4 A = __ldg(np), B = __ldg(np + 1);
-                    ref0 = (int)B.z; ref1 = (int)B.w;
-                    hit0 = tb_box_fast(fr, tb_qlo(A.x), tb_qhi(A.x), tb_qlo(A.y), tb_qhi(A.y), tb_qlo(A.z), tb_qhi(A.z), &tmin0);
-                    hit1 = tb_box_fast(fr, tb_qlo(A.w), tb_qhi(A.w), tb_qlo(B.x), tb_qhi(B.x), tb_qlo(B.y), tb_qhi(B.y), &tmin1);
-                } else {
+                {
                     const float4* np = a.nodes + (size_t)cur * 4;
                     float4 q0, q1, q2, q3;
-                    if (LD256) tb_load_node256(np, q0, q1, q2, q3);
-                    else { q0 = __ldg(np); q1 = __ldg(np + 1); q2 = __ldg(np + 2); q3 = __ldg(np + 3); }
+                    tb_load_node256(np, q0, q1, q2, q3);
                     ref0 = __float_as_int(q3.x); ref1 = __float_as_int(q3.y);
                     if (EXACT) {
                         hit0 = tb_box(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
@@ -234,7 +226,8 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                 const float4 tb = __ldg(a.tris + (size_t)best_rank * 3 + 1);
                 h.x = best_t;
                 h.y = a.emit_prim ? ta.w : __int_as_float(best_rank);
-                h.z = best_u; h.w = best_v;
+                h.z = a.emit_prim ? best_u : tb.w;         // wavefront: object | preset << 8 for the shade pass (u, v are not used there)
+                    h.w = best_v;
                 preset = (__float_as_int(tb.w) >> 8) & 0xff;
             } else {
                 h.x = -1.f; h.y = __int_as_float(-1); h.z = 0.f; h.w = 0.f;

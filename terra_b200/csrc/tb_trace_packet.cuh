@@ -20,8 +20,12 @@
 
 #define TB_PACKET_STACK (TB_STACK_SMEM + TB_STACK_LOCAL)
 
-template <bool EXACT, int MINB>
-__global__ void __launch_bounds__(TB_TRACE_THREADS, MINB) k_trace_packet(TbTraceArgs a) {
+// GEN: the packet's rays are camera rays derived in registers from the slot index (tb_gen_ray) — nothing is read
+// from the ray arrays, and the only path state written besides the hit is a zero radiance for the paths that leave
+// the scene (the first shade pass initialises the others). Saves the 112 B per slot k_raygen wrote at the HBM
+// write roof and the 32 B per slot this kernel read back (ncu r1w).
+template <bool EXACT, bool GEN>
+__global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace_packet(TbTraceArgs a, TbGenArgs g) {
     __shared__ int   s_ref[TB_TRACE_THREADS / 32][TB_PACKET_STACK];
     __shared__ float s_tmin[TB_TRACE_THREADS / 32][TB_PACKET_STACK];
     const int tid = threadIdx.x;
@@ -45,10 +49,17 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, MINB) k_trace_packet(TbTrace
         TbFastRay fr;
         fr.ix = fr.iy = fr.iz = fr.ox = fr.oy = fr.oz = 0.f;
         if (alive) {
-            slot = a.queue ? a.queue[q] : q;
-            const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
-            const V3 d = v3(d4.x, d4.y, d4.z);
-            r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
+            V3 o, d;
+            if (GEN) {
+                slot = q;
+                uint64_t key;
+                d = tb_gen_ray(g, slot, &key, &o);
+            } else {
+                slot = a.queue ? a.queue[q] : q;
+                const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
+                o = v3(o4.x, o4.y, o4.z); d = v3(d4.x, d4.y, d4.z);
+            }
+            r = tb_ray_setup(o, d);
             if (!EXACT) fr = tb_fast_ray(r, d);
         }
         int   best_rank = -1;
@@ -144,10 +155,12 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, MINB) k_trace_packet(TbTrace
                 const float4 tb = __ldg(a.tris + (size_t)best_rank * 3 + 1);
                 h.x = best_t;
                 h.y = a.emit_prim ? ta.w : __int_as_float(best_rank);
-                h.z = best_u; h.w = best_v;
+                h.z = a.emit_prim ? best_u : tb.w;         // wavefront: object | preset << 8 for the shade pass (u, v are not used there)
+                    h.w = best_v;
                 preset = (__float_as_int(tb.w) >> 8) & 0xff;
             } else {
                 h.x = -1.f; h.y = __int_as_float(-1); h.z = 0.f; h.w = 0.f;
+                if (GEN) a.lo[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
             a.hit_out[slot] = h;
         }

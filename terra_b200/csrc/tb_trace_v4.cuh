@@ -126,8 +126,8 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                 bool hit0, hit1;
                 if (QUANT) {
                     ref0 = (int)qb.z; ref1 = (int)qb.w;
-                    hit0 = tb_box_fast(fr, tb_qlo(qa.x), tb_qhi(qa.x), tb_qlo(qa.y), tb_qhi(qa.y), tb_qlo(qa.z), tb_qhi(qa.z), &tmin0);
-                    hit1 = tb_box_fast(fr, tb_qlo(qa.w), tb_qhi(qa.w), tb_qlo(qb.x), tb_qhi(qb.x), tb_qlo(qb.y), tb_qhi(qb.y), &tmin1);
+                    hit0 = tb_box_fast(fr, tb_qlo(qa.x), tb_qlo(qa.y), tb_qlo(qa.z), tb_qhi(qa.x), tb_qhi(qa.y), tb_qhi(qa.z), &tmin0);
+                    hit1 = tb_box_fast(fr, tb_qlo(qa.w), tb_qlo(qb.x), tb_qlo(qb.y), tb_qhi(qa.w), tb_qhi(qb.x), tb_qhi(qb.y), &tmin1);
                 } else if (EXACT) {
                     ref0 = __float_as_int(q3.x); ref1 = __float_as_int(q3.y);
                     hit0 = tb_box(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
@@ -176,7 +176,8 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                 const float4 tb = __ldg(a.tris + (size_t)best_rank * 3 + 1);
                 h.x = best_t;
                 h.y = a.emit_prim ? ta.w : __int_as_float(best_rank);
-                h.z = best_u; h.w = best_v;
+                h.z = a.emit_prim ? best_u : tb.w;         // wavefront: object | preset << 8 for the shade pass (u, v are not used there)
+                    h.w = best_v;
                 preset = (__float_as_int(tb.w) >> 8) & 0xff;
             } else {
                 h.x = -1.f; h.y = __int_as_float(-1); h.z = 0.f; h.w = 0.f;

@@ -1,0 +1,289 @@
+// tb_trace_v6.cuh — closest hit for INCOHERENT rays (bounce, visibility and API rays): the rounds kernel.
+//
+// What it computes: terra_scene_raycast without the surface record (Terra.c:1623-1657 -> terra_bvh_traverse
+// TerraBVH.c:250-310 -> box Terra.c:851-878 -> triangle TerraGeometry.c:159-259), same answer as every other
+// trace kernel of this library: same triangles, same tb_triangle, equal t -> smaller rank.
+//
+// Shape (kept from round 1's k_trace_v4): persistent CTAs, per-lane rays in warp-synchronous ROUNDS — every lane
+// that owns a ray fetches one 32-byte quantised node per round with ONE 256-bit load, a leaf is parked and the
+// watertight triangle test runs for all parked leaves at once when enough lanes hold one, idle lanes are refilled
+// by ballot, the stack is one 64-bit {ref, tmin} word per entry in shared memory, [depth][thread].
+//
+// What round 2 changed, and why (ncu r1r, k_trace_v4 on C2 bounce rays: sm__pipe_alu_cycles_active 70 % against
+// sm__pipe_fma 19 % and issue-active 69.5 % — the kernel is bound by the half-rate ALU pipe, i.e. by PRMT / FMNMX /
+// ISETP / SEL, not by FMAs, loads or total issue slots; per round 69 ALU-pipe instructions of 146):
+//   - SIGN-SELECTED PLANES. The two planes of an axis share a word of the node (tb_trace.cuh), and the ray carries
+//     one byte-permute selector per axis and side, fixed by the sign of its direction: the PRMT that decodes the
+//     16-bit grid value picks the near or the far plane directly. The six min / max pairs per box of the generic
+//     slab test disappear: a box is 6 PRMT + 6 FFMA + max3, max(., 0), min3 + 2 compares (11 ALU-pipe instructions,
+//     was 17).
+//   - the stack pointer is the shared-memory ADDRESS of the lane's next free entry, and the row below entry 0 holds
+//     a {DONE, 0} sentinel: a pop is one LDS at [sp - row] and three selects, an empty stack pops "finished" by
+//     itself, a push is one STS at [sp] — no index arithmetic, no empty test;
+//   - OPT bit 0: a second pop in the same round when the first popped entry is already culled (a culled entry then
+//     costs 8 instructions instead of the lane's round);
+//   - OPT bit 1: a lane may park two leaves (siblings at the bottom of the tree arrive back to back; with one slot
+//     the second blocked the lane until the next triangle round);
+//   - the shared stack is sized from the tree (dynamic shared memory, TbTraceArgs::stack_smem rows), so no bench
+//     configuration runs the SPILL instantiation; trees deeper than TB_V6_MAX_SMEM_DEPTH keep 16 rows + local memory;
+//   - the three reciprocals behind the box planes are rcp.approx (1 ulp: four orders of magnitude inside the box
+//     padding); the one behind the triangle test stays IEEE (bit-exact t, u, v);
+//   - a hit record is written when the closest hit improves (the triangle's tag words are in registers right then),
+//     not at retirement: no dependent triangle re-fetch when a ray ends, and u, v need no registers;
+//   - registers (64 per thread at 8 CTAs per SM; the first version of this file spilled three selectors into local
+//     memory and re-read them every round): the axis permutation of the triangle test is one packed word, the cull
+//     distance is recomputed from the closest hit instead of carried;
+//   - finished rays are retired only when the warp has one.
+#pragma once
+
+#define TB_V6_MAX_SMEM_DEPTH   25          /* (25 + 2) rows x 1 KB x 8 CTAs = 216 KB of the SM's 228 KB */
+#define TB_V6_SPILL_SMEM_DEPTH 16
+#define TB_V6_LOCAL            (TB_STACK_SMEM + TB_STACK_LOCAL)
+
+struct TbSelRay {              // plane = fma(8388608 + q, i, o), see tb_quant_ray
+    float    ix, iy, iz, ox, oy, oz;
+    unsigned nx, ny, nz;       // PRMT selectors of the near plane of each axis (0x7610: low half, 0x7632: high half)
+    unsigned fx, fy, fz;       // ... of the far plane
+};
+
+__device__ __forceinline__ float tb_rcp_approx(float a) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+}
+__device__ __forceinline__ float tb_finite_inverse_approx(float d) {
+    const float lim = 1e-30f;
+    const float a = fabsf(d) < lim ? copysignf(lim, d) : d;
+    return tb_rcp_approx(a);
+}
+
+__device__ __forceinline__ TbSelRay tb_sel_ray(const TbRay& r, V3 d, const float* glo, const float* gcell) {
+    TbSelRay f;
+    const float ix = tb_finite_inverse_approx(d.x), iy = tb_finite_inverse_approx(d.y), iz = tb_finite_inverse_approx(d.z);
+    f.ix = gcell[0] * ix; f.iy = gcell[1] * iy; f.iz = gcell[2] * iz;
+    f.ox = __fmaf_rn(-8388608.f, f.ix, (glo[0] - r.o.x) * ix);
+    f.oy = __fmaf_rn(-8388608.f, f.iy, (glo[1] - r.o.y) * iy);
+    f.oz = __fmaf_rn(-8388608.f, f.iz, (glo[2] - r.o.z) * iz);
+    // direction >= 0: planes are entered at min (low half) and left at max (high half); < 0: the other way round
+    f.nx = ix < 0.f ? 0x7632u : 0x7610u; f.fx = ix < 0.f ? 0x7610u : 0x7632u;
+    f.ny = iy < 0.f ? 0x7632u : 0x7610u; f.fy = iy < 0.f ? 0x7610u : 0x7632u;
+    f.nz = iz < 0.f ? 0x7632u : 0x7610u; f.fz = iz < 0.f ? 0x7610u : 0x7632u;
+    return f;
+}
+
+// prmt.b32 straight (no __byte_perm: with a run-time selector that intrinsic masks it with 0x7777 first, one more
+// ALU-pipe instruction per plane)
+__device__ __forceinline__ float tb_qsel(unsigned w, unsigned sel) {
+    float r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=f"(r) : "r"(w), "r"(0x4B000000u), "r"(sel));
+    return r;
+}
+
+// One child box, planes already ordered by the ray's direction signs. tmin is clamped at 0 like every other
+// box test here (tmax > max(tmin, 0), Terra.c:877).
+__device__ __forceinline__ bool tb_box_sel(const TbSelRay& f, unsigned wx, unsigned wy, unsigned wz, float* tmin_out) {
+    const float ax = __fmaf_rn(tb_qsel(wx, f.nx), f.ix, f.ox), bx = __fmaf_rn(tb_qsel(wx, f.fx), f.ix, f.ox);
+    const float ay = __fmaf_rn(tb_qsel(wy, f.ny), f.iy, f.oy), by = __fmaf_rn(tb_qsel(wy, f.fy), f.iy, f.oy);
+    const float az = __fmaf_rn(tb_qsel(wz, f.nz), f.iz, f.oz), bz = __fmaf_rn(tb_qsel(wz, f.fz), f.iz, f.oz);
+    const float tmin = fmaxf(fmaxf(fmaxf(ax, ay), az), 0.f);
+    const float tmax = fminf(fminf(bx, by), bz);
+    *tmin_out = tmin;
+    return tmax > tmin;
+}
+
+__device__ __forceinline__ int2 tb_lds64(unsigned addr) {
+    int2 v;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void tb_sts64(unsigned addr, int2 v) {
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" :: "r"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+
+template <bool COUNT, bool EXACT, bool SPILL, int OPT>
+__global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace_v6(TbTraceArgs a) {
+    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 2][TB_TRACE_THREADS] x 8 B
+    constexpr int ROW = TB_TRACE_THREADS * 8;
+    int2 l_stack[SPILL ? TB_V6_LOCAL : 1];
+    const int tid = threadIdx.x;
+    const unsigned lane = tid & 31u;
+    const unsigned FULL = 0xffffffffu;
+    const int total = a.count_ptr ? *a.count_ptr : a.count;
+    // entry k of this lane's stack lives at bottom + k * ROW (shared-space addresses); the row below entry 0 holds the
+    // sentinel an empty pop reads, the row above the deepest entry is the scratch an unconditional push writes
+    const unsigned bottom = (unsigned)__cvta_generic_to_shared(s_v6_stack) + ROW + tid * 8;
+    tb_sts64(bottom - ROW, make_int2(TB_REF_DONE, 0));             // never culled (tmin 0), never overwritten
+    const unsigned smem_end = bottom + a.stack_smem * ROW;         // SPILL: entries from this address on live in local memory
+
+    int   slot = -1, cur = TB_REF_DONE, pend = TB_REF_DONE, pend2 = TB_REF_DONE;
+    unsigned sp = bottom;                          // address of the next free entry
+    int   best_rank = -1, best_tag = 0;
+    float best_t = FLT_MAX;
+    TbRay r;                                       // kx / ky / kz live packed in `kpack` between triangle rounds
+    r.o = r.inv = v3s(0.f); r.sx = r.sy = r.sz = 0.f; r.kx = r.ky = r.kz = 0;
+    int   kpack = 0;
+    TbSelRay sr;
+    sr.ix = sr.iy = sr.iz = sr.ox = sr.oy = sr.oz = 0.f;
+    sr.nx = sr.ny = sr.nz = sr.fx = sr.fy = sr.fz = 0u;
+    // bit 8 of kpack: the ray queue is empty — nothing to refill with, stay in the rounds to the end (a flag of its own
+    // was one register too many: the compiler spilled it and re-read it every round)
+    unsigned n_nodes = 0, n_tris = 0;
+
+    while (true) {
+        // ---- refill idle lanes (warp converged here)
+        const bool idle = cur == TB_REF_DONE && pend == TB_REF_DONE;
+        const unsigned idle_mask = __ballot_sync(FULL, idle);
+        if (idle_mask && !(kpack & 0x100)) {
+            const int want = __popc(idle_mask);
+            const int leader = __ffs(idle_mask) - 1;
+            int base = 0;
+            if ((int)lane == leader) base = atomicAdd(a.cursor, want);
+            base = __shfl_sync(FULL, base, leader);
+            if (base + want >= total) kpack |= 0x100;
+            if (idle) {
+                const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
+                if (q < total) {
+                    slot = a.queue ? a.queue[q] : q;
+                    const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
+                    const V3 d = v3(d4.x, d4.y, d4.z);
+                    r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
+                    kpack = (kpack & 0x100) | r.kx | (r.ky << 2) | (r.kz << 4);
+                    if (!EXACT) sr = tb_sel_ray(r, d, a.grid_lo, a.grid_cell);
+                    cur = 0; sp = bottom;
+                    best_rank = -1; best_t = FLT_MAX;
+                }
+            }
+        }
+        if (__ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE) == 0u) break;
+
+        // ---- rounds
+        while (true) {
+            // entries and boxes beyond this distance cannot hold the closest hit (inf while there is none: culls nothing);
+            // the margin keeps candidates with an EQUAL t alive for the smaller-rank rule
+            const float cull_t = best_t + best_t * 1e-5f;
+            // 1. park a leaf (a further leaf waits in `cur` until a parking slot is free)
+            {
+                const bool is_leaf = (unsigned)cur > (unsigned)TB_REF_POP;       // ~rank: 0x80000002 .. 0xffffffff
+                if (OPT & 2) {
+                    const bool p0 = is_leaf && pend == TB_REF_DONE;
+                    const bool p1 = is_leaf && !p0 && pend2 == TB_REF_DONE;
+                    pend = p0 ? cur : pend;
+                    pend2 = p1 ? cur : pend2;
+                    cur = (p0 || p1) ? TB_REF_POP : cur;
+                } else {
+                    const bool park = is_leaf && pend == TB_REF_DONE;
+                    pend = park ? cur : pend;
+                    cur = park ? TB_REF_POP : cur;
+                }
+            }
+            // 2. pop, resolved with selects. An entry the closest hit has culled since it was pushed leaves the
+            //    lane in POP state: with OPT bit 0 the second turn pops again at once.
+#pragma unroll
+            for (int turn = 0; turn < ((OPT & 1) ? 2 : 1); ++turn) {
+                int2 e;
+                if (SPILL && sp > smem_end) e = l_stack[(sp - smem_end) / ROW - 1];
+                else e = tb_lds64(sp - ROW);
+                const bool need = cur == TB_REF_POP;
+                const int popped = __int_as_float(e.y) > cull_t ? TB_REF_POP : e.x;
+                cur = need ? popped : cur;
+                sp = need ? sp - ROW : sp;
+            }
+            // 3. what does this round do?
+            const bool is_node = cur >= 0;
+            const unsigned node_mask = __ballot_sync(FULL, is_node);
+            const unsigned pend_mask = __ballot_sync(FULL, pend != TB_REF_DONE);
+            const bool tri_round = pend_mask != 0u && (__popc(pend_mask) >= a.tri_min || node_mask == 0u);
+            const bool do_tri = tri_round && pend != TB_REF_DONE;
+            // 4. all loads of the round first, so node and triangle latencies overlap
+            float4 q0, q1, q2, q3, ta, tb, tc;
+            uint4 qa, qb;
+            if (is_node) {
+                if (!EXACT) {
+                    const uint4* np = a.qnodes + (size_t)cur * 2;
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
+                } else {
+                    tb_load_node256(a.nodes + (size_t)cur * 4, q0, q1, q2, q3);
+                }
+            }
+            if (do_tri) {
+                const float4* tp = a.tris + (size_t)(~pend) * 3;
+                ta = __ldg(tp); tb = __ldg(tp + 1); tc = __ldg(tp + 2);
+            }
+            // 5. node step
+            if (is_node) {
+                if (COUNT) ++n_nodes;
+                int ref0, ref1;
+                float tmin0, tmin1;
+                bool hit0, hit1;
+                if (!EXACT) {
+                    ref0 = (int)qb.z; ref1 = (int)qb.w;
+                    hit0 = tb_box_sel(sr, qa.x, qa.y, qa.z, &tmin0);
+                    hit1 = tb_box_sel(sr, qa.w, qb.x, qb.y, &tmin1);
+                } else {
+                    ref0 = __float_as_int(q3.x); ref1 = __float_as_int(q3.y);
+                    hit0 = tb_box(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, &tmin0);
+                    hit1 = tb_box(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, &tmin1);
+                }
+                hit0 = hit0 && !(tmin0 > cull_t);
+                hit1 = hit1 && !(tmin1 > cull_t);
+                const bool near1 = tmin1 < tmin0;
+                const bool both = hit0 && hit1;
+                const int2 far = make_int2(near1 ? ref0 : ref1, __float_as_int(near1 ? tmin0 : tmin1));
+                if (SPILL && sp >= smem_end) l_stack[(sp - smem_end) / ROW] = far;
+                else tb_sts64(sp, far);                                    // scratch row when !both
+                sp += both ? ROW : 0;
+                const int one = hit0 ? ref0 : (hit1 ? ref1 : TB_REF_POP);
+                cur = both ? (near1 ? ref1 : ref0) : one;
+            }
+            // 6. triangle step for the parked leaves
+            if (do_tri) {
+                const int rank = ~pend;
+                if (COUNT) ++n_tris;
+                float t, u, v;
+                r.kx = kpack & 3; r.ky = (kpack >> 2) & 3; r.kz = (kpack >> 4) & 3;
+                if (tb_triangle(r, v3(ta.x, ta.y, ta.z), v3(tb.x, tb.y, tb.z), v3(tc.x, tc.y, tc.z), &t, &u, &v)) {
+                    if (t < best_t || (t == best_t && best_rank >= 0 && rank < best_rank)) {
+                        best_t = t; best_rank = rank; best_tag = __float_as_int(tb.w);
+                        // API rays: object | triangle << 8, u, v; wavefront: rank and the object | preset << 8 tag for the
+                        // shade pass (u, v are not used there). A later, closer hit overwrites the record.
+                        a.hit_out[slot] = make_float4(t, a.emit_prim ? ta.w : __int_as_float(rank), a.emit_prim ? u : tb.w, v);
+                    }
+                }
+                if (OPT & 2) { pend = pend2; pend2 = TB_REF_DONE; }
+                else pend = TB_REF_DONE;
+            }
+            // 7. leave the rounds when the warp is done or has too few rays left to be worth a round
+            const unsigned live = __ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE);
+            if (live == 0u || (!(kpack & 0x100) && __popc(live) < a.refetch_below)) break;
+        }
+
+        // ---- retire finished rays (warp converged)
+        const bool finished = cur == TB_REF_DONE && pend == TB_REF_DONE && slot >= 0;
+        if (__any_sync(FULL, finished)) {
+            int preset = -1;
+            if (finished) {
+                if (best_rank >= 0) preset = (best_tag >> 8) & 0xff;
+                else a.hit_out[slot] = make_float4(-1.f, __int_as_float(-1), 0.f, 0.f);
+            }
+            if (a.matq) {
+#pragma unroll
+                for (int p = 0; p < TB_PRESET_COUNT; ++p) {
+                    const unsigned m = __ballot_sync(FULL, finished && preset == p);
+                    if (m) {
+                        const int leader = __ffs(m) - 1;
+                        int base = 0;
+                        if ((int)lane == leader) base = atomicAdd(a.matq_count + p, __popc(m));
+                        base = __shfl_sync(FULL, base, leader);
+                        if (finished && preset == p) a.matq[(size_t)p * a.matq_stride + base + __popc(m & ((1u << lane) - 1u))] = slot;
+                    }
+                }
+            }
+            if (finished) slot = -1;
+        }
+    }
+    if (COUNT) {
+        atomicAdd(a.visit_counters, (unsigned long long)n_nodes);
+        atomicAdd(a.visit_counters + 1, (unsigned long long)n_tris);
+    }
+}
