@@ -267,8 +267,10 @@ struct TbScene {
     int               stack_bound;
     int               bvh_mode;
     float             commit_ms[4];   // last commit: tree build, flatten, quantise, upload
-    const TerraTexture* env_tex;      // environment texture of the last upload (NULL: constant environment)
-    const void*       env_pixels;
+    std::vector<uint32_t> rank_of_triangle;   // of the last flatten: [object_base[obj] + tri] -> rank (the light table needs it)
+    std::vector<size_t>   object_base;
+    std::vector<uint8_t>  presets;            // preset per object as tagged into the uploaded triangle records
+    bool              host_boxes_stale;       // terra_b200_refit moved the boxes on the device only
     TbDevice*         dev;
     uint64_t          seed;
     bool              seed_fixed;
@@ -292,6 +294,7 @@ static int bvh_mode() {
     return TB_BVH_SAH3;
 }
 static void build_bvh(TbScene* s, int mode);
+static void sync_host_nodes(TbScene* s);
 enum { TB_PREALLOCATED_OBJECTS = 64 };
 
 extern "C" HTerraScene terra_scene_create(void) {                                                   // Terra.c:130-138
@@ -306,7 +309,7 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     s->stack_bound = 0;
     s->bvh_mode = -1;
     memset(s->commit_ms, 0, sizeof s->commit_ms);
-    s->env_tex = NULL; s->env_pixels = NULL;
+    s->host_boxes_stale = false;
     s->dev = NULL;
     s->seed = 0;
     s->seed_fixed = false;
@@ -412,6 +415,17 @@ static void build_bvh(TbScene* s, int mode) {
     }
     else tb_bvh_build_sah3(s->objects, (int)s->objects_pop, s->nodes);
     s->bvh_mode = mode;
+    s->host_boxes_stale = false;
+}
+
+// After terra_b200_refit the host tree still holds the boxes of the last build. Anything that reads s->nodes
+// (a commit that re-flattens without rebuilding, terra_b200_bvh_nodes) first brings the device's boxes back.
+static void sync_host_nodes(TbScene* s) {
+    if (!s->host_boxes_stale || !s->dev) return;
+    std::vector<float> flat(s->nodes.size() * 16);
+    tb_device_download_nodes(s->dev, flat.data(), s->nodes.size());
+    for (size_t i = 0; i < s->nodes.size(); ++i) memcpy(&s->nodes[i].aabb[0], &flat[i * 16], 48);
+    s->host_boxes_stale = false;
 }
 
 extern "C" void terra_scene_commit(HTerraScene h) {                                                 // Terra.c:162-236
@@ -448,78 +462,56 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         }
     }
 
+    // ---- materials and textures are classified at EVERY commit: the reference reads object->material live at every
+    //      hit (Terra.c:1745-1762), so an in-place material / emissive edit followed by a commit must show
     TbTextureTable table;
     TbDevAttr env = classify_attribute(&s->opts.environment_map, &table, "environment_map");
-    // An options-only commit keeps the device copy of the scene; a NEW environment texture is not in it yet
-    // (the environment is texture 0 of the table), so that takes the upload path as well.
-    const TerraTexture* env_tex = table.list.empty() ? NULL : table.list[0];
-    const void* env_pixels = env_tex ? env_tex->pixels : NULL;
-    const bool new_env_texture = env_tex != NULL && (env_tex != s->env_tex || env_pixels != s->env_pixels);
-    s->env_tex = env_tex; s->env_pixels = env_pixels;
-    if (dirty_accelerator || s->dirty_lights || new_env_texture) {
-        typedef std::chrono::steady_clock Clock;
-        auto ms_since = [](Clock::time_point t0) { return std::chrono::duration<float, std::milli>(Clock::now() - t0).count(); };
+    std::vector<TbDevMaterial> mats(s->objects_pop);
+    std::vector<uint8_t> presets(s->objects_pop);
+    for (size_t i = 0; i < s->objects_pop; ++i) {
+        const TerraMaterial* m = &s->objects[i].material;
+        int preset = classify_bsdf(&m->bsdf);
+        if (preset < 0) {
+            terra_log("terra_b200: object %zu: material.bsdf is not one of terra_bsdf_{diffuse,phong,ggx,glass}_init\n", i);
+            tb_fatal("custom BSDF callbacks cannot run on the GPU and there is no CPU fallback");
+        }
+        if (m->attributes_count > TERRA_MATERIAL_MAX_ATTRIBUTES) tb_fatal("attributes_count > TERRA_MATERIAL_MAX_ATTRIBUTES");
+        memset(&mats[i], 0, sizeof mats[i]);
+        mats[i].preset = preset;
+        mats[i].attr_count = (int)m->attributes_count;
+        mats[i].ior = m->ior;
+        mats[i].light_index = -1;
+        mats[i].emissive = classify_attribute(&m->emissive, &table, "emissive");
+        for (size_t k = 0; k < m->attributes_count; ++k) mats[i].attr[k] = classify_attribute(&m->attributes[k], &table, "material");
+        presets[i] = (uint8_t)preset;
+    }
+    // the triangle records carry object | preset << 8 (the trace kernels bin hits by material without touching the
+    // material table): a preset swapped in place re-tags them, i.e. takes the geometry path without a rebuild
+    const bool retag = presets != s->presets;
+    typedef std::chrono::steady_clock Clock;
+    auto ms_since = [](Clock::time_point t0) { return std::chrono::duration<float, std::milli>(Clock::now() - t0).count(); };
+    if (dirty_accelerator || retag) {
         Clock::time_point t0 = Clock::now();
         if (dirty_accelerator) build_bvh(s, bvh_mode());
+        else sync_host_nodes(s);                        // a refit left the up-to-date boxes on the device only
+        s->host_boxes_stale = false;
         s->commit_ms[0] = ms_since(t0);
         t0 = Clock::now();
         TbFlatBvh flat;
         tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
         s->commit_ms[1] = ms_since(t0);
         s->stack_bound = flat.stack_bound;
-        std::vector<TbDevMaterial> mats(s->objects_pop);
-        for (size_t i = 0; i < s->objects_pop; ++i) {
-            const TerraMaterial* m = &s->objects[i].material;
-            int preset = classify_bsdf(&m->bsdf);
-            if (preset < 0) {
-                terra_log("terra_b200: object %zu: material.bsdf is not one of terra_bsdf_{diffuse,phong,ggx,glass}_init\n", i);
-                tb_fatal("custom BSDF callbacks cannot run on the GPU and there is no CPU fallback");
-            }
-            if (m->attributes_count > TERRA_MATERIAL_MAX_ATTRIBUTES) tb_fatal("attributes_count > TERRA_MATERIAL_MAX_ATTRIBUTES");
-            memset(&mats[i], 0, sizeof mats[i]);
-            mats[i].preset = preset;
-            mats[i].attr_count = (int)m->attributes_count;
-            mats[i].ior = m->ior;
-            mats[i].light_index = -1;
-            mats[i].emissive = classify_attribute(&m->emissive, &table, "emissive");
-            for (size_t k = 0; k < m->attributes_count; ++k) mats[i].attr[k] = classify_attribute(&m->attributes[k], &table, "material");
-        }
-        // tag every triangle record with object | preset << 8 so the trace kernel can bin hits by
-        // material without touching the material table
         for (size_t r = 0; r < total; ++r) {
             uint32_t obj;
             memcpy(&obj, &flat.tris[r * 12 + 7], 4);
             uint32_t tag = obj | ((uint32_t)mats[obj].preset << 8);
             memcpy(&flat.tris[r * 12 + 7], &tag, 4);
         }
-        std::vector<TbDevLight> lights(s->lights.size());
-        std::vector<float> light_area;
-        std::vector<uint32_t> light_rank;
-        for (size_t l = 0; l < s->lights.size(); ++l) {
-            size_t obj = s->lights[l].object;
-            lights[l].object = (int32_t)obj;
-            lights[l].tri_count = (uint32_t)s->objects[obj].triangles_count;
-            lights[l].tri_base = (uint32_t)light_area.size();
-            lights[l].area = s->lights[l].area;
-            mats[obj].light_index = (int32_t)l;
-            for (size_t j = 0; j < s->objects[obj].triangles_count; ++j) {
-                light_area.push_back(s->lights[l].triangle_area[j]);
-                light_rank.push_back(flat.rank_of_triangle[flat.object_base[obj] + j]);
-            }
-        }
         TbFlatScene up;
         memset(&up, 0, sizeof up);
         up.nodes = flat.nodes.data();   up.n_nodes = s->nodes.size();
         up.tris = flat.tris.data();     up.n_tris = total;
         up.props = flat.props.data();
-        up.materials = mats.data();     up.n_objects = s->objects_pop;
-        up.lights = lights.data();      up.n_lights = lights.size();
-        up.light_tri_area = light_area.data();
-        up.light_tri_rank = light_rank.data();
-        up.n_light_tris = light_area.size();
-        up.textures = table.list.data(); up.n_textures = table.list.size();
-        up.lights_triangles_count = s->lights_triangles_count;
-        up.env = env;
         up.stack_bound = flat.stack_bound;
         up.exact_boxes = s->bvh_mode == TB_BVH_REFERENCE ? 1 : 0;
         t0 = Clock::now();
@@ -532,9 +524,42 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         }
         s->commit_ms[2] = ms_since(t0);
         t0 = Clock::now();
-        tb_device_upload(s->dev, &up);
+        tb_device_upload_geometry(s->dev, &up);
         s->commit_ms[3] = ms_since(t0);
+        s->rank_of_triangle.swap(flat.rank_of_triangle);
+        s->object_base.swap(flat.object_base);
+        s->presets = presets;
         s->has_bvh = true;
+    }
+    {
+        std::vector<TbDevLight> lights(s->lights.size());
+        std::vector<float> light_area;
+        std::vector<uint32_t> light_rank;
+        for (size_t l = 0; l < s->lights.size(); ++l) {
+            size_t obj = s->lights[l].object;
+            lights[l].object = (int32_t)obj;
+            lights[l].tri_count = (uint32_t)s->objects[obj].triangles_count;
+            lights[l].tri_base = (uint32_t)light_area.size();
+            lights[l].area = s->lights[l].area;
+            mats[obj].light_index = (int32_t)l;
+            for (size_t j = 0; j < s->objects[obj].triangles_count; ++j) {
+                light_area.push_back(s->lights[l].triangle_area[j]);
+                light_rank.push_back(s->rank_of_triangle[s->object_base[obj] + j]);
+            }
+        }
+        TbFlatScene up;
+        memset(&up, 0, sizeof up);
+        up.materials = mats.data();     up.n_objects = s->objects_pop;
+        up.lights = lights.data();      up.n_lights = lights.size();
+        up.light_tri_area = light_area.data();
+        up.light_tri_rank = light_rank.data();
+        up.n_light_tris = light_area.size();
+        up.textures = table.list.data(); up.n_textures = table.list.size();
+        up.lights_triangles_count = s->lights_triangles_count;
+        up.env = env;
+        Clock::time_point t0 = Clock::now();
+        tb_device_upload_tables(s->dev, &up);
+        if (!(dirty_accelerator || retag)) s->commit_ms[3] = ms_since(t0);
     }
     tb_device_set_options(s->dev, &s->opts, &env);
     s->dirty_objects = false;
@@ -698,12 +723,15 @@ extern "C" float terra_b200_refit(HTerraScene h) {
     float ms = 0.f;
     tb_device_refit(s->dev, tris.data(), props.data(), base.data(), s->objects_pop, lights.data(), lights.size(),
                     light_area.data(), light_area.size(), &ms);
+    s->host_boxes_stale = true;
     return ms;
 }
 extern "C" void terra_b200_set_graph_paths(HTerraScene h, size_t max_paths) { tb_device_set_graph_paths(committed(h, "terra_b200_set_graph_paths")->dev, max_paths); }
 extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;
+    std::lock_guard<std::mutex> guard(s->lock);
+    sync_host_nodes(s);
     *nodes_count = (int)s->nodes.size();
     return s->nodes.data();
 }

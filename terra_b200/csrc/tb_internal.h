@@ -124,7 +124,9 @@ extern "C" {
 #endif
 TbDevice* tb_device_create(int device_index);
 void      tb_device_destroy(TbDevice* dev);
-void      tb_device_upload(TbDevice* dev, const TbFlatScene* flat);
+void      tb_device_upload_geometry(TbDevice* dev, const TbFlatScene* flat);
+void      tb_device_upload_tables(TbDevice* dev, const TbFlatScene* flat);
+void      tb_device_download_nodes(TbDevice* dev, float* out16, size_t n_nodes);
 void      tb_device_set_options(TbDevice* dev, const TerraSceneOptions* opts, const TbDevAttr* env);
 void      tb_device_render(TbDevice* dev, const TbCameraFrame* cam, const TerraFramebuffer* fb,
                            size_t x, size_t y, size_t w, size_t h, size_t spp, uint64_t seed);

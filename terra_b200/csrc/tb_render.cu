@@ -121,6 +121,7 @@ struct TbCallParams {
     void*    results;           // device-resident calls: the caller's full-framebuffer results array (k_finalize)
 };
 
+struct TbTextureSig { const void* host; const void* pixels; uint32_t width, height, components, depth, filter, address_mode; };
 struct TbEventPair { cudaEvent_t a, b; int coherent; };
 
 struct TbDevice {
@@ -139,6 +140,7 @@ struct TbDevice {
     uint32_t*      d_light_rank;
     std::vector<void*> tex_pixels;
     std::vector<TbDevTexture> h_texs;    // host copy of the texture table (dims for the environment importance map)
+    std::vector<TbTextureSig> tex_sig;   // what the device copies of the textures were made from
     float       *d_env_f, *d_env_cdf, *d_env_rows, *d_env_marg;   // TbDevDist2D storage of sc.env_dist
     int          stack_bound;
     TbWave       wave;
@@ -310,6 +312,7 @@ static void tb_scene_free(TbDevice* d) {
     tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
     for (void* p : d->tex_pixels) tb_free(p);
     d->tex_pixels.clear();
+    d->tex_sig.clear();
     tb_free(d->d_env_f); tb_free(d->d_env_cdf); tb_free(d->d_env_rows); tb_free(d->d_env_marg);
     d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
     d->sc.env_nee = 0;
@@ -348,7 +351,8 @@ template <typename T> static T* tb_upload(const T* host, size_t n, TbDevice* d) 
     return p;
 }
 
-extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
+// Geometry half of a commit: nodes, rank-ordered triangle / property records, quantised nodes.
+extern "C" void tb_device_upload_geometry(TbDevice* d, const TbFlatScene* f) {
     TB_CUDA(cudaSetDevice(d->index));
     TB_CUDA(cudaStreamSynchronize(d->stream));
     if (f->stack_bound > TB_STACK_SMEM + TB_STACK_LOCAL) {
@@ -356,7 +360,8 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
         abort();
     }
     d->graph_epoch++;
-    tb_scene_free(d);
+    tb_free(d->d_nodes); tb_free(d->d_tris); tb_free(d->d_props); tb_free(d->d_qnodes);
+    d->d_qnodes = NULL;
     d->d_nodes = (float4*)tb_upload(f->nodes, f->n_nodes * 16, d);
     d->d_tris = (float4*)tb_upload(f->tris, f->n_tris * 12, d);
     if (f->qnodes) {
@@ -365,37 +370,74 @@ extern "C" void tb_device_upload(TbDevice* d, const TbFlatScene* f) {
         memcpy(d->grid_cell, f->grid_cell, sizeof d->grid_cell);
     }
     d->d_props = (float4*)tb_upload(f->props, f->n_tris * 16, d);
-    std::vector<TbDevMaterial> mats(f->materials, f->materials + f->n_objects);
-    d->d_mats = tb_upload(mats.data(), mats.size(), d);
-    std::vector<TbDevTexture> texs(f->n_textures);
-    for (size_t i = 0; i < f->n_textures; ++i) {
-        const TerraTexture* t = f->textures[i];
-        size_t bytes = (size_t)t->width * t->height * t->components * t->depth;
-        void* px = tb_upload((const uint8_t*)t->pixels, bytes, d);
-        d->tex_pixels.push_back(px);
-        texs[i].pixels = px;
-        texs[i].width = t->width; texs[i].height = t->height;
-        texs[i].components = t->components; texs[i].depth = t->depth;
-        texs[i].filter = t->filter; texs[i].address_mode = t->address_mode;
-        texs[i].pad_ = 0;
-    }
-    d->d_texs = tb_upload(texs.data(), texs.size(), d);
-    d->h_texs = texs;
-    d->d_lights = tb_upload(f->lights, f->n_lights, d);
-    d->d_light_area = tb_upload(f->light_tri_area, f->n_light_tris, d);
-    d->d_light_rank = tb_upload(f->light_tri_rank, f->n_light_tris, d);
     d->stack_bound = f->stack_bound;
     d->exact_boxes = f->exact_boxes;
     TbDevScene& sc = d->sc;
     sc.nodes = d->d_nodes; sc.tris = d->d_tris; sc.props = d->d_props;
+    sc.n_nodes = (int)f->n_nodes; sc.n_tris = (int)f->n_tris;
+}
+
+// Table half of a commit, run at EVERY commit (the reference reads object->material live at every hit, so an
+// in-place material edit followed by a commit must show): materials, light table, textures. Texel data goes up
+// again only when the set of textures (address, pixel pointer, shape, modes) changed.
+extern "C" void tb_device_upload_tables(TbDevice* d, const TbFlatScene* f) {
+    TB_CUDA(cudaSetDevice(d->index));
+    TB_CUDA(cudaStreamSynchronize(d->stream));
+    d->graph_epoch++;
+    tb_free(d->d_mats); tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
+    std::vector<TbDevMaterial> mats(f->materials, f->materials + f->n_objects);
+    d->d_mats = tb_upload(mats.data(), mats.size(), d);
+    d->d_lights = tb_upload(f->lights, f->n_lights, d);
+    d->d_light_area = tb_upload(f->light_tri_area, f->n_light_tris, d);
+    d->d_light_rank = tb_upload(f->light_tri_rank, f->n_light_tris, d);
+    std::vector<TbTextureSig> sig(f->n_textures);
+    for (size_t i = 0; i < f->n_textures; ++i) {
+        const TerraTexture* t = f->textures[i];
+        TbTextureSig g;
+        memset(&g, 0, sizeof g);
+        g.host = t; g.pixels = t->pixels; g.width = t->width; g.height = t->height;
+        g.components = t->components; g.depth = t->depth; g.filter = t->filter; g.address_mode = t->address_mode;
+        sig[i] = g;
+    }
+    const bool same = sig.size() == d->tex_sig.size() &&
+                      (sig.empty() || memcmp(sig.data(), d->tex_sig.data(), sig.size() * sizeof(TbTextureSig)) == 0);
+    if (!same) {
+        for (void* p : d->tex_pixels) tb_free(p);
+        d->tex_pixels.clear();
+        tb_free(d->d_texs);
+        std::vector<TbDevTexture> texs(f->n_textures);
+        for (size_t i = 0; i < f->n_textures; ++i) {
+            const TerraTexture* t = f->textures[i];
+            size_t bytes = (size_t)t->width * t->height * t->components * t->depth;
+            void* px = tb_upload((const uint8_t*)t->pixels, bytes, d);
+            d->tex_pixels.push_back(px);
+            texs[i].pixels = px;
+            texs[i].width = t->width; texs[i].height = t->height;
+            texs[i].components = t->components; texs[i].depth = t->depth;
+            texs[i].filter = t->filter; texs[i].address_mode = t->address_mode;
+            texs[i].pad_ = 0;
+        }
+        d->d_texs = tb_upload(texs.data(), texs.size(), d);
+        d->h_texs = texs;
+        d->tex_sig = sig;
+    }
+    TbDevScene& sc = d->sc;
     sc.materials = d->d_mats; sc.textures = d->d_texs; sc.lights = d->d_lights;
     sc.light_tri_area = d->d_light_area; sc.light_tri_rank = d->d_light_rank;
-    sc.n_nodes = (int)f->n_nodes; sc.n_tris = (int)f->n_tris;
     sc.n_objects = (int)f->n_objects; sc.n_lights = (int)f->n_lights;
     sc.lights_triangles_count = f->lights_triangles_count;
     sc.env = f->env;
     sc.preset_mask = 0;
     for (size_t i = 0; i < f->n_objects; ++i) sc.preset_mask |= 1 << f->materials[i].preset;
+}
+
+// The device's float nodes (16 floats each, the flatten layout) back to the host: after a refit they are the
+// only up-to-date boxes.
+extern "C" void tb_device_download_nodes(TbDevice* d, float* out, size_t n_nodes) {
+    TB_CUDA(cudaSetDevice(d->index));
+    TB_CUDA(cudaStreamSynchronize(d->stream));
+    TB_CUDA(cudaMemcpy(out, d->d_nodes, n_nodes * 16 * sizeof(float), cudaMemcpyDeviceToHost));
+    d->stats.d2h_bytes += n_nodes * 64;
 }
 
 extern "C" void tb_device_set_env_lit(TbDevice* d, int on);
@@ -1335,7 +1377,7 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         return;
     }
     if (kind == TB_K_V6) {
-        static const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
+        const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
         int rows = d->stack_bound > 1 ? d->stack_bound : 1;
         if (forced > 0 && forced < rows) rows = forced;
         const bool spill = rows > TB_V6_MAX_SMEM_DEPTH || rows < d->stack_bound;

@@ -157,3 +157,63 @@ class no_commit:
 def build_host(scenes, api, lib, name, **over):
     with no_commit(api):
         return build(scenes, lib, name, **over)
+
+
+# ---- 2-D texture-mapped material attributes (reference src/Terra.c:368-466 sampling, :1748-1752 texcoord
+#      interpolation, :1804-1810 attribute dispatch): a Cornell box whose wall albedos AND emissives are textures
+def _uv_quad(scenes, p0, p1, p2, p3, uv0, uv1, uv2, uv3):
+    """scenes.quad's two triangles (p0-p2-p1, p0-p3-p2) with per-vertex texcoords in TEXEL units."""
+    tris = scenes.quad(p0, p1, p2, p3)
+    uv = np.asarray([[uv0, uv2, uv1], [uv0, uv3, uv2]], np.float32)
+    return tris, uv
+
+
+def texture_images():
+    rng = np.random.default_rng(23)
+    tex8 = rng.integers(8, 256, (7, 5, 3), dtype=np.uint8)            # h, w, c; no zero texel: every emissive lookup lights
+    texf = rng.uniform(0.05, 0.9, (6, 8, 3)).astype(np.float32)
+    return tex8, texf
+
+
+TEXTURED_CASES = {      # name -> scene kwargs; bounces 0 + jitter 0: the image is the emissive lookup at the first hit, no random numbers
+    "textured_emissive": dict(integrator=0, spp=2, bounces=0, jitter=0.0),
+}
+TEXTURED_SIZE = (48, 40)
+
+
+def textured_cornell(scenes, api, lib, *, integrator=0, spp=2, bounces=0, jitter=0.0, emissive_scale=1.0, commit=True):
+    """Five walls, each its own object and its own (texture, filter, address mode) pair bound to BOTH albedo and
+    emissive; texcoords chosen so that every address mode leaves its first period without touching the texels the
+    reference's mirror arithmetic indexes one past the edge (Terra.c:385-386): in a mirrored period x % w and
+    y % h stay away from 0."""
+    s = api.Scene(lib)
+    tex8, texf = texture_images()
+    if emissive_scale != 1.0:
+        texf = (texf * np.float32(emissive_scale)).astype(np.float32)
+    F, A = api, api
+    walls = [
+        # floor: u8, point, wrap — three periods in u, two in v
+        (((0, 0, 0), (1, 0, 0), (1, 0, 1), (0, 0, 1)), ((0.2, 0.3), (14.6, 0.3), (14.6, 13.4), (0.2, 13.4)), tex8, F.FILTER_POINT, A.ADDRESS_WRAP),
+        # ceiling: f32, bilinear, clamp — runs past the last texel
+        (((0, 1, 0), (0, 1, 1), (1, 1, 1), (1, 1, 0)), ((0.4, 0.2), (0.4, 9.7), (12.3, 9.7), (12.3, 0.2)), texf, F.FILTER_BILINEAR, A.ADDRESS_CLAMP),
+        # back: u8, bilinear, wrap
+        (((0, 0, 1), (1, 0, 1), (1, 1, 1), (0, 1, 1)), ((0.1, 0.1), (9.3, 0.1), (9.3, 12.8), (0.1, 12.8)), tex8, F.FILTER_BILINEAR, A.ADDRESS_WRAP),
+        # left: f32, point, mirror — inside the SECOND (mirrored) period of the 8x6 texture, away from its edges
+        (((0, 0, 0), (0, 0, 1), (0, 1, 1), (0, 1, 0)), ((9.2, 1.2), (14.8, 1.2), (14.8, 5.8), (9.2, 5.8)), texf, F.FILTER_POINT, A.ADDRESS_MIRROR),
+        # right: u8, point, clamp
+        (((1, 0, 0), (1, 1, 0), (1, 1, 1), (1, 0, 1)), ((0.0, 0.0), (0.0, 8.5), (6.5, 8.5), (6.5, 0.0)), tex8, F.FILTER_POINT, A.ADDRESS_CLAMP),
+    ]
+    for (p, uv, img, filt, addr) in walls:
+        tris, tuv = _uv_quad(scenes, *p, *uv)
+        o = s.add_object(tris, texcoords=tuv)
+        s.set_diffuse(o, (0.5, 0.5, 0.5))
+        tex = s.make_texture(img, filter=filt, address=addr)
+        lib.terra_attribute_init_texture(C.byref(o.material.attributes[0]), C.byref(tex))
+        lib.terra_attribute_init_texture(C.byref(o.material.emissive), C.byref(tex))
+    # a plain box in the middle so that some first hits are untextured and the walls get shadowed bounce light
+    s.set_diffuse(s.add_object(scenes.box((0.35, 0.0, 0.35), (0.65, 0.45, 0.65), rot_y=0.3)), (0.7, 0.7, 0.7))
+    s.set_options(integrator=integrator, spp=spp, bounces=bounces, jitter=jitter)
+    if commit:
+        s.commit()
+    cam = scenes.make_camera((0.5, 0.5, -1.35), (0, 0, 1), (0, 1, 0), 45.0)
+    return s, cam

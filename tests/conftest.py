@@ -27,8 +27,13 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")
 
 
+def _harness_api():
+    from oracle.binding import harness_api      # terra_b200.api + the checker bindings (oracle/binding.py) as one namespace
+    return harness_api()
+
+
 def _ensure_built():
-    from terra_b200 import api
+    api = _harness_api()
     if not api.PRODUCT_LIB.exists():
         subprocess.run(["sh", str(REPO / "build.sh")], check=True)
     if not api.ORACLE_LIB.exists() or (Path("/root/reference/src").is_dir() and not api.REFERENCE_LIB.exists()):
@@ -38,8 +43,7 @@ def _ensure_built():
 @pytest.fixture(scope="session")
 def api():
     _ensure_built()
-    from terra_b200 import api as _api
-    return _api
+    return _harness_api()
 
 
 @pytest.fixture(scope="session")

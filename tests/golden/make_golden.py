@@ -18,7 +18,10 @@ sys.path.insert(0, str(REPO))
 sys.path.insert(0, str(REPO / "tests"))
 
 import cases  # noqa: E402
-from terra_b200 import api, scenes  # noqa: E402
+from terra_b200 import scenes  # noqa: E402
+from oracle.binding import harness_api  # noqa: E402
+
+api = harness_api()
 
 OUT = Path(__file__).resolve().parent
 
@@ -152,6 +155,18 @@ def main():
         out[f"{tname}_latlong"] = r
     out["tex8"], out["texf"] = tex8, texf
     np.savez_compressed(OUT / "textures.npz", **out)
+    # ---- 2-D texture-mapped material attributes through the whole renderer (Terra.c:368-466, 1748-1752, 1804-1810)
+    out = {}
+    tw, th = cases.TEXTURED_SIZE
+    for name, kw in cases.TEXTURED_CASES.items():
+        s, cam = cases.textured_cornell(scenes, api, ref, **kw)
+        _, rays, paths, res, pix = s.ref_render_farm(cam, tw, th, kw["spp"], tile=max(tw, th), nproc=1, seed=cases.RENDER_SEED)
+        out[f"{name}_acc"] = res["acc"]
+        out[f"{name}_samples"] = res["samples"]
+        hits, _ = s.ref_primary_hits(cam, tw, th)
+        out[f"{name}_primary"] = hits
+        s.destroy()
+    np.savez_compressed(OUT / "textured.npz", **out)
     # ---- discrete distributions (Terra.c:760-846), the reference's exported functions called directly
     np.savez_compressed(OUT / "distribution.npz", **distribution_fixture(api, ref))
     print("golden fixtures written to", OUT)

@@ -156,6 +156,16 @@ def test_medium_scene_vs_oracle(api, scenes, gpu, oracle):
         # a sample of those rays through the reference's own un-culled walk of ITS tree
         ref_walk = osc.trace_rays(o[:300], d[:300])
         assert np.array_equal(bits(got["t"][:300]), bits(ref_walk["t"]))
+        # primary hits at 320x180 (camera rays: the packet kernel) against the oracle's walk of the reference tree
+        w, h = 320, 180
+        prim = s.primary_hits(cam, w, h)
+        want_prim, _ = osc.primary_hits(cam, w, h)
+        assert (want_prim["t"] >= 0).mean() > 0.3
+        assert np.array_equal(bits(prim["t"]), bits(want_prim["t"]))
+        assert (prim["prim"] != want_prim["prim"]).mean() < 1e-3
+        same = prim["prim"] == want_prim["prim"]
+        assert np.array_equal(bits(prim["u"][same]), bits(want_prim["u"][same]))
+        assert np.array_equal(bits(prim["v"][same]), bits(want_prim["v"][same]))
         osc.destroy()
         s.destroy()
 

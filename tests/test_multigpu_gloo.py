@@ -45,7 +45,9 @@ def _worker(rank, world, port, mode, out_path):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     import cases
-    from terra_b200 import api, scenes
+    from terra_b200 import scenes
+    from oracle.binding import harness_api
+    api = harness_api()
     from terra_b200.multigpu import float_as_results, reduce_partials, results_as_float, split_rows, split_samples
     prod, oracle = api.TerraLib(), api.OracleLib()
     W = H = 24
@@ -79,7 +81,9 @@ def _worker(rank, world, port, mode, out_path):
 def test_two_rank_reduce_matches_single_process(tmp_path, mode):
     sys.path.insert(0, str(REPO / "tests"))
     import cases
-    from terra_b200 import api, scenes
+    from terra_b200 import scenes
+    from oracle.binding import harness_api
+    api = harness_api()
     out = tmp_path / "reduced.npy"
     mp.spawn(_worker, args=(2, _free_port(), mode, str(out)), nprocs=2, join=True)
     got = np.load(out).view(api.RESULT_DTYPE).reshape(24, 24)

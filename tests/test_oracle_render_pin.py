@@ -155,3 +155,23 @@ def test_envlit_oracle_vs_patched_reference_live(api, scenes, oracle, oracle_pre
     res, _ = osc.render(cam, 24, 24)
     assert np.array_equal(bits(res["acc"]), bits(rres["acc"]))
     osc.destroy(); s2.destroy(); s.destroy()
+
+
+@pytest.mark.parametrize("name", list(cases.TEXTURED_CASES))
+def test_textured_attributes_bit_exact_vs_golden(api, scenes, prod, oracle, name):
+    """2-D texture-mapped albedo / emissive (terra_texture_sample Terra.c:410-466, terra_texture_read :368-408 with
+    its three address modes, texcoord interpolation :1748-1752, attribute dispatch :1804-1810) through the whole
+    renderer: the oracle's integrator over the PRODUCT's host texture callbacks (tb_texture.h, the code the
+    kernels compile) reproduces the fixture the unmodified reference rendered, bit for bit."""
+    g = golden("textured.npz")
+    w, h = cases.TEXTURED_SIZE
+    s, cam = cases.textured_cornell(scenes, api, prod, commit=False, **cases.TEXTURED_CASES[name])
+    osc = api.OracleScene(oracle, s)
+    api.srand(cases.RENDER_SEED + 1)
+    res, _ = osc.render(cam, w, h)
+    osc.destroy()
+    s.destroy()
+    assert np.array_equal(res["samples"], g[f"{name}_samples"])
+    assert np.array_equal(bits(res["acc"]), bits(g[f"{name}_acc"]))
+    lit = g[f"{name}_acc"].sum(axis=-1) > 0
+    assert lit.mean() > 0.5           # the textured walls fill most of the frame: the test is not vacuous
