@@ -292,10 +292,23 @@ typedef struct {
     double   coherent_kernel_ms;
     uint64_t coherent_kernel_launches;
     uint64_t coherent_nodes_visited, coherent_tris_tested;
+    uint64_t p2p_bytes;          /* device-to-device copies (scene replicas over NVLink) */
 } TerraB200Stats;
 
 int  terra_b200_device_count(void);
 void terra_b200_set_device(int device);              /* before terra_scene_commit */
+/* Multi-GPU behind terra_render (the splitter of SURVEY 8b / 8e; the reference's own fan-out is one terra_render per
+ * tile from a thread pool, satellite/src/Renderer.cpp:316-349): a scene lives on one or more GPUs of one box —
+ * terra_b200_scene_set_devices before its first commit, default the environment variable TERRA_B200_DEVICES
+ * ("0,1,2,3" or "all"), else the terra_b200_set_device one. terra_scene_commit replicates the scene (geometry goes
+ * up once and is copied device to device over NVLink). A terra_render call of at least min_paths (pixel, sample)
+ * pairs (default 16M) is then split by sample range: GPU g renders range g of the whole region, and finalises and
+ * returns row band g of it, summing the band over all GPUs' accumulators through peer-mapped memory inside the
+ * accumulate / tonemap kernel. Smaller calls, and every other entry point, run on the first device. Sample ranges
+ * use the same counter-based random numbers as one GPU; the per-pixel float sum re-associates. */
+void terra_b200_scene_set_devices(HTerraScene scene, const int* device_ids, int count);
+int  terra_b200_scene_device_count(HTerraScene scene);
+void terra_b200_set_fanout_min_paths(HTerraScene scene, size_t min_paths);
 void terra_b200_set_seed(HTerraScene scene, uint64_t seed);   /* default: time based, like the reference */
 void terra_b200_get_stats(HTerraScene scene, TerraB200Stats* out);
 void terra_b200_reset_stats(HTerraScene scene);
@@ -331,17 +344,17 @@ void        terra_b200_set_bvh_mode(int mode);
  * leaves the scene adds throughput * environment_map(direction) (constant, 2-D texture or lat-long texture,
  * src/Terra.c:468-477, 1804-1810). Off by default; call after terra_scene_commit. Checked against the
  * reference compiled with exactly that one line restored (oracle/Makefile, "patched oracle"). */
-void        terra_b200_set_env_lit(HTerraScene scene, int on);
 /* on = 2 ("env-lit, importance sampled"): the same radiance as on = 1, estimated with explicit environment
  * samples in the direct and direct-MIS integrators: the reference's written-but-never-called
  * TerraDistributon2D (src/Terra.c:760-846) over luminance x sin(theta) of the lat-long environment texture picks
  * a direction per bounce, a visibility ray tests it, power-heuristic weights combine it with the BSDF sample
  * under MIS, and rays that leave the scene count at the camera ray only. Needs a lat-long environment
  * (terra_attribute_init_cubemap); anything else behaves as on = 1. The simple integrator is unchanged. */
+void        terra_b200_set_env_lit(HTerraScene scene, int on);
 
 /* terra_distribution_2d_init + n x terra_distribution_2d_sample (src/Terra.c:811-846) on the device, for a
  * function f of ny rows x nx columns: out4[4*i] = { s1 (row axis), s2 (column axis), pdf, 0 } for (e1[i], e2[i]).
- * Bit-identical to the reference's exported functions (tests/test_gpu_distribution.py). */
+ * Bit-identical to the reference's exported functions (tests/test_distribution.py). */
 void        terra_b200_distribution_2d_sample(HTerraScene scene, const float* f, size_t nx, size_t ny, size_t n,
                                               const float* e1, const float* e2, float* out4);
 /* Wall time of the last terra_scene_commit's stages, ms: [0] tree build (terra_bvh_create's replacement),

@@ -23,28 +23,27 @@ C3_VARIANTS = [
     ("v4 (round 1)", dict(TERRA_B200_INCOHERENT="v4")),
     ("v6 opt0", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0")),
     ("v6 opt1 (double pop)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1")),
-    ("v6 opt2 (two parking slots)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="2")),
-    ("v6 opt3", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="3")),
-    ("v6 opt1 stack 16 rows + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_STACK_SMEM="16")),
-    ("v6 opt0 stack 16 rows + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_STACK_SMEM="16")),
-    ("v6 opt1 tri_min 4", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_TRI_MIN="4")),
-    ("v6 opt1 tri_min 12", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_TRI_MIN="12")),
-    ("v6 opt1 tri_min 16", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_TRI_MIN="16")),
-    ("v6 opt3 tri_min 12", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="3", TERRA_B200_TRI_MIN="12")),
-    ("v6 opt1 refetch 22", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_REFETCH="22")),
-    ("v6 opt1 refetch 29", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_REFETCH="29")),
+    ("v6 opt4 (cache hints)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4")),
+    ("v6 opt5 (double pop + cache hints)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="5")),
+    ("v6 opt0 preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_NODE_ORDER="preorder")),
+    ("v6 opt4 preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder")),
+    ("v6 opt5 preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="5", TERRA_B200_NODE_ORDER="preorder")),
+    ("v4 preorder", dict(TERRA_B200_INCOHERENT="v4", TERRA_B200_NODE_ORDER="preorder")),
+    ("v6 opt4 preorder stack 16 + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_STACK_SMEM="16")),
+    ("v6 opt4 preorder stack 20 + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_STACK_SMEM="20")),
+    ("v6 opt4 preorder refetch 22", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_REFETCH="22")),
+    ("v6 opt4 preorder tri_min 6", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_TRI_MIN="6")),
 ]
 C2_VARIANTS = [
     ("round-1 kernels (v4, k_raygen)", dict(TERRA_B200_INCOHERENT="v4", TERRA_B200_FUSED_RAYGEN="0")),
-    ("v4 + fused raygen", dict(TERRA_B200_INCOHERENT="v4", TERRA_B200_FUSED_RAYGEN="1")),
-    ("v6 opt1, k_raygen", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_FUSED_RAYGEN="0")),
     ("v6 opt0 + fused raygen", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_FUSED_RAYGEN="1")),
-    ("v6 opt1 + fused raygen (default)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_FUSED_RAYGEN="1")),
-    ("v6 opt3 + fused raygen", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="3", TERRA_B200_FUSED_RAYGEN="1")),
-    ("v6 opt1 + fused, stack 16 + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_STACK_SMEM="16")),
+    ("v6 opt4 + fused raygen", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_FUSED_RAYGEN="1")),
+    ("v6 opt0 + fused raygen, preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_NODE_ORDER="preorder")),
+    ("v6 opt4 + fused raygen, preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_NODE_ORDER="preorder")),
+    ("v6 opt5 + fused raygen, preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="5", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_NODE_ORDER="preorder")),
 ]
 SWITCHES = ["TERRA_B200_INCOHERENT", "TERRA_B200_COHERENT", "TERRA_B200_V6_OPT", "TERRA_B200_STACK_SMEM", "TERRA_B200_TRI_MIN",
-            "TERRA_B200_REFETCH", "TERRA_B200_FUSED_RAYGEN"]
+            "TERRA_B200_REFETCH", "TERRA_B200_FUSED_RAYGEN", "TERRA_B200_NODE_ORDER"]
 
 
 def set_env(env):

@@ -39,7 +39,11 @@ smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio smsp__a
 smsp__average_warps_issue_stalled_wait_per_issue_active.ratio smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio
 smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio
 smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio
-launch__shared_mem_per_block_static launch__occupancy_limit_registers launch__occupancy_limit_shared_mem sm__cycles_active.avg""".split()
+launch__shared_mem_per_block_static launch__shared_mem_per_block_dynamic launch__occupancy_limit_registers launch__occupancy_limit_shared_mem sm__cycles_active.avg
+sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active
+sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active
+l1tex__data_pipe_lsu_wavefronts.avg l1tex__data_pipe_lsu_wavefronts_mem_shared.avg l1tex__data_pipe_lsu_wavefronts_mem_lgds.avg
+l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum smsp__inst_executed_pipe_alu.sum smsp__inst_executed_pipe_fma.sum smsp__inst_executed_pipe_lsu.sum""".split()
 for rep in reps:
     p = REPO / "gpurun_out" / f"{tag}_{rep}.ncu-rep"
     if not p.exists():

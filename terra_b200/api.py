@@ -96,7 +96,7 @@ class Stats(C.Structure):
                 ("render_ms", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64), ("graph_replays", C.c_uint64),
                 ("coherent_rays", C.c_uint64), ("coherent_kernel_ms", C.c_double), ("coherent_kernel_launches", C.c_uint64),
-                ("coherent_nodes_visited", C.c_uint64), ("coherent_tris_tested", C.c_uint64)]
+                ("coherent_nodes_visited", C.c_uint64), ("coherent_tris_tested", C.c_uint64), ("p2p_bytes", C.c_uint64)]
 
 
 HIT_DTYPE = np.dtype([("t", "<f4"), ("prim", "<u4"), ("u", "<f4"), ("v", "<f4")])
@@ -169,6 +169,9 @@ class TerraLib:
             sig("terra_bsdf_glass_init", None, C.POINTER(BSDF))
             sig("terra_b200_device_count", C.c_int)
             sig("terra_b200_set_device", None, C.c_int)
+            sig("terra_b200_scene_set_devices", None, _vp, C.POINTER(C.c_int), C.c_int)
+            sig("terra_b200_scene_device_count", C.c_int, _vp)
+            sig("terra_b200_set_fanout_min_paths", None, _vp, _sz)
             sig("terra_b200_probe_bandwidth", C.c_double, _sz, C.c_int)
             sig("terra_b200_set_env_lit", None, _vp, C.c_int)
             sig("terra_b200_render_async", _vp, C.POINTER(Camera), _vp, C.POINTER(Framebuffer), _sz, _sz, _sz, _sz, _sz, _vp, _vp, _vp)

@@ -271,7 +271,11 @@ struct TbScene {
     std::vector<size_t>   object_base;
     std::vector<uint8_t>  presets;            // preset per object as tagged into the uploaded triangle records
     bool              host_boxes_stale;       // terra_b200_refit moved the boxes on the device only
-    TbDevice*         dev;
+    TbDevice*         dev;            // primary device: every entry point but a fanned-out terra_render runs here
+    std::vector<int>  device_ids;     // devices of this scene (terra_b200_scene_set_devices / TERRA_B200_DEVICES), [0] = primary
+    std::vector<TbDevice*> devs;      // one per device_ids entry once committed; devs[0] == dev
+    bool              peers_ok;       // every pair of the scene's devices can map the other's memory
+    size_t            fanout_min_paths;   // terra_render calls of at least this many paths are split over the devices
     uint64_t          seed;
     bool              seed_fixed;
     uint64_t          render_calls;
@@ -279,6 +283,28 @@ struct TbScene {
 };
 
 static int g_device_index = 0;
+// Devices a new scene renders on: TERRA_B200_DEVICES="0,1,2,3" (or "all"), else the one terra_b200_set_device chose.
+// The scene is replicated on each of them at commit; a large terra_render call is split over them by sample range.
+static std::vector<int> default_device_ids() {
+    std::vector<int> ids;
+    const char* e = getenv("TERRA_B200_DEVICES");
+    if (e && *e) {
+        if (strcmp(e, "all") == 0) {
+            const int n = tb_cuda_device_count();
+            for (int i = 0; i < n; ++i) ids.push_back(i);
+        } else {
+            for (const char* p = e; *p;) {
+                char* end = NULL;
+                const long v = strtol(p, &end, 10);
+                if (end == p) break;
+                ids.push_back((int)v);
+                p = *end == ',' ? end + 1 : end;
+            }
+        }
+    }
+    if (ids.empty()) ids.push_back(g_device_index);
+    return ids;
+}
 // Acceleration structure the next commit builds: 0 = the reference's tree (x-only SAH, TerraBVH.c),
 // 1 = binned SAH over three axes in the same node format (default; see tb_bvh.cpp).
 // 2 = linear BVH built on the GPU (tb_lbvh.cu): the fast-build mode for large scenes.
@@ -311,6 +337,10 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     memset(s->commit_ms, 0, sizeof s->commit_ms);
     s->host_boxes_stale = false;
     s->dev = NULL;
+    s->device_ids = default_device_ids();
+    s->peers_ok = false;
+    s->fanout_min_paths = (size_t)1 << 24;
+    if (const char* e = getenv("TERRA_B200_FANOUT_MIN")) s->fanout_min_paths = (size_t)strtoull(e, NULL, 10);
     s->seed = 0;
     s->seed_fixed = false;
     s->render_calls = 0;
@@ -358,7 +388,7 @@ extern "C" void terra_scene_destroy(HTerraScene h) {                            
         terra_free(s->objects[i].properties);
     }
     terra_free(s->objects);
-    if (s->dev) tb_device_destroy(s->dev);
+    for (TbDevice* d : s->devs) tb_device_destroy(d);
     delete s;
 }
 
@@ -438,7 +468,14 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
     size_t total = 0;
     for (size_t i = 0; i < s->objects_pop; ++i) total += s->objects[i].triangles_count;
     if (total < 2) tb_fatal("terra_scene_commit needs at least 2 triangles (the reference builder reads out of range below that)");
-    if (!s->dev) s->dev = tb_device_create(g_device_index);
+    if (!s->dev) {
+        if (s->device_ids.size() == 1 && !getenv("TERRA_B200_DEVICES")) s->device_ids[0] = g_device_index;   // terra_b200_set_device after create
+        for (int id : s->device_ids) s->devs.push_back(tb_device_create(id));
+        s->dev = s->devs[0];
+        s->peers_ok = s->devs.size() > 1 && tb_device_enable_peers(s->devs.data(), (int)s->devs.size()) != 0;
+        if (s->devs.size() > 1 && !s->peers_ok)
+            terra_log("terra_b200: the scene's devices cannot map each other's memory: terra_render stays on device %d\n", s->device_ids[0]);
+    }
 
     if (s->dirty_lights) {                                                                          // Terra.c:194-231
         s->lights.clear();
@@ -525,6 +562,11 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         s->commit_ms[2] = ms_since(t0);
         t0 = Clock::now();
         tb_device_upload_geometry(s->dev, &up);
+        // replicas: device to device (NVLink) when the devices are peers, else a second upload from the host
+        for (size_t g = 1; g < s->devs.size(); ++g) {
+            if (s->peers_ok) tb_device_clone_geometry(s->devs[g], s->dev);
+            else tb_device_upload_geometry(s->devs[g], &up);
+        }
         s->commit_ms[3] = ms_since(t0);
         s->rank_of_triangle.swap(flat.rank_of_triangle);
         s->object_base.swap(flat.object_base);
@@ -558,10 +600,10 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
         up.lights_triangles_count = s->lights_triangles_count;
         up.env = env;
         Clock::time_point t0 = Clock::now();
-        tb_device_upload_tables(s->dev, &up);
+        for (TbDevice* d : s->devs) tb_device_upload_tables(d, &up);
         if (!(dirty_accelerator || retag)) s->commit_ms[3] = ms_since(t0);
     }
-    tb_device_set_options(s->dev, &s->opts, &env);
+    for (TbDevice* d : s->devs) tb_device_set_options(d, &s->opts, &env);
     s->dirty_objects = false;
     s->dirty_lights = false;
 }
@@ -613,7 +655,25 @@ extern "C" void terra_render(const TerraCamera* camera, HTerraScene h, const Ter
     if (x + width > fb->width || y + height > fb->height) tb_fatal("terra_render region outside the framebuffer");
     std::lock_guard<std::mutex> guard(s->lock);
     TbCameraFrame cam = camera_frame(camera);
-    tb_device_render(s->dev, &cam, fb, x, y, width, height, effective_spp(&s->opts), next_seed(s));
+    const size_t spp = effective_spp(&s->opts);
+    const uint64_t seed = next_seed(s);
+    const size_t n_dev = s->devs.size();
+    if (n_dev > 1 && s->peers_ok && width * height * spp >= s->fanout_min_paths && n_dev <= 16) {
+        // ---- the multi-GPU splitter behind the reference's call: the scene is replicated, device g
+        //      renders sample range g of the whole region, then finalises and returns row band g — a reduce-scatter
+        //      over NVLink fused into the accumulate / tonemap kernel, and every PCIe link carries 1/n of the
+        //      framebuffer in each direction (tb_render.cu, tb_device_partial_*). One host thread issues everything:
+        //      nothing below blocks until the waits.
+        std::vector<size_t> row0(n_dev + 1), base(n_dev + 1);
+        for (size_t g = 0; g <= n_dev; ++g) { row0[g] = height * g / n_dev; base[g] = spp * g / n_dev; }
+        for (size_t g = 0; g < n_dev; ++g)
+            tb_device_partial_begin(s->devs[g], &cam, fb, x, y, width, height, row0[g], row0[g + 1] - row0[g], base[g], base[g + 1] - base[g], seed);
+        for (size_t g = 0; g < n_dev; ++g)
+            tb_device_partial_finish(s->devs[g], s->devs.data(), (int)n_dev, fb, x, y, width, height, row0[g], row0[g + 1] - row0[g], spp);
+        for (size_t g = 0; g < n_dev; ++g) tb_device_partial_wait(s->devs[g], s->devs.data(), (int)n_dev);
+        return;
+    }
+    tb_device_render(s->dev, &cam, fb, x, y, width, height, spp, seed);
 }
 
 // =============================================================================== async tile jobs
@@ -677,9 +737,32 @@ extern "C" void terra_b200_set_seed(HTerraScene h, uint64_t seed) {
     TbScene* s = (TbScene*)h;
     s->seed = seed; s->seed_fixed = true; s->render_calls = 0;
 }
-extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) { tb_device_get_stats(committed(h, "terra_b200_get_stats")->dev, out); }
-extern "C" void terra_b200_reset_stats(HTerraScene h) { tb_device_reset_stats(committed(h, "terra_b200_reset_stats")->dev); }
-extern "C" void terra_b200_set_env_lit(HTerraScene h, int on) { tb_device_set_env_lit(committed(h, "terra_b200_set_env_lit")->dev, on); }
+extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) {      // summed over the scene's devices
+    TbScene* s = committed(h, "terra_b200_get_stats");
+    memset(out, 0, sizeof *out);
+    for (TbDevice* d : s->devs) {
+        TerraB200Stats t;
+        tb_device_get_stats(d, &t);
+        out->kernel_launches += t.kernel_launches; out->rays_traced += t.rays_traced; out->paths_traced += t.paths_traced;
+        out->trace_kernel_ms += t.trace_kernel_ms; out->trace_kernel_launches += t.trace_kernel_launches;
+        out->render_ms = t.render_ms > out->render_ms ? t.render_ms : out->render_ms;     // the devices of one call run side by side
+        out->h2d_bytes += t.h2d_bytes; out->d2h_bytes += t.d2h_bytes; out->nodes_visited += t.nodes_visited; out->tris_tested += t.tris_tested;
+        out->graph_replays += t.graph_replays; out->coherent_rays += t.coherent_rays; out->coherent_kernel_ms += t.coherent_kernel_ms;
+        out->coherent_kernel_launches += t.coherent_kernel_launches; out->coherent_nodes_visited += t.coherent_nodes_visited;
+        out->coherent_tris_tested += t.coherent_tris_tested; out->p2p_bytes += t.p2p_bytes;
+    }
+}
+extern "C" void terra_b200_reset_stats(HTerraScene h) { for (TbDevice* d : committed(h, "terra_b200_reset_stats")->devs) tb_device_reset_stats(d); }
+extern "C" void terra_b200_set_env_lit(HTerraScene h, int on) { for (TbDevice* d : committed(h, "terra_b200_set_env_lit")->devs) tb_device_set_env_lit(d, on); }
+// Devices of a scene, before its first commit (default: TERRA_B200_DEVICES, else the terra_b200_set_device one).
+extern "C" void terra_b200_scene_set_devices(HTerraScene h, const int* device_ids, int count) {
+    TbScene* s = (TbScene*)h;
+    if (s->dev) tb_fatal("terra_b200_scene_set_devices after the first terra_scene_commit");
+    if (count < 1 || count > 16) tb_fatal("terra_b200_scene_set_devices: 1 to 16 devices");
+    s->device_ids.assign(device_ids, device_ids + count);
+}
+extern "C" int terra_b200_scene_device_count(HTerraScene h) { return (int)((TbScene*)h)->device_ids.size(); }
+extern "C" void terra_b200_set_fanout_min_paths(HTerraScene h, size_t min_paths) { ((TbScene*)h)->fanout_min_paths = min_paths; }
 extern "C" void terra_b200_distribution_2d_sample(HTerraScene h, const float* f, size_t nx, size_t ny, size_t n,
                                                   const float* e1, const float* e2, float* out4) {
     TbScene* s = committed(h, "terra_b200_distribution_2d_sample");
@@ -726,8 +809,8 @@ extern "C" float terra_b200_refit(HTerraScene h) {
     s->host_boxes_stale = true;
     return ms;
 }
-extern "C" void terra_b200_set_graph_paths(HTerraScene h, size_t max_paths) { tb_device_set_graph_paths(committed(h, "terra_b200_set_graph_paths")->dev, max_paths); }
-extern "C" void terra_b200_set_counting(HTerraScene h, int on) { tb_device_set_counting(committed(h, "terra_b200_set_counting")->dev, on); }
+extern "C" void terra_b200_set_graph_paths(HTerraScene h, size_t max_paths) { for (TbDevice* d : committed(h, "terra_b200_set_graph_paths")->devs) tb_device_set_graph_paths(d, max_paths); }
+extern "C" void terra_b200_set_counting(HTerraScene h, int on) { for (TbDevice* d : committed(h, "terra_b200_set_counting")->devs) tb_device_set_counting(d, on); }
 extern "C" const void* terra_b200_bvh_nodes(HTerraScene h, int* nodes_count) {
     TbScene* s = (TbScene*)h;
     std::lock_guard<std::mutex> guard(s->lock);

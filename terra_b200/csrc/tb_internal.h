@@ -133,6 +133,13 @@ void      tb_device_render(TbDevice* dev, const TbCameraFrame* cam, const TerraF
 void      tb_device_render_resident(TbDevice* dev, const TbCameraFrame* cam, size_t fbw, size_t fbh,
                                     size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
                                     uint64_t seed, void* d_results, void* stream);
+void      tb_device_partial_begin(TbDevice* dev, const TbCameraFrame* cam, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
+                                  size_t band_row0, size_t band_rows, size_t sample_base, size_t spp, uint64_t seed);
+void      tb_device_partial_finish(TbDevice* dev, TbDevice* const* devs, int n_dev, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
+                                   size_t band_row0, size_t band_rows, size_t spp_total);
+void      tb_device_partial_wait(TbDevice* dev, TbDevice* const* devs, int n_dev);
+int       tb_device_enable_peers(TbDevice* const* devs, int n_dev);
+void      tb_device_clone_geometry(TbDevice* dst, const TbDevice* src);
 void      tb_device_resolve(TbDevice* dev, size_t fbw, size_t fbh, const void* d_results, void* d_pixels, void* stream);
 void      tb_device_trace_host(TbDevice* dev, size_t n, const float* origins, const float* dirs, TerraB200Hit* out);
 void      tb_device_trace_resident(TbDevice* dev, size_t n, const void* d_o, const void* d_d, void* d_hits, void* stream);

@@ -59,7 +59,7 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_SHADE_MIN_BLOCKS_SIMPLE 3        // ... and the simple-integrator ones (<= 85 registers)
 #endif
 #define TB_QUEUE_SENTINEL     0x7fffffff
-#define TB_V6_OPT_DEFAULT      1            // k_trace_v6 control options (tb_trace_v6.cuh): bit 0 second pop, bit 1 second parking slot
+#define TB_V6_OPT_DEFAULT      0            // k_trace_v6 control options (tb_trace_v6.cuh): bit 0 second pop, bit 1 second parking slot, bit 2 cache hints
 
 // ------------------------------------------------------------------------------------ RNG
 // Counter-based: splitmix64 over (path key, dimension). The reference draws BSDF/RR numbers from
@@ -169,6 +169,7 @@ struct TbDevice {
     std::vector<TbEventPair> ev_pool;
     size_t       ev_used;
     cudaEvent_t  ev_call_a, ev_call_b, ev_legacy;
+    cudaEvent_t  ev_partial, ev_band;      // multi-device terra_render: this device's accumulator is complete / its band is finalised
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
@@ -303,6 +304,8 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
     TB_CUDA(cudaEventCreate(&d->ev_call_b));
     TB_CUDA(cudaEventCreateWithFlags(&d->ev_legacy, cudaEventDisableTiming));
+    TB_CUDA(cudaEventCreateWithFlags(&d->ev_partial, cudaEventDisableTiming));
+    TB_CUDA(cudaEventCreateWithFlags(&d->ev_band, cudaEventDisableTiming));
     return d;
 }
 
@@ -340,6 +343,8 @@ extern "C" void tb_device_destroy(TbDevice* d) {
     cudaEventDestroy(d->ev_call_a);
     cudaEventDestroy(d->ev_call_b);
     cudaEventDestroy(d->ev_legacy);
+    cudaEventDestroy(d->ev_partial);
+    cudaEventDestroy(d->ev_band);
     cudaStreamDestroy(d->stream);
     delete d;
 }
@@ -1254,6 +1259,40 @@ __global__ void __launch_bounds__(256) k_finalize(TbFinalizeArgs a) {
         }
     }
 }
+// Multi-device terra_render: every GPU rendered its own sample range of the WHOLE region into its own accumulator;
+// GPU g then finalises ITS row band — it sums the band's pixels over all accumulators (its own and, through
+// peer-mapped pointers, the others': loads over NVLink), in device order so the result does not depend on which GPU
+// finishes first, adds the caller's running results[] and tonemaps. Reduce-scatter and Terra.c:569-630 in one
+// kernel: no intermediate buffer, no second pass, and each GPU then copies its band back over its own PCIe link.
+#define TB_MAX_DEVICES 16
+struct TbPeerFinalizeArgs {
+    const float4* acc[TB_MAX_DEVICES];   // region-linear accumulators, one per device
+    int n_dev;
+    int p0, n_px;                        // the band: region-linear pixel range [p0, p0 + n_px)
+    TerraRawIntegrationResult* results;  // band-linear staging of the caller's results[] (read-modify-write)
+    float* pixels;                       // band-linear staging of pixels[]
+    int spp, tonemap;
+    float exposure, inv_gamma;
+};
+__global__ void __launch_bounds__(256) k_finalize_peers(TbPeerFinalizeArgs a) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n_px; i += gridDim.x * blockDim.x) {
+        const int p = a.p0 + i;
+        float4 s = a.acc[0][p];
+        for (int g = 1; g < a.n_dev; ++g) {
+            const float4 o = a.acc[g][p];
+            s.x = s.x + o.x; s.y = s.y + o.y; s.z = s.z + o.z;
+        }
+        TerraRawIntegrationResult* r = a.results + i;
+        const V3 acc = v3(s.x + r->acc.x, s.y + r->acc.y, s.z + r->acc.z);
+        const int samples = r->samples + a.spp;
+        r->acc.x = acc.x; r->acc.y = acc.y; r->acc.z = acc.z;
+        r->samples = samples;
+        V3 color = vmul(vdiv(acc, (float)samples), a.exposure);
+        color = tb_tonemap(color, a.tonemap, a.inv_gamma);
+        float* px = a.pixels + (size_t)i * 3;
+        px[0] = color.x; px[1] = color.y; px[2] = color.z;
+    }
+}
 __global__ void __launch_bounds__(256) k_resolve(const TerraRawIntegrationResult* results, float* pixels, size_t n,
                                                  int tonemap, float exposure, float inv_gamma) {
     for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (size_t)gridDim.x * blockDim.x) {
@@ -1384,13 +1423,13 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         if (rows > TB_V6_MAX_SMEM_DEPTH) rows = TB_V6_SPILL_SMEM_DEPTH;
         c.stack_smem = rows;
         const size_t smem = (size_t)(rows + 2) * TB_TRACE_THREADS * 8;
-#define TB_V6_LAUNCH(CNT, EX, SP, OP) k_trace_v6<CNT, EX, SP, OP><<<grid, TB_TRACE_THREADS, smem, st>>>(c)
+#define TB_V6_LAUNCH(CNT, EX, SP, OP) k_trace_v6<CNT, EX, SP, OP><<<d->sm_count * TB_V6_CTAS_PER_SM, TB_TRACE_THREADS, smem, st>>>(c)
         if (COUNT || exact) {           // counting and the reference tree run the default control options
             if (exact) { if (spill) TB_V6_LAUNCH(COUNT, true, true, TB_V6_OPT_DEFAULT); else TB_V6_LAUNCH(COUNT, true, false, TB_V6_OPT_DEFAULT); }
             else       { if (spill) TB_V6_LAUNCH(COUNT, false, true, TB_V6_OPT_DEFAULT); else TB_V6_LAUNCH(COUNT, false, false, TB_V6_OPT_DEFAULT); }
             return;
         }
-        switch ((d->v6_opt & 3) * 2 + (spill ? 1 : 0)) {
+        switch ((d->v6_opt & 7) * 2 + (spill ? 1 : 0)) {
             case 0: TB_V6_LAUNCH(false, false, false, 0); break;
             case 1: TB_V6_LAUNCH(false, false, true, 0); break;
             case 2: TB_V6_LAUNCH(false, false, false, 1); break;
@@ -1398,7 +1437,12 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
             case 4: TB_V6_LAUNCH(false, false, false, 2); break;
             case 5: TB_V6_LAUNCH(false, false, true, 2); break;
             case 6: TB_V6_LAUNCH(false, false, false, 3); break;
-            default: TB_V6_LAUNCH(false, false, true, 3); break;
+            case 7: TB_V6_LAUNCH(false, false, true, 3); break;
+            case 8: TB_V6_LAUNCH(false, false, false, 4); break;
+            case 9: TB_V6_LAUNCH(false, false, true, 4); break;
+            case 10: TB_V6_LAUNCH(false, false, false, 5); break;
+            case 11: TB_V6_LAUNCH(false, false, true, 5); break;
+            default: TB_V6_LAUNCH(false, false, false, 0); break;
         }
 #undef TB_V6_LAUNCH
         return;
@@ -1755,6 +1799,126 @@ extern "C" void tb_device_render_resident(TbDevice* d, const TbCameraFrame* cam,
         body();
     }
     tb_finish_call(d, st, true);
+}
+
+// ---- multi-device terra_render (tb_host.cpp fans a large call out over the scene's devices) -----------------
+// 1. tb_device_partial_begin on every device: upload the device's row band of the caller's results[], render the
+//    device's sample range of the whole region into its accumulator, record an event. Nothing blocks.
+// 2. tb_device_partial_finish on every device: wait for ALL devices' events, finalise the band from all
+//    accumulators (k_finalize_peers), copy the band back to the caller's framebuffer. Nothing blocks.
+// 3. tb_device_partial_wait on every device.
+extern "C" void tb_device_partial_begin(TbDevice* d, const TbCameraFrame* cam, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
+                                        size_t band_row0, size_t band_rows, size_t sample_base, size_t spp, uint64_t seed) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    const size_t npx = w * h, band_px = band_rows * w;
+    if (band_px > d->fb_capacity) {
+        d->graph_epoch++;
+        tb_free(d->d_results); tb_free(d->d_pixels);
+        d->d_results = tb_alloc<TerraRawIntegrationResult>(band_px);
+        d->d_pixels = tb_alloc<float>(band_px * 3);
+        d->fb_capacity = band_px;
+    }
+    tb_acc_reserve(d, npx);
+    TB_CUDA(cudaEventRecord(d->ev_call_a, st));
+    if (band_rows) {
+        TB_CUDA(cudaMemcpy2DAsync(d->d_results, w * sizeof(TerraRawIntegrationResult),
+                                  fb->results + (y + band_row0) * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
+                                  w * sizeof(TerraRawIntegrationResult), band_rows, cudaMemcpyHostToDevice, st));
+        d->stats.h2d_bytes += band_px * sizeof(TerraRawIntegrationResult);
+    }
+    TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
+    tb_set_call(d, st, cam, fb->width, fb->height, x, y, sample_base, seed, NULL);
+    if (spp) tb_render_region(d, st, w, h, spp, d->d_acc);
+    TB_CUDA(cudaEventRecord(d->ev_partial, st));
+}
+
+extern "C" void tb_device_partial_finish(TbDevice* d, TbDevice* const* devs, int n_dev, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
+                                         size_t band_row0, size_t band_rows, size_t spp_total) {
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = d->stream;
+    for (int g = 0; g < n_dev; ++g)
+        if (devs[g] != d) TB_CUDA(cudaStreamWaitEvent(st, devs[g]->ev_partial, 0));
+    if (band_rows) {
+        TbPeerFinalizeArgs fa;
+        memset(&fa, 0, sizeof fa);
+        for (int g = 0; g < n_dev; ++g) fa.acc[g] = devs[g]->d_acc;
+        fa.n_dev = n_dev;
+        fa.p0 = (int)(band_row0 * w); fa.n_px = (int)(band_rows * w);
+        fa.results = d->d_results; fa.pixels = d->d_pixels;
+        fa.spp = (int)spp_total; fa.tonemap = d->sc.tonemap; fa.exposure = d->sc.exposure; fa.inv_gamma = d->sc.inv_gamma;
+        k_finalize_peers<<<d->sm_count * 4, 256, 0, st>>>(fa);
+        d->stats.kernel_launches += 1;
+        TB_CUDA(cudaMemcpy2DAsync(fb->results + (y + band_row0) * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
+                                  d->d_results, w * sizeof(TerraRawIntegrationResult),
+                                  w * sizeof(TerraRawIntegrationResult), band_rows, cudaMemcpyDeviceToHost, st));
+        TB_CUDA(cudaMemcpy2DAsync(fb->pixels + (y + band_row0) * fb->width + x, fb->width * sizeof(TerraFloat3),
+                                  d->d_pixels, w * sizeof(TerraFloat3), w * sizeof(TerraFloat3), band_rows, cudaMemcpyDeviceToHost, st));
+        d->stats.d2h_bytes += band_rows * w * (sizeof(TerraRawIntegrationResult) + sizeof(TerraFloat3));
+    }
+    // the other devices read this device's accumulator: the next call must not reset it before they are done
+    TB_CUDA(cudaEventRecord(d->ev_band, st));
+}
+
+extern "C" void tb_device_partial_wait(TbDevice* d, TbDevice* const* devs, int n_dev) {
+    TB_CUDA(cudaSetDevice(d->index));
+    tb_finish_call(d, d->stream, true);
+    for (int g = 0; g < n_dev; ++g) if (devs[g] != d) TB_CUDA(cudaEventSynchronize(devs[g]->ev_band));
+}
+
+// Peer access between every pair of the scene's devices (NVLink / NVSwitch on an HGX box). Returns 0 when some pair
+// cannot map the other's memory: the caller then keeps to one device.
+extern "C" int tb_device_enable_peers(TbDevice* const* devs, int n_dev) {
+    for (int a = 0; a < n_dev; ++a)
+        for (int b = 0; b < n_dev; ++b) {
+            if (a == b) continue;
+            int can = 0;
+            TB_CUDA(cudaDeviceCanAccessPeer(&can, devs[a]->index, devs[b]->index));
+            if (!can) return 0;
+        }
+    for (int a = 0; a < n_dev; ++a) {
+        TB_CUDA(cudaSetDevice(devs[a]->index));
+        for (int b = 0; b < n_dev; ++b) {
+            if (a == b) continue;
+            cudaError_t e = cudaDeviceEnablePeerAccess(devs[b]->index, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) TB_CUDA(e);
+            cudaGetLastError();
+        }
+    }
+    return 1;
+}
+
+// Replica of `src`'s geometry on `dst`, copied device to device (NVLink) instead of a second trip over PCIe:
+// a 10M-triangle scene is 1.8 GB per GPU. Tables (materials, lights, textures) are small and hold device pointers:
+// they go up from the host per device (tb_device_upload_tables).
+extern "C" void tb_device_clone_geometry(TbDevice* dst, const TbDevice* src) {
+    TB_CUDA(cudaSetDevice(src->index));
+    TB_CUDA(cudaStreamSynchronize(src->stream));
+    TB_CUDA(cudaSetDevice(dst->index));
+    TB_CUDA(cudaStreamSynchronize(dst->stream));
+    dst->graph_epoch++;
+    tb_free(dst->d_nodes); tb_free(dst->d_tris); tb_free(dst->d_props); tb_free(dst->d_qnodes);
+    dst->d_qnodes = NULL;
+    const size_t n_nodes = (size_t)src->sc.n_nodes, n_tris = (size_t)src->sc.n_tris;
+    dst->d_nodes = tb_alloc<float4>(n_nodes * 4);
+    dst->d_tris = tb_alloc<float4>(n_tris * 3);
+    dst->d_props = tb_alloc<float4>(n_tris * 4);
+    TB_CUDA(cudaMemcpyPeerAsync(dst->d_nodes, dst->index, src->d_nodes, src->index, n_nodes * 64, dst->stream));
+    TB_CUDA(cudaMemcpyPeerAsync(dst->d_tris, dst->index, src->d_tris, src->index, n_tris * 48, dst->stream));
+    TB_CUDA(cudaMemcpyPeerAsync(dst->d_props, dst->index, src->d_props, src->index, n_tris * 64, dst->stream));
+    if (src->d_qnodes) {
+        dst->d_qnodes = tb_alloc<uint4>(n_nodes * 2);
+        TB_CUDA(cudaMemcpyPeerAsync(dst->d_qnodes, dst->index, src->d_qnodes, src->index, n_nodes * 32, dst->stream));
+        memcpy(dst->grid_lo, src->grid_lo, sizeof dst->grid_lo);
+        memcpy(dst->grid_cell, src->grid_cell, sizeof dst->grid_cell);
+    }
+    TB_CUDA(cudaStreamSynchronize(dst->stream));
+    dst->stats.p2p_bytes += n_nodes * (64 + (src->d_qnodes ? 32 : 0)) + n_tris * 112;
+    dst->stack_bound = src->stack_bound;
+    dst->exact_boxes = src->exact_boxes;
+    TbDevScene& sc = dst->sc;
+    sc.nodes = dst->d_nodes; sc.tris = dst->d_tris; sc.props = dst->d_props;
+    sc.n_nodes = src->sc.n_nodes; sc.n_tris = src->sc.n_tris;
 }
 
 extern "C" void tb_device_resolve(TbDevice* d, size_t fbw, size_t fbh, const void* d_results, void* d_pixels, void* stream) {

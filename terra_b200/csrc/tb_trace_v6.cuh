@@ -36,7 +36,7 @@
 //   - finished rays are retired only when the warp has one.
 #pragma once
 
-#define TB_V6_MAX_SMEM_DEPTH   25          /* (25 + 2) rows x 1 KB x 8 CTAs = 216 KB of the SM's 228 KB */
+#define TB_V6_MAX_SMEM_DEPTH   28          /* (28 + 2) rows x 1 KB x 7 CTAs = 210 KB of the SM's 228 KB */
 #define TB_V6_SPILL_SMEM_DEPTH 16
 #define TB_V6_LOCAL            (TB_STACK_SMEM + TB_STACK_LOCAL)
 
@@ -100,8 +100,35 @@ __device__ __forceinline__ void tb_sts64(unsigned addr, int2 v) {
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" :: "r"(addr), "r"(v.x), "r"(v.y) : "memory");
 }
 
+// OPT bit 2: cache policy per stream — nodes are re-used (by this ray's siblings in the warp and by the next rays),
+// triangles, rays and hit records are touched once: triangle and ray loads do not allocate in L1, node loads ask to
+// be evicted last. The kernel is bound by the latency of node fetches that miss L1 (r2a A/B: shrinking L1 from 92 KB
+// to 28 KB per SM cost 23 %), so what sits in L1 should be nodes.
+template <int OPT>
+__device__ __forceinline__ void tb_ld_qnode(const uint4* np, uint4& qa, uint4& qb) {
+    if (OPT & 4)
+        asm volatile("ld.global.nc.L1::evict_last.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
+    else
+        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
+}
+template <int OPT>
+__device__ __forceinline__ float4 tb_ld_once(const float4* p) {
+    if (OPT & 4) {
+        float4 v;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+        return v;
+    }
+    return __ldg(p);
+}
+
+#ifndef TB_V6_CTAS_PER_SM
+#define TB_V6_CTAS_PER_SM 7     /* 72 registers: no spills; measured +9 % over 8 CTAs x 64 registers on C3 1M (profiles/r2a) */
+#endif
+
 template <bool COUNT, bool EXACT, bool SPILL, int OPT>
-__global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trace_v6(TbTraceArgs a) {
+__global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v6(TbTraceArgs a) {
     extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 2][TB_TRACE_THREADS] x 8 B
     constexpr int ROW = TB_TRACE_THREADS * 8;
     int2 l_stack[SPILL ? TB_V6_LOCAL : 1];
@@ -144,7 +171,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
                 const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
                 if (q < total) {
                     slot = a.queue ? a.queue[q] : q;
-                    const float4 o4 = a.ray_o[slot], d4 = a.ray_d[slot];
+                    const float4 o4 = tb_ld_once<OPT>(a.ray_o + slot), d4 = tb_ld_once<OPT>(a.ray_d + slot);
                     const V3 d = v3(d4.x, d4.y, d4.z);
                     r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
                     kpack = (kpack & 0x100) | r.kx | (r.ky << 2) | (r.kz << 4);
@@ -199,16 +226,14 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_TRACE_CTAS_PER_SM) k_trac
             uint4 qa, qb;
             if (is_node) {
                 if (!EXACT) {
-                    const uint4* np = a.qnodes + (size_t)cur * 2;
-                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                 : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
+                    tb_ld_qnode<OPT>(a.qnodes + (size_t)cur * 2, qa, qb);
                 } else {
                     tb_load_node256(a.nodes + (size_t)cur * 4, q0, q1, q2, q3);
                 }
             }
             if (do_tri) {
                 const float4* tp = a.tris + (size_t)(~pend) * 3;
-                ta = __ldg(tp); tb = __ldg(tp + 1); tc = __ldg(tp + 2);
+                ta = tb_ld_once<OPT>(tp); tb = tb_ld_once<OPT>(tp + 1); tc = tb_ld_once<OPT>(tp + 2);
             }
             // 5. node step
             if (is_node) {

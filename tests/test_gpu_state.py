@@ -41,7 +41,7 @@ def test_render_entry_points_share_one_accumulator(api, scenes, gpu):
     # and a scene that is still usable afterwards (a corrupted wave / scene buffer would show here)
     s2, cam2 = scenes.cornell(gpu, spp=spp)
     hits = s2.primary_hits(cam2, 64, 64)
-    assert (hits["t"] > 0).mean() > 0.9
+    assert (hits["t"] > 0).mean() > 0.7
     s2.destroy()
 
 
