@@ -438,15 +438,40 @@ def run_render_arm(args):
         ms_e2e, _ = timed(lambda: lib.terra_render(C.byref(cam), s.h, C.byref(fb), 0, 0, w, h), e2e_steps, max(1, min(3, args.warmup)))
         h2d, d2h = w * h * 16 + 40, w * h * 28
     else:
-        def e2e_step():
-            if rank == 0:
-                r.results.copy_(r.host_results, non_blocking=True)    # the running accumulators go up (then are reset: one frame)
-            r.render(spp)
-            if rank == 0:
-                r.to_host()
-        ms_e2e, _ = timed(e2e_step, max(1, args.steps // 2), max(1, min(3, args.warmup)))
+        # N > 1: the reference-facing call at N GPUs is terra_render on a scene that lives on all N devices (the
+        # in-library splitter: sample ranges per GPU, peer-memory reduce-scatter fused into the finalize kernel, every
+        # GPU returns its own row band over its own PCIe link). One process drives it — rank 0 — while the other ranks
+        # wait at a CPU (gloo) barrier with their GPUs idle; the timed region is the call on a host framebuffer.
+        cpu_group = dist.new_group(backend="gloo")
+        ms_e2e = 0.0
+        if rank == 0:
+            orig_commit = api.Scene.commit
+            api.Scene.commit = lambda self: None
+            try:
+                s_all, cam_all = build_scene(lib, scenes, args.workload, spp, args.integrator)
+            finally:
+                api.Scene.commit = orig_commit
+            ids = (C.c_int * world)(*range(world))
+            lib.terra_b200_scene_set_devices(s_all.h, ids, world)
+            s_all.commit()
+            lib.terra_b200_set_seed(s_all.h, 2024)
+            fb = api.Framebuffer()
+            assert lib.terra_framebuffer_create(C.byref(fb), w, h)
+            for _ in range(max(1, min(3, args.warmup))):
+                lib.terra_render(C.byref(cam_all), s_all.h, C.byref(fb), 0, 0, w, h)
+            n_e2e = max(1, args.steps // 2)
+            tot = 0.0
+            for _ in range(n_e2e):
+                flush.zero_(); torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                lib.terra_render(C.byref(cam_all), s_all.h, C.byref(fb), 0, 0, w, h)      # blocking: returns with the framebuffer final
+                tot += (time.perf_counter() - t0) * 1e3
+            ms_e2e = tot / n_e2e
+            st_all = s_all.stats()
+            e2e_note = {"devices": world, "p2p_bytes_at_commit": int(st_all.p2p_bytes), "render_ms_device_clock": st_all.render_ms / (n_e2e + max(1, min(3, args.warmup)))}
+            s_all.destroy()
+        dist.barrier(group=cpu_group)
         h2d, d2h = w * h * 16 + 40, w * h * 28
-
     # ---- small workloads are replayed from a CUDA graph, which takes no per-kernel timings: the roofline's
     #      trace-kernel times come from one extra, untimed pass launched kernel by kernel
     if st.trace_kernel_launches == 0:
@@ -491,7 +516,9 @@ def run_render_arm(args):
         "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": line_config(args, wl, world),
-        "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+        "e2e": dict({"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+                    **({"path": "terra_render on one scene replicated on all GPUs (single process, peer-memory reduce-scatter)", **e2e_note}
+                       if world > 1 else {"path": "terra_render"})),
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": dict(dominant, kernels=kernels, l2_probe={"stream_gbs": l2_stream, "gather_gbs": l2_gather},

@@ -20,27 +20,17 @@ REPO = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(REPO))
 
 C3_VARIANTS = [
-    ("v4 (round 1)", dict(TERRA_B200_INCOHERENT="v4")),
-    ("v6 opt0", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0")),
-    ("v6 opt1 (double pop)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="1")),
-    ("v6 opt4 (cache hints)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4")),
-    ("v6 opt5 (double pop + cache hints)", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="5")),
-    ("v6 opt0 preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_NODE_ORDER="preorder")),
-    ("v6 opt4 preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder")),
-    ("v6 opt5 preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="5", TERRA_B200_NODE_ORDER="preorder")),
-    ("v4 preorder", dict(TERRA_B200_INCOHERENT="v4", TERRA_B200_NODE_ORDER="preorder")),
-    ("v6 opt4 preorder stack 16 + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_STACK_SMEM="16")),
-    ("v6 opt4 preorder stack 20 + spill", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_STACK_SMEM="20")),
-    ("v6 opt4 preorder refetch 22", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_REFETCH="22")),
-    ("v6 opt4 preorder tri_min 6", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_NODE_ORDER="preorder", TERRA_B200_TRI_MIN="6")),
+    ("v6 (default)", dict()),
+    ("v6 refetch 26", dict(TERRA_B200_REFETCH="26")),
+    ("v6 refetch 18", dict(TERRA_B200_REFETCH="18")),
+    ("v6 stack 16 rows + spill", dict(TERRA_B200_STACK_SMEM="16")),
+    ("v6 tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
+    ("v6 tri_min 10", dict(TERRA_B200_TRI_MIN="10")),
 ]
 C2_VARIANTS = [
-    ("round-1 kernels (v4, k_raygen)", dict(TERRA_B200_INCOHERENT="v4", TERRA_B200_FUSED_RAYGEN="0")),
-    ("v6 opt0 + fused raygen", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_FUSED_RAYGEN="1")),
-    ("v6 opt4 + fused raygen", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_FUSED_RAYGEN="1")),
-    ("v6 opt0 + fused raygen, preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="0", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_NODE_ORDER="preorder")),
-    ("v6 opt4 + fused raygen, preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="4", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_NODE_ORDER="preorder")),
-    ("v6 opt5 + fused raygen, preorder", dict(TERRA_B200_INCOHERENT="v6", TERRA_B200_V6_OPT="5", TERRA_B200_FUSED_RAYGEN="1", TERRA_B200_NODE_ORDER="preorder")),
+    ("default (v6 + fused raygen)", dict()),
+    ("k_raygen instead of fused generation", dict(TERRA_B200_FUSED_RAYGEN="0")),
+    ("refetch 26", dict(TERRA_B200_REFETCH="26")),
 ]
 SWITCHES = ["TERRA_B200_INCOHERENT", "TERRA_B200_COHERENT", "TERRA_B200_V6_OPT", "TERRA_B200_STACK_SMEM", "TERRA_B200_TRI_MIN",
             "TERRA_B200_REFETCH", "TERRA_B200_FUSED_RAYGEN", "TERRA_B200_NODE_ORDER"]

@@ -211,7 +211,7 @@ void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbH
 // Pruned traversals visit a subsequence of this order, hence "first found on an exact t tie"
 // == "smallest rank".
 void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* objects, int objects_count,
-                    TbFlatBvh* out) {
+                    TbFlatBvh* out, const std::vector<int32_t>* rank_override) {
     size_t total = 0;
     std::vector<size_t> object_base((size_t)objects_count + 1, 0);
     for (int j = 0; j < objects_count; ++j) { object_base[j] = total; total += objects[j].triangles_count; }
@@ -236,6 +236,7 @@ void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* obj
             else leaf_rank[(size_t)e.first * 2 + c] = (int32_t)next_rank++;
         }
     }
+    if (rank_override) leaf_rank = *rank_override;
     out->stack_bound = max_depth;
     // pass 2: write nodes and rank-ordered triangle/property records
     parallel_chunks(0, (int)nodes.size(), host_threads(), [&](int lo_, int hi_, int) {

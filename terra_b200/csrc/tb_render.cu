@@ -49,7 +49,7 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_STACK_SMEM         16           // traversal stack entries held in shared memory ...
 #define TB_STACK_LOCAL        112          // ... deeper entries spill to local memory
 #define TB_TRI_MIN            8            // rounds kernel: parked leaves needed before a triangle round
-#define TB_REFETCH_ROUNDS     26           // rounds kernel: refill the warp when fewer lanes own a ray (swept on B200: 16/20/26/30)
+#define TB_REFETCH_ROUNDS     22           // rounds kernel: refill the warp when fewer lanes own a ray (swept on B200 with k_trace_v6: 18/22/26/29)
 #define TB_REFETCH_BELOW      20           // dynamic fetch: refill the warp when fewer lanes are busy
 #define TB_SHADE_THREADS      256
 #ifndef TB_SHADE_MIN_BLOCKS
@@ -59,7 +59,8 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_SHADE_MIN_BLOCKS_SIMPLE 3        // ... and the simple-integrator ones (<= 85 registers)
 #endif
 #define TB_QUEUE_SENTINEL     0x7fffffff
-#define TB_V6_OPT_DEFAULT      0            // k_trace_v6 control options (tb_trace_v6.cuh): bit 0 second pop, bit 1 second parking slot, bit 2 cache hints
+#define TB_K_V6_ID            2            // = TB_K_V6 / TB_K_PACKET below (the device is created before the enum is seen)
+#define TB_K_PACKET_ID        3
 
 // ------------------------------------------------------------------------------------ RNG
 // Counter-based: splitmix64 over (path key, dimension). The reference draws BSDF/RR numbers from
@@ -173,7 +174,6 @@ struct TbDevice {
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
-    int          v6_opt;            // k_trace_v6 OPT bits (tb_trace_v6.cuh)
     int          fused_raygen;      // 1: camera rays are generated inside the packet kernel (no k_raygen, no ray arrays for bounce 0)
     int          coherent_kind;     // TB_K_* used for camera-ray launches when trace_kind is auto
     int          incoherent_kind;   // TB_K_* used for incoherent launches when trace_kind is auto
@@ -280,25 +280,23 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->counting = 0;
     d->exact_boxes = 0;
     {
-        // A/B switches (profiles/ records what each one measured): TERRA_B200_TRACE forces one kernel for every
-        // launch; TERRA_B200_INCOHERENT / TERRA_B200_COHERENT choose it for bounce / visibility / API rays and for
-        // camera rays. walk = per-ray while-while (the work counters' kernel), v4 = rounds kernel of round 1,
-        // v6 = rounds kernel with sign-selected planes (tb_trace_v6.cuh), packet = one warp per 32-ray packet.
-        static const char* names[] = { "auto", "walk", "v4", "v6", "packet" };
+        // A/B switches: TERRA_B200_TRACE forces one kernel for every launch; TERRA_B200_INCOHERENT / TERRA_B200_COHERENT
+        // choose it for bounce / visibility / API rays and for camera rays. walk = per-ray while-while (the work
+        // counters' kernel), v6 = rounds kernel (tb_trace_v6.cuh), packet = one warp per 32-ray packet.
+        static const char* names[] = { "auto", "walk", "v6", "packet" };
         auto kind_of = [&](const char* env, int dflt) {
             const char* e = getenv(env);
-            for (int k = 0; e && k < 5; ++k) if (strcmp(e, names[k]) == 0) return k;
+            for (int k = 0; e && k < 4; ++k) if (strcmp(e, names[k]) == 0) return k;
             return dflt;
         };
         d->trace_kind = kind_of("TERRA_B200_TRACE", 0);
-        d->incoherent_kind = kind_of("TERRA_B200_INCOHERENT", 3);
-        d->coherent_kind = kind_of("TERRA_B200_COHERENT", 4);
+        d->incoherent_kind = kind_of("TERRA_B200_INCOHERENT", TB_K_V6_ID);
+        d->coherent_kind = kind_of("TERRA_B200_COHERENT", TB_K_PACKET_ID);
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
         const char* ws = getenv("TERRA_B200_WARP_SAMPLES"); d->warp_samples = ws ? atoi(ws) : 32;
         const char* gp = getenv("TERRA_B200_GRAPH_PATHS"); d->graph_max_paths = gp ? (size_t)strtoull(gp, NULL, 10) : ((size_t)1 << 22);
         const char* f = getenv("TERRA_B200_REFETCH"); d->refetch_below = f ? atoi(f) : TB_REFETCH_ROUNDS;
-        const char* vo = getenv("TERRA_B200_V6_OPT"); d->v6_opt = vo ? atoi(vo) : TB_V6_OPT_DEFAULT;
         const char* fr = getenv("TERRA_B200_FUSED_RAYGEN"); d->fused_raygen = fr ? atoi(fr) : 1;
     }
     TB_CUDA(cudaEventCreate(&d->ev_call_a));
@@ -699,7 +697,6 @@ __device__ __forceinline__ V3 tb_gen_ray(const TbGenArgs& g, int slot, uint64_t*
 }
 
 #include "tb_trace.cuh"
-#include "tb_trace_v4.cuh"
 #include "tb_trace_v6.cuh"
 #include "tb_trace_packet.cuh"
 
@@ -1383,10 +1380,11 @@ static void tb_drain_events(TbDevice* d) {
 
 // Which closest-hit kernel a launch uses (measured on B200, profiles/): camera rays are coherent — one warp walks
 // the tree once for its 32 rays (k_trace_packet); bounce / visibility / API rays are incoherent — per-lane rays in
-// warp-synchronous rounds over 32-byte quantised nodes (k_trace_v6; k_trace_v4 = round 1's version, kept while
-// the two are measured side by side). The work counters of SURVEY §8(d) mean the per-ray walk: a counting
-// camera launch runs k_trace<COUNT> (a packet would count the union over its 32 rays).
-enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V4, TB_K_V6, TB_K_PACKET };
+// warp-synchronous rounds over 32-byte quantised nodes (k_trace_v6). The work counters of SURVEY §8(d) mean the
+// per-ray walk: a counting camera launch runs k_trace<COUNT> (a packet would count the union over its 32 rays).
+// Earlier structures and the options that lost their A/B live in experiments/ (not built).
+enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V6, TB_K_PACKET };
+static_assert(TB_K_V6 == TB_K_V6_ID && TB_K_PACKET == TB_K_PACKET_ID, "kernel ids used by tb_device_create");
 
 template <bool COUNT>
 static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind, const TbGenArgs* gen) {
@@ -1415,46 +1413,21 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         else       k_trace<COUNT, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
         return;
     }
-    if (kind == TB_K_V6) {
-        const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
-        int rows = d->stack_bound > 1 ? d->stack_bound : 1;
-        if (forced > 0 && forced < rows) rows = forced;
-        const bool spill = rows > TB_V6_MAX_SMEM_DEPTH || rows < d->stack_bound;
-        if (rows > TB_V6_MAX_SMEM_DEPTH) rows = TB_V6_SPILL_SMEM_DEPTH;
-        c.stack_smem = rows;
-        const size_t smem = (size_t)(rows + 2) * TB_TRACE_THREADS * 8;
-#define TB_V6_LAUNCH(CNT, EX, SP, OP) k_trace_v6<CNT, EX, SP, OP><<<d->sm_count * TB_V6_CTAS_PER_SM, TB_TRACE_THREADS, smem, st>>>(c)
-        if (COUNT || exact) {           // counting and the reference tree run the default control options
-            if (exact) { if (spill) TB_V6_LAUNCH(COUNT, true, true, TB_V6_OPT_DEFAULT); else TB_V6_LAUNCH(COUNT, true, false, TB_V6_OPT_DEFAULT); }
-            else       { if (spill) TB_V6_LAUNCH(COUNT, false, true, TB_V6_OPT_DEFAULT); else TB_V6_LAUNCH(COUNT, false, false, TB_V6_OPT_DEFAULT); }
-            return;
-        }
-        switch ((d->v6_opt & 7) * 2 + (spill ? 1 : 0)) {
-            case 0: TB_V6_LAUNCH(false, false, false, 0); break;
-            case 1: TB_V6_LAUNCH(false, false, true, 0); break;
-            case 2: TB_V6_LAUNCH(false, false, false, 1); break;
-            case 3: TB_V6_LAUNCH(false, false, true, 1); break;
-            case 4: TB_V6_LAUNCH(false, false, false, 2); break;
-            case 5: TB_V6_LAUNCH(false, false, true, 2); break;
-            case 6: TB_V6_LAUNCH(false, false, false, 3); break;
-            case 7: TB_V6_LAUNCH(false, false, true, 3); break;
-            case 8: TB_V6_LAUNCH(false, false, false, 4); break;
-            case 9: TB_V6_LAUNCH(false, false, true, 4); break;
-            case 10: TB_V6_LAUNCH(false, false, false, 5); break;
-            case 11: TB_V6_LAUNCH(false, false, true, 5); break;
-            default: TB_V6_LAUNCH(false, false, false, 0); break;
-        }
-#undef TB_V6_LAUNCH
-        return;
-    }
-    // TB_K_V4
-    const bool spill = d->stack_bound > TB_V4_DEPTH;
+    // TB_K_V6: the rounds kernel
+    const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
+    int rows = d->stack_bound > 1 ? d->stack_bound : 1;
+    if (forced > 0 && forced < rows) rows = forced;
+    const bool spill = rows > TB_V6_MAX_SMEM_DEPTH || rows < d->stack_bound;
+    if (rows > TB_V6_MAX_SMEM_DEPTH) rows = TB_V6_SPILL_SMEM_DEPTH;
+    c.stack_smem = rows;
+    const size_t smem = (size_t)(rows + 3) * TB_TRACE_THREADS * 8;
+    const int grid6 = d->sm_count * TB_V6_CTAS_PER_SM;
     if (exact) {
-        if (spill) k_trace_v4<COUNT, true, false, true, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else       k_trace_v4<COUNT, true, false, false, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        if (spill) k_trace_v6<COUNT, true, true><<<grid6, TB_TRACE_THREADS, smem, st>>>(c);
+        else       k_trace_v6<COUNT, true, false><<<grid6, TB_TRACE_THREADS, smem, st>>>(c);
     } else {
-        if (spill) k_trace_v4<COUNT, false, true, true, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
-        else       k_trace_v4<COUNT, false, true, false, 3><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        if (spill) k_trace_v6<COUNT, false, true><<<grid6, TB_TRACE_THREADS, smem, st>>>(c);
+        else       k_trace_v6<COUNT, false, false><<<grid6, TB_TRACE_THREADS, smem, st>>>(c);
     }
 }
 

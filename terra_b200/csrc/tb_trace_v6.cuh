@@ -9,9 +9,13 @@
 // watertight triangle test runs for all parked leaves at once when enough lanes hold one, idle lanes are refilled
 // by ballot, the stack is one 64-bit {ref, tmin} word per entry in shared memory, [depth][thread].
 //
-// What round 2 changed, and why (ncu r1r, k_trace_v4 on C2 bounce rays: sm__pipe_alu_cycles_active 70 % against
-// sm__pipe_fma 19 % and issue-active 69.5 % — the kernel is bound by the half-rate ALU pipe, i.e. by PRMT / FMNMX /
-// ISETP / SEL, not by FMAs, loads or total issue slots; per round 69 ALU-pipe instructions of 146):
+// What round 2 changed, and why. ncu r1r (k_trace_v4 on C2 bounce rays) showed sm__pipe_alu_cycles_active 70 % against
+// sm__pipe_fma 19 % and issue-active 69.5 %: the busiest unit was the half-rate ALU pipe (PRMT / FMNMX / ISETP / SEL),
+// 69 of the 146 instructions of a round. Cutting those (first three items) took 20 % of the instructions out
+// (185 -> 148 warp instructions per ray on C3 1M, ncu r2d) but only 2 % of the time at equal occupancy and stack
+// settings: with the instruction count down, the kernel waits on the node fetch instead (35 % of all stall samples
+// sit on the first use of the node load, issue-active 60 %). The rest of the gain came from registers, L1 and L2
+// (last items). Measured end to end: 4.29 -> 4.94 Grays/s on C3 1M, profiles/r2_summary.md.
 //   - SIGN-SELECTED PLANES. The two planes of an axis share a word of the node (tb_trace.cuh), and the ray carries
 //     one byte-permute selector per axis and side, fixed by the sign of its direction: the PRMT that decodes the
 //     16-bit grid value picks the near or the far plane directly. The six min / max pairs per box of the generic
@@ -20,23 +24,26 @@
 //   - the stack pointer is the shared-memory ADDRESS of the lane's next free entry, and the row below entry 0 holds
 //     a {DONE, 0} sentinel: a pop is one LDS at [sp - row] and three selects, an empty stack pops "finished" by
 //     itself, a push is one STS at [sp] — no index arithmetic, no empty test;
-//   - OPT bit 0: a second pop in the same round when the first popped entry is already culled (a culled entry then
-//     costs 8 instructions instead of the lane's round);
-//   - OPT bit 1: a lane may park two leaves (siblings at the bottom of the tree arrive back to back; with one slot
-//     the second blocked the lane until the next triangle round);
-//   - the shared stack is sized from the tree (dynamic shared memory, TbTraceArgs::stack_smem rows), so no bench
-//     configuration runs the SPILL instantiation; trees deeper than TB_V6_MAX_SMEM_DEPTH keep 16 rows + local memory;
+//   - the shared stack is sized from the tree (dynamic shared memory, TbTraceArgs::stack_smem rows): trees up to 24
+//     levels (C1, C2, C5, C3 at 1M) run without the SPILL code; deeper ones keep 16 rows + local memory, because the
+//     shared stack comes out of the same 256 KB as L1 and a 30-row stack at 7 CTAs leaves the node fetches 18 KB of it
+//     (r2f A/B on the 10M-triangle terrain: 2.14 Grays/s with 30 rows, 3.23 with 16 + spill);
+//   - L2 policy per stream (ncu r2d, C3 1M: L2 hit rate 74 %, 115 B of DRAM traffic per ray — the 32 B rays and 16 B hit
+//     records of a 64M-ray batch stream through L2 and push the 80 MB of nodes + triangles out): node loads ask L2 to
+//     evict them last, ray loads and hit stores go through an evict-first policy (createpolicy: the descriptor lives
+//     in uniform registers, no per-thread cost). +2 % on C3 1M;
 //   - the three reciprocals behind the box planes are rcp.approx (1 ulp: four orders of magnitude inside the box
 //     padding); the one behind the triangle test stays IEEE (bit-exact t, u, v);
 //   - a hit record is written when the closest hit improves (the triangle's tag words are in registers right then),
 //     not at retirement: no dependent triangle re-fetch when a ray ends, and u, v need no registers;
-//   - registers (64 per thread at 8 CTAs per SM; the first version of this file spilled three selectors into local
-//     memory and re-read them every round): the axis permutation of the triangle test is one packed word, the cull
-//     distance is recomputed from the closest hit instead of carried;
+//   - registers: 7 CTAs per SM at 72 registers instead of 8 at 64. At 64 the compiler spilled a selector and the
+//     refill flag into local memory and re-read them every round (+9 % on C3 1M for the 7-CTA build, r2a A/B); the
+//     axis permutation of the triangle test is one packed word and the cull distance is recomputed from the closest
+//     hit instead of carried, which is what keeps it at 72;
 //   - finished rays are retired only when the warp has one.
 #pragma once
 
-#define TB_V6_MAX_SMEM_DEPTH   28          /* (28 + 2) rows x 1 KB x 7 CTAs = 210 KB of the SM's 228 KB */
+#define TB_V6_MAX_SMEM_DEPTH   24          /* (24 + 3) rows x 1 KB x 7 CTAs = 189 KB of the SM's 256 KB of L1 + shared memory */
 #define TB_V6_SPILL_SMEM_DEPTH 16
 #define TB_V6_LOCAL            (TB_STACK_SMEM + TB_STACK_LOCAL)
 
@@ -100,36 +107,33 @@ __device__ __forceinline__ void tb_sts64(unsigned addr, int2 v) {
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" :: "r"(addr), "r"(v.x), "r"(v.y) : "memory");
 }
 
-// OPT bit 2: cache policy per stream — nodes are re-used (by this ray's siblings in the warp and by the next rays),
-// triangles, rays and hit records are touched once: triangle and ray loads do not allocate in L1, node loads ask to
-// be evicted last. The kernel is bound by the latency of node fetches that miss L1 (r2a A/B: shrinking L1 from 92 KB
-// to 28 KB per SM cost 23 %), so what sits in L1 should be nodes.
-template <int OPT>
 __device__ __forceinline__ void tb_ld_qnode(const uint4* np, uint4& qa, uint4& qb) {
-    if (OPT & 4)
-        asm volatile("ld.global.nc.L1::evict_last.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                     : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
-    else
-        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                     : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
+    asm volatile("ld.global.nc.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));
 }
-template <int OPT>
-__device__ __forceinline__ float4 tb_ld_once(const float4* p) {
-    if (OPT & 4) {
-        float4 v;
-        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-        return v;
-    }
-    return __ldg(p);
+// ray records and hit records: streamed once through the whole hierarchy
+__device__ __forceinline__ float4 tb_ld_stream(const float4* p) {
+    float4 v;
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ void tb_st_stream(float4* p, float4 v) {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol) : "memory");
 }
 
 #ifndef TB_V6_CTAS_PER_SM
 #define TB_V6_CTAS_PER_SM 7     /* 72 registers: no spills; measured +9 % over 8 CTAs x 64 registers on C3 1M (profiles/r2a) */
 #endif
 
-template <bool COUNT, bool EXACT, bool SPILL, int OPT>
+template <bool COUNT, bool EXACT, bool SPILL>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v6(TbTraceArgs a) {
-    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 2][TB_TRACE_THREADS] x 8 B
+    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][TB_TRACE_THREADS] x 8 B
     constexpr int ROW = TB_TRACE_THREADS * 8;
     int2 l_stack[SPILL ? TB_V6_LOCAL : 1];
     const int tid = threadIdx.x;
@@ -138,11 +142,13 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
     const int total = a.count_ptr ? *a.count_ptr : a.count;
     // entry k of this lane's stack lives at bottom + k * ROW (shared-space addresses); the row below entry 0 holds the
     // sentinel an empty pop reads, the row above the deepest entry is the scratch an unconditional push writes
-    const unsigned bottom = (unsigned)__cvta_generic_to_shared(s_v6_stack) + ROW + tid * 8;
+    // (one more row below the sentinel: the pop is unconditional, and after the sentinel has been popped the lanes
+    // that are finished keep reading one row further down until the warp refills)
+    const unsigned bottom = (unsigned)__cvta_generic_to_shared(s_v6_stack) + 2 * ROW + tid * 8;
     tb_sts64(bottom - ROW, make_int2(TB_REF_DONE, 0));             // never culled (tmin 0), never overwritten
     const unsigned smem_end = bottom + a.stack_smem * ROW;         // SPILL: entries from this address on live in local memory
 
-    int   slot = -1, cur = TB_REF_DONE, pend = TB_REF_DONE, pend2 = TB_REF_DONE;
+    int   slot = -1, cur = TB_REF_DONE, pend = TB_REF_DONE;
     unsigned sp = bottom;                          // address of the next free entry
     int   best_rank = -1, best_tag = 0;
     float best_t = FLT_MAX;
@@ -171,7 +177,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
                 const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
                 if (q < total) {
                     slot = a.queue ? a.queue[q] : q;
-                    const float4 o4 = tb_ld_once<OPT>(a.ray_o + slot), d4 = tb_ld_once<OPT>(a.ray_d + slot);
+                    const float4 o4 = tb_ld_stream(a.ray_o + slot), d4 = tb_ld_stream(a.ray_d + slot);
                     const V3 d = v3(d4.x, d4.y, d4.z);
                     r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
                     kpack = (kpack & 0x100) | r.kx | (r.ky << 2) | (r.kz << 4);
@@ -191,22 +197,14 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
             // 1. park a leaf (a further leaf waits in `cur` until a parking slot is free)
             {
                 const bool is_leaf = (unsigned)cur > (unsigned)TB_REF_POP;       // ~rank: 0x80000002 .. 0xffffffff
-                if (OPT & 2) {
-                    const bool p0 = is_leaf && pend == TB_REF_DONE;
-                    const bool p1 = is_leaf && !p0 && pend2 == TB_REF_DONE;
-                    pend = p0 ? cur : pend;
-                    pend2 = p1 ? cur : pend2;
-                    cur = (p0 || p1) ? TB_REF_POP : cur;
-                } else {
-                    const bool park = is_leaf && pend == TB_REF_DONE;
-                    pend = park ? cur : pend;
-                    cur = park ? TB_REF_POP : cur;
-                }
+                const bool park = is_leaf && pend == TB_REF_DONE;
+                pend = park ? cur : pend;
+                cur = park ? TB_REF_POP : cur;
             }
-            // 2. pop, resolved with selects. An entry the closest hit has culled since it was pushed leaves the
-            //    lane in POP state: with OPT bit 0 the second turn pops again at once.
-#pragma unroll
-            for (int turn = 0; turn < ((OPT & 1) ? 2 : 1); ++turn) {
+            // 2. pop, resolved with selects. An entry the closest hit has culled since it was pushed leaves the lane
+            //    in POP state: it pops again next round (a second pop in the same round, and a pop loop, were measured:
+            //    -1.5 % and -10 %, experiments/README.md)
+            {
                 int2 e;
                 if (SPILL && sp > smem_end) e = l_stack[(sp - smem_end) / ROW - 1];
                 else e = tb_lds64(sp - ROW);
@@ -226,14 +224,14 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
             uint4 qa, qb;
             if (is_node) {
                 if (!EXACT) {
-                    tb_ld_qnode<OPT>(a.qnodes + (size_t)cur * 2, qa, qb);
+                    tb_ld_qnode(a.qnodes + (size_t)cur * 2, qa, qb);
                 } else {
                     tb_load_node256(a.nodes + (size_t)cur * 4, q0, q1, q2, q3);
                 }
             }
             if (do_tri) {
                 const float4* tp = a.tris + (size_t)(~pend) * 3;
-                ta = tb_ld_once<OPT>(tp); tb = tb_ld_once<OPT>(tp + 1); tc = tb_ld_once<OPT>(tp + 2);
+                ta = __ldg(tp); tb = __ldg(tp + 1); tc = __ldg(tp + 2);
             }
             // 5. node step
             if (is_node) {
@@ -272,11 +270,10 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
                         best_t = t; best_rank = rank; best_tag = __float_as_int(tb.w);
                         // API rays: object | triangle << 8, u, v; wavefront: rank and the object | preset << 8 tag for the
                         // shade pass (u, v are not used there). A later, closer hit overwrites the record.
-                        a.hit_out[slot] = make_float4(t, a.emit_prim ? ta.w : __int_as_float(rank), a.emit_prim ? u : tb.w, v);
+                        tb_st_stream(a.hit_out + slot, make_float4(t, a.emit_prim ? ta.w : __int_as_float(rank), a.emit_prim ? u : tb.w, v));
                     }
                 }
-                if (OPT & 2) { pend = pend2; pend2 = TB_REF_DONE; }
-                else pend = TB_REF_DONE;
+                pend = TB_REF_DONE;
             }
             // 7. leave the rounds when the warp is done or has too few rays left to be worth a round
             const unsigned live = __ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE);
@@ -289,7 +286,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
             int preset = -1;
             if (finished) {
                 if (best_rank >= 0) preset = (best_tag >> 8) & 0xff;
-                else a.hit_out[slot] = make_float4(-1.f, __int_as_float(-1), 0.f, 0.f);
+                else tb_st_stream(a.hit_out + slot, make_float4(-1.f, __int_as_float(-1), 0.f, 0.f));
             }
             if (a.matq) {
 #pragma unroll

@@ -12,6 +12,7 @@
  *                  [--camera px py pz dx dy dz] [--fov deg] [--tonemap none|linear|reinhard|filmic|uncharted2]
  *                  [--exposure E] [--gamma G] [--env r g b] [--tile N] [--passes N] [--progress]
  *                  [--config satellite.config] [--out image.pfm|.ppm|.png|.hdr] [--dry-run]
+ *                  [--scene cornell|field] [--devices 0,1,...  (product build only: multi-GPU fan-out behind terra_render)]
  * --config reads the reference front-end's `name = value` file (satellite/include/Config.hpp:19-117,
  * satellite/src/Config.cpp:170-231); options are applied in command-line order. .png / .hdr are written the way
  * satellite's save_to_file does (Visualization.cpp:286-349): 8-bit clamp(v)*255 and Radiance RGBE of pixels[].
@@ -165,6 +166,47 @@ static void builtin_cornell(GroupVec* groups, MtlVec* mtls) {
     add_quad(group_for(groups, 2), p100, p101, p111, p110);   /* right -x: green */
     const float l0[3] = {.35f,.999f,.35f}, l1[3] = {.65f,.999f,.35f}, l2[3] = {.65f,.999f,.65f}, l3[3] = {.35f,.999f,.65f};
     add_quad(group_for(groups, 3), l0, l1, l2, l3);
+}
+
+/* --scene field: a procedural field of uv-spheres on a jittered grid over a floor (the shape of BASELINE config C2:
+ * 125 spheres x 760 triangles = 95k, 16 Lambert groups, 4 emissive spheres), so the multi-GPU fan-out has a workload
+ * without an asset file. Plain C generator (own LCG): same class of scene as terra_b200/scenes.py, not its bytes. */
+static unsigned field_rng = 12345u;
+static float field_rand(void) { field_rng = field_rng * 1664525u + 1013904223u; return (float)(field_rng >> 8) / 16777216.f; }
+static void add_tri_n(Group* g, const float* a, const float* b, const float* c, const float* ctr, float r) {
+    const float* p[3] = { a, b, c };
+    for (int k = 0; k < 3; ++k) for (int j = 0; j < 3; ++j) fpush(&g->pos, p[k][j]);
+    for (int k = 0; k < 3; ++k) for (int j = 0; j < 3; ++j) fpush(&g->nrm, (p[k][j] - ctr[j]) / r);
+    for (int k = 0; k < 6; ++k) fpush(&g->tex, 0.f);
+}
+static void builtin_field(GroupVec* groups, MtlVec* mtls, float* cam) {
+    const float extent = 100.f; const int gdim = 5, n_lat = 20, n_lon = 20, n_groups = 16;
+    for (int i = 0; i < n_groups; ++i) { char nm[32]; snprintf(nm, sizeof nm, "lambert%d", i); Mtl* m = mtl_add(mtls, nm); for (int k = 0; k < 3; ++k) m->kd[k] = 0.2f + 0.6f * field_rand(); }
+    { Mtl* m = mtl_add(mtls, "emitter"); m->ke[0] = 12.f; m->ke[1] = 11.f; m->ke[2] = 10.f; }
+    { Mtl* m = mtl_add(mtls, "floor"); m->kd[0] = m->kd[1] = m->kd[2] = 0.5f; }
+    const float cell = extent / gdim, PI = 3.14159265358979f;
+    int idx = 0, emitters = 0;
+    for (int i = 0; i < gdim; ++i) for (int j = 0; j < gdim; ++j) for (int k = 0; k < gdim; ++k, ++idx) {
+        const float ctr[3] = { (i + 0.3f + 0.4f * field_rand()) * cell, (j + 0.3f + 0.4f * field_rand()) * cell, (k + 0.3f + 0.4f * field_rand()) * cell };
+        const float r = cell * (0.22f + 0.10f * field_rand());
+        int grp = idx % n_groups;
+        if (idx % 31 == 7 && emitters < 4) { grp = n_groups; ++emitters; }
+        Group* g = group_for(groups, grp);
+        for (int a = 0; a < n_lat; ++a) for (int b = 0; b < n_lon; ++b) {
+            float v[4][3];
+            for (int q = 0; q < 4; ++q) {
+                const float th = PI * (a + (q >> 1)) / n_lat, ph = 2 * PI * (b + (q & 1)) / n_lon;
+                v[q][0] = ctr[0] + r * sinf(th) * cosf(ph); v[q][1] = ctr[1] + r * cosf(th); v[q][2] = ctr[2] + r * sinf(th) * sinf(ph);
+            }
+            if (a != 0) add_tri_n(g, v[0], v[2], v[1], ctr, r);
+            if (a != n_lat - 1) add_tri_n(g, v[1], v[2], v[3], ctr, r);
+        }
+    }
+    const float m = 0.15f * extent, y = -0.5f;
+    const float f0[3] = { -m, y, -m }, f1[3] = { extent + m, y, -m }, f2[3] = { extent + m, y, extent + m }, f3[3] = { -m, y, extent + m };
+    add_quad(group_for(groups, n_groups + 1), f0, f3, f2, f1);
+    const float c[6] = { extent * 0.5f, extent * 0.62f, -extent * 1.05f, 0.f, -0.18f, 1.f };
+    memcpy(cam, c, sizeof c);
 }
 
 /* ------------------------------------------------------------------ image output */
@@ -374,6 +416,8 @@ int main(int argc, char** argv) {
     const char* out = "terra.pfm";
     size_t passes = 1;
     int dry = 0, progress = 0;
+    const char* builtin = "cornell";
+    int devices[16], n_devices = 0;
     Settings S;
     memset(&S, 0, sizeof S);
     S.width = 256; S.height = 256; S.spp = 16; S.bounces = 8;
@@ -400,6 +444,13 @@ int main(int argc, char** argv) {
         else if (!strcmp(a, "--gamma")) { NEED(1); S.gamma_ = strtof(argv[++i], NULL); }
         else if (!strcmp(a, "--env")) { NEED(3); for (int k = 0; k < 3; ++k) S.env[k] = strtof(argv[++i], NULL); }
         else if (!strcmp(a, "--camera")) { NEED(6); for (int k = 0; k < 6; ++k) S.cam[k] = strtof(argv[++i], NULL); S.have_cam = 1; }
+        else if (!strcmp(a, "--scene")) { NEED(1); builtin = argv[++i]; }
+#ifdef TERRA_HEADLESS_B200
+        else if (!strcmp(a, "--devices")) {      /* "0,1,2,3": the scene is replicated on these GPUs and full-frame calls are split over them */
+            NEED(1);
+            for (const char* q = argv[++i]; *q && n_devices < 16;) { char* end; long v = strtol(q, &end, 10); if (end == q) break; devices[n_devices++] = (int)v; q = *end == ',' ? end + 1 : end; }
+        }
+#endif
         else if (!strcmp(a, "--progress")) progress = 1;
         else if (!strcmp(a, "--dry-run")) dry = 1;
         else { fprintf(stderr, "usage: terra_headless [--config satellite.config] [--obj f.obj] [--width W] [--height H] [--spp N] [--bounces N]\n"
@@ -409,17 +460,23 @@ int main(int argc, char** argv) {
     }
     const char* obj = S.have_obj ? S.obj : NULL;
     const size_t width = S.width, height = S.height, spp = S.spp, bounces = S.bounces, tile = S.tile;
-    const int integrator = S.integrator, tonemap = S.tonemap, have_cam = S.have_cam;
+    const int integrator = S.integrator, tonemap = S.tonemap;
     const float jitter = S.jitter, fov = S.fov, exposure = S.exposure, gamma_ = S.gamma_;
     float* env = S.env; float* cam = S.cam;
     GroupVec groups = {0}; MtlVec mtls = {0};
     if (obj) { if (!load_obj(obj, &groups, &mtls)) return 1; }
+    else if (!strcmp(builtin, "field")) { builtin_field(&groups, &mtls, cam); S.have_cam = 1; }
     else builtin_cornell(&groups, &mtls);
     if (groups.n == 0) { fprintf(stderr, "terra_headless: no triangles\n"); return 1; }
     if (groups.n > 64) { fprintf(stderr, "terra_headless: %zu material groups; Terra supports 64 objects (SURVEY Q14)\n", groups.n); return 1; }
 
     /* ---- scene: one TerraObject per material group (satellite/src/Scene.cpp:147-233) */
     HTerraScene scene = terra_scene_create();
+#ifdef TERRA_HEADLESS_B200
+    if (n_devices) terra_b200_scene_set_devices(scene, devices, n_devices);
+#else
+    (void)devices; (void)n_devices;
+#endif
     size_t total = 0;
     float lo[3] = { 1e30f, 1e30f, 1e30f }, hi[3] = { -1e30f, -1e30f, -1e30f };
     for (size_t g = 0; g < groups.n; ++g) {
@@ -477,7 +534,7 @@ int main(int argc, char** argv) {
     opt->gamma = gamma_;
 
     TerraCamera camera;
-    if (!have_cam && obj) {                                   /* frame the model from the front */
+    if (!S.have_cam && obj) {                                   /* frame the model from the front */
         const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), ext = fmaxf(hi[0] - lo[0], fmaxf(hi[1] - lo[1], hi[2] - lo[2]));
         cam[0] = cx; cam[1] = cy; cam[2] = lo[2] - 1.5f * ext; cam[3] = 0; cam[4] = 0; cam[5] = 1;
     }
@@ -497,7 +554,10 @@ int main(int argc, char** argv) {
     clock_gettime(CLOCK_MONOTONIC, &t1);
     TerraFramebuffer fb;
     if (!terra_framebuffer_create(&fb, width, height)) { fprintf(stderr, "terra_headless: framebuffer %zux%zu\n", width, height); return 1; }
+    double last_pass_s = 0;
     for (size_t p = 0; p < passes; ++p) {                     /* progressive: results[] accumulate across calls, Terra.c:570-572 */
+        struct timespec p0, p1;
+        clock_gettime(CLOCK_MONOTONIC, &p0);
         if (tile == 0) terra_render(&camera, scene, &fb, 0, 0, width, height);
         else {                                                /* the tile grid of Renderer.cpp:316-349, begin / end events as :70-98 */
             const size_t n_tiles = ((width + tile - 1) / tile) * ((height + tile - 1) / tile);
@@ -511,6 +571,9 @@ int main(int argc, char** argv) {
                     if (progress) on_tile("end", x, y, tw, th, done, n_tiles);
                 }
         }
+        clock_gettime(CLOCK_MONOTONIC, &p1);
+        last_pass_s = (p1.tv_sec - p0.tv_sec) + 1e-9 * (p1.tv_nsec - p0.tv_nsec);
+        if (passes > 1) printf("terra_headless: pass %zu: %.4f s (%.2f Mpaths/s)\n", p + 1, last_pass_s, (double)width * height * spp / last_pass_s / 1e6);
     }
     clock_gettime(CLOCK_MONOTONIC, &t2);
     const double commit_s = (t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec);
