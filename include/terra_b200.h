@@ -295,6 +295,12 @@ typedef struct {
     uint64_t p2p_bytes;          /* device-to-device copies (scene replicas over NVLink) */
 } TerraB200Stats;
 
+/* Where the lanes of the incoherent-ray kernel's rounds go (counting on, primary device; reset by terra_b200_reset_stats).
+ * Lane-rounds: [0] all (32 x warp rounds)  [1] fetched a node  [2] popped an entry the closest hit had culled
+ * [3] held a second leaf while the first waits for a triangle round  [4] parked with nothing else to do
+ * [5] owned no ray  [6] lanes x triangle rounds (32 each)  [7] lanes that tested a triangle
+ * [8] 32 x refills  [9] lanes refilled.  profiles/r2_summary.md reads the kernel's instruction budget from these. */
+void terra_b200_round_stats(HTerraScene scene, uint64_t* out10);
 int  terra_b200_device_count(void);
 void terra_b200_set_device(int device);              /* before terra_scene_commit */
 /* Multi-GPU behind terra_render (the splitter of SURVEY 8b / 8e; the reference's own fan-out is one terra_render per

@@ -22,15 +22,12 @@ sys.path.insert(0, str(REPO))
 C3_VARIANTS = [
     ("v6 (default)", dict()),
     ("v6 refetch 26", dict(TERRA_B200_REFETCH="26")),
-    ("v6 refetch 18", dict(TERRA_B200_REFETCH="18")),
     ("v6 stack 16 rows + spill", dict(TERRA_B200_STACK_SMEM="16")),
     ("v6 tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
-    ("v6 tri_min 10", dict(TERRA_B200_TRI_MIN="10")),
 ]
 C2_VARIANTS = [
     ("default (v6 + fused raygen)", dict()),
     ("k_raygen instead of fused generation", dict(TERRA_B200_FUSED_RAYGEN="0")),
-    ("refetch 26", dict(TERRA_B200_REFETCH="26")),
 ]
 SWITCHES = ["TERRA_B200_INCOHERENT", "TERRA_B200_COHERENT", "TERRA_B200_V6_OPT", "TERRA_B200_STACK_SMEM", "TERRA_B200_TRI_MIN",
             "TERRA_B200_REFETCH", "TERRA_B200_FUSED_RAYGEN", "TERRA_B200_NODE_ORDER"]
@@ -100,8 +97,17 @@ def main():
             same = None if want is None else bool(torch.equal(got.view(torch.int32), want.view(torch.int32)))
             if want is None:
                 want = got
+            # work counters on a 1M-ray sample
+            lib.terra_b200_reset_stats(s.h)
+            lib.terra_b200_set_counting(s.h, 1)
+            m = min(n, 1 << 20)
+            lib.terra_b200_trace_rays_device(s.h, m, C.c_void_p(o4.data_ptr()), C.c_void_p(d4.data_ptr()), C.c_void_p(hits.data_ptr()), sp)
+            torch.cuda.synchronize()
+            st = s.stats()
+            lib.terra_b200_set_counting(s.h, 0)
             print(json.dumps({"ab": "c3", "build": tag, "variant": name, "tris": args.tris, "rays": n, "ms": ms,
-                              "mrays_per_s": n / ms / 1e3, "hit_t_same_as_first_variant": same}), flush=True)
+                              "mrays_per_s": n / ms / 1e3, "hit_t_same_as_first_variant": same,
+                              "nodes_per_ray": st.nodes_visited / m, "tris_per_ray": st.tris_tested / m}), flush=True)
             s.destroy()
     else:
         w, h, spp = 1920, 1080, args.spp

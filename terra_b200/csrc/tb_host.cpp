@@ -752,6 +752,7 @@ extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) {      
         out->coherent_tris_tested += t.coherent_tris_tested; out->p2p_bytes += t.p2p_bytes;
     }
 }
+extern "C" void terra_b200_round_stats(HTerraScene h, uint64_t* out10) { tb_device_round_stats(committed(h, "terra_b200_round_stats")->dev, out10); }
 extern "C" void terra_b200_reset_stats(HTerraScene h) { for (TbDevice* d : committed(h, "terra_b200_reset_stats")->devs) tb_device_reset_stats(d); }
 extern "C" void terra_b200_set_env_lit(HTerraScene h, int on) { for (TbDevice* d : committed(h, "terra_b200_set_env_lit")->devs) tb_device_set_env_lit(d, on); }
 // Devices of a scene, before its first commit (default: TERRA_B200_DEVICES, else the terra_b200_set_device one).

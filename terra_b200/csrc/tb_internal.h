@@ -147,6 +147,7 @@ void      tb_device_primary_hits(TbDevice* dev, const TbCameraFrame* cam, size_t
 void      tb_device_bsdf_kat(TbDevice* dev, size_t object_idx, size_t n, const float* e123, const float* wo,
                              const float* normal, float* out);
 void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
+void      tb_device_round_stats(TbDevice* dev, uint64_t* out10);
 void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 void      tb_device_set_env_lit(TbDevice* dev, int on);

@@ -263,8 +263,8 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
     d->stack_bound = 0;
     memset(&d->wave, 0, sizeof d->wave);
-    d->wave.counters = tb_alloc<int>(32);
-    TB_CUDA(cudaMemset(d->wave.counters, 0, 32 * sizeof(int)));
+    d->wave.counters = tb_alloc<int>(64);
+    TB_CUDA(cudaMemset(d->wave.counters, 0, 64 * sizeof(int)));
     d->fb_capacity = 0; d->d_results = NULL; d->d_pixels = NULL; d->d_acc = NULL; d->acc_capacity = 0;
     d->io_capacity = 0; d->d_io_o = d->d_io_d = NULL; d->d_io_hit = NULL;
     d->st_in = d->st_out = NULL; d->pipe_capacity = 0;
@@ -570,6 +570,7 @@ struct TbTraceArgs {
     int           tri_min, refetch_below;   // rounds kernels: parked leaves needed for a triangle round; refill below this many live lanes
     int           stack_smem;               // k_trace_v6: stack entries per lane held in (dynamic) shared memory
     float4*       lo;                       // fused ray generation: zeroed for the paths that leave the scene (k_trace_packet<.., GEN>)
+    unsigned long long* round_stats;        // COUNT: lane-rounds by state, see terra_b200_round_stats
 };
 
 // ==================================================================================== K1: ray generation
@@ -923,15 +924,26 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, MODE == TB_SHADE_SIMPLE ? TB
     const int rounds = (count + stride - 1) / stride;
     const TbDevScene& sc = a.sc;
     const bool first = a.gen.on != 0;
+    // The kernel is bound by the latency of a chain of dependent gathers (ncu r1w / r2d: long-scoreboard 6-35 stalled
+    // warps per issue, issue-active 12-36 %): queue entry -> slot -> hit record -> triangle / properties / material.
+    // The first two links do not depend on the shading of the previous hit, so they are fetched one and two rounds
+    // ahead (5 registers) and only the last link is exposed: -3 % on the non-trace part of the C2 step (r2i A/B;
+    // 4 CTAs per SM at 64 registers instead: no gain on C2, -3 % on C5).
+    const int i0 = blockIdx.x * blockDim.x + threadIdx.x;
+    int slot_c = i0 < count ? a.q[i0] : 0;
+    int slot_n = i0 + stride < count ? a.q[i0 + stride] : 0;
+    float4 hit_c = i0 < count ? a.hit[slot_c] : make_float4(0, 0, 0, 0);
     for (int it = 0; it < rounds; ++it) {
-        const int i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const int i = it * stride + i0;
         const bool valid = i < count;
+        const float4 hit_n = i + stride < count ? a.hit[slot_n] : make_float4(0, 0, 0, 0);
+        const int slot_nn = i + 2 * stride < count ? a.q[i + 2 * stride] : 0;
         bool alive = false, want_aux0 = false, want_aux1 = false, want_aux2 = false;
         int slot = 0;
         V3 next_o = v3s(0.f), next_d = v3s(0.f), aux0_d = v3s(0.f), aux1_d = v3s(0.f), aux2_d = v3s(0.f), aux_o = v3s(0.f);
         float4 o4 = make_float4(0, 0, 0, 0), d4 = o4;
         if (valid) {
-            slot = a.q[i];
+            slot = slot_c;
             if (first) {
                 uint64_t k0; V3 go;
                 const V3 gd = tb_gen_ray(a.gen, slot, &k0, &go);
@@ -940,7 +952,7 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, MODE == TB_SHADE_SIMPLE ? TB
             } else {
                 o4 = a.ray_o[slot]; d4 = a.ray_d[slot];
             }
-            const float4 h4 = a.hit[slot];
+            const float4 h4 = hit_c;
             const uint64_t key = ((uint64_t)__float_as_uint(d4.w) << 32) | __float_as_uint(o4.w);
             const uint32_t dim0 = 2u + (uint32_t)a.bounce * TB_DIMS_PER_BOUNCE;
             const V3 d = v3(d4.x, d4.y, d4.z);
@@ -1140,6 +1152,7 @@ __global__ void __launch_bounds__(TB_SHADE_THREADS, MODE == TB_SHADE_SIMPLE ? TB
                 a.next_q[at] = slot;
             }
         }
+        slot_c = slot_n; slot_n = slot_nn; hit_c = hit_n;
     }
 }
 
@@ -1329,7 +1342,8 @@ __global__ void k_bsdf_kat(TbDevScene sc, int object, size_t n, const float* e12
 // [3] visibility rays  [4..7] per-preset hit counts  [8..9] u64 rays traced (statistics)
 // [10..13] u64 nodes fetched, triangles tested by the incoherent-ray launches (counting variants only)
 // [14..15] u64 camera rays  [16..19] u64 nodes, triangles of the camera-ray launches
-#define TB_COUNTER_INTS 32
+// [32..51] u64 x 10: lane states of k_trace_v6's rounds (counting variants only, TbTraceArgs::round_stats)
+#define TB_COUNTER_INTS 64
 __global__ void k_counters(int* c, int mode, int value) {
     unsigned long long* rays = (unsigned long long*)(c + 8);
     unsigned long long* cam_rays = (unsigned long long*)(c + 14);
@@ -1341,7 +1355,8 @@ __global__ void k_counters(int* c, int mode, int value) {
         case 3: c[1] = c[2]; c[0] = 0; c[2] = 0; c[3] = 0; c[4] = c[5] = c[6] = c[7] = 0; *rays += (unsigned long long)c[1]; break;   // bounce ends, the next one begins
         case 4: *rays += (unsigned long long)value; c[0] = 0; break;                                 // stand-alone trace of `value` rays
         case 5: *rays += (unsigned long long)value; *cam_rays += (unsigned long long)value; c[0] = 0; break;   // ... of camera rays
-        default: for (int k = 8; k < 20; ++k) c[k] = 0; break;
+        default: for (int k = 8; k < 20; ++k) c[k] = 0;
+                 for (int k = 32; k < 52; ++k) c[k] = 0; break;
     }
 }
 
@@ -1444,6 +1459,7 @@ static void tb_launch_trace(TbDevice* d, cudaStream_t st, const TbTraceArgs& a, 
     if (e) TB_CUDA(cudaEventRecord(e->a, st));
     TbTraceArgs c = a;
     c.visit_counters = (unsigned long long*)(d->wave.counters + (coherent ? 16 : 10));
+    c.round_stats = coherent ? NULL : (unsigned long long*)(d->wave.counters + 32);
     c.tri_min = d->tri_min; c.refetch_below = d->refetch_below;
     const int kind = tb_trace_kind(d, coherent);
     if (d->counting) tb_launch_trace_kernel<true>(d, st, c, kind, NULL);
@@ -2333,6 +2349,10 @@ extern "C" void tb_device_get_stats(TbDevice* d, TerraB200Stats* out) {
     *out = d->stats;
 }
 
+extern "C" void tb_device_round_stats(TbDevice* d, uint64_t* out10) {
+    TB_CUDA(cudaSetDevice(d->index));
+    TB_CUDA(cudaMemcpy(out10, d->wave.counters + 32, 10 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+}
 extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; d->graph_epoch++; }
 extern "C" void tb_device_set_graph_paths(TbDevice* d, size_t max_paths) { d->graph_max_paths = max_paths; }
 // Builds TbDevDist2D over `f` (ny rows of nx, device) into freshly allocated device arrays.

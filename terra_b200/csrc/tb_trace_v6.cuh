@@ -130,7 +130,6 @@ __device__ __forceinline__ void tb_st_stream(float4* p, float4 v) {
 #ifndef TB_V6_CTAS_PER_SM
 #define TB_V6_CTAS_PER_SM 7     /* 72 registers: no spills; measured +9 % over 8 CTAs x 64 registers on C3 1M (profiles/r2a) */
 #endif
-
 template <bool COUNT, bool EXACT, bool SPILL>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v6(TbTraceArgs a) {
     extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][TB_TRACE_THREADS] x 8 B
@@ -161,6 +160,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
     // bit 8 of kpack: the ray queue is empty — nothing to refill with, stay in the rounds to the end (a flag of its own
     // was one register too many: the compiler spilled it and re-read it every round)
     unsigned n_nodes = 0, n_tris = 0;
+    unsigned n_rounds = 0, n_culled = 0, n_second = 0, n_parked = 0, n_empty = 0, n_tri_rounds = 0, n_refills = 0, n_refilled = 0;
 
     while (true) {
         // ---- refill idle lanes (warp converged here)
@@ -173,6 +173,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
             if ((int)lane == leader) base = atomicAdd(a.cursor, want);
             base = __shfl_sync(FULL, base, leader);
             if (base + want >= total) kpack |= 0x100;
+            if (COUNT) ++n_refills;
             if (idle) {
                 const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
                 if (q < total) {
@@ -184,6 +185,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
                     if (!EXACT) sr = tb_sel_ray(r, d, a.grid_lo, a.grid_cell);
                     cur = 0; sp = bottom;
                     best_rank = -1; best_t = FLT_MAX;
+                    if (COUNT) ++n_refilled;
                 }
             }
         }
@@ -219,6 +221,16 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
             const unsigned pend_mask = __ballot_sync(FULL, pend != TB_REF_DONE);
             const bool tri_round = pend_mask != 0u && (__popc(pend_mask) >= a.tri_min || node_mask == 0u);
             const bool do_tri = tri_round && pend != TB_REF_DONE;
+            if (COUNT) {
+                ++n_rounds;
+                if (tri_round) ++n_tri_rounds;
+                if (!is_node) {
+                    if (cur == TB_REF_POP) ++n_culled;                                   // popped an entry the closest hit had culled
+                    else if (cur != TB_REF_DONE) ++n_second;                             // a leaf, while the parked one waits
+                    else if (pend != TB_REF_DONE) ++n_parked;
+                    else ++n_empty;
+                }
+            }
             // 4. all loads of the round first, so node and triangle latencies overlap
             float4 q0, q1, q2, q3, ta, tb, tc;
             uint4 qa, qb;
@@ -307,5 +319,10 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V6_CTAS_PER_SM) k_trace_v
     if (COUNT) {
         atomicAdd(a.visit_counters, (unsigned long long)n_nodes);
         atomicAdd(a.visit_counters + 1, (unsigned long long)n_tris);
+        if (a.round_stats) {
+            const unsigned v[10] = { n_rounds, n_nodes, n_culled, n_second, n_parked, n_empty, n_tri_rounds, n_tris, n_refills, n_refilled };
+#pragma unroll
+            for (int k = 0; k < 10; ++k) atomicAdd(a.round_stats + k, (unsigned long long)v[k]);
+        }
     }
 }
