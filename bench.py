@@ -453,7 +453,9 @@ def run_render_arm(args):
                 api.Scene.commit = orig_commit
             ids = (C.c_int * world)(*range(world))
             lib.terra_b200_scene_set_devices(s_all.h, ids, world)
+            t_commit = time.perf_counter()
             s_all.commit()
+            t_commit = time.perf_counter() - t_commit
             lib.terra_b200_set_seed(s_all.h, 2024)
             fb = api.Framebuffer()
             assert lib.terra_framebuffer_create(C.byref(fb), w, h)
@@ -468,7 +470,8 @@ def run_render_arm(args):
                 tot += (time.perf_counter() - t0) * 1e3
             ms_e2e = tot / n_e2e
             st_all = s_all.stats()
-            e2e_note = {"devices": world, "p2p_bytes_at_commit": int(st_all.p2p_bytes), "render_ms_device_clock": st_all.render_ms / (n_e2e + max(1, min(3, args.warmup)))}
+            e2e_note = {"devices": world, "p2p_bytes_at_commit": int(st_all.p2p_bytes), "render_ms_device_clock": st_all.render_ms / (n_e2e + max(1, min(3, args.warmup))),
+                        "commit_s_all_devices": t_commit}
             s_all.destroy()
         dist.barrier(group=cpu_group)
         h2d, d2h = w * h * 16 + 40, w * h * 28

@@ -311,10 +311,15 @@ void terra_b200_set_device(int device);              /* before terra_scene_commi
  * pairs (default 16M) is then split by sample range: GPU g renders range g of the whole region, and finalises and
  * returns row band g of it, summing the band over all GPUs' accumulators through peer-mapped memory inside the
  * accumulate / tonemap kernel. Smaller calls, and every other entry point, run on the first device. Sample ranges
- * use the same counter-based random numbers as one GPU; the per-pixel float sum re-associates. */
+ * use the same counter-based random numbers as one GPU; the per-pixel float sum re-associates.
+ * A split call of at least 2 x chunk_paths (pixel, sample) pairs per GPU (default 16M) goes through as two row chunks,
+ * the first seven eighths of the region and the rest: the framebuffer traffic of the first chunk (PCIe in and out,
+ * NVLink reduce) runs beside the rendering of the second. The image does not depend on the chunking, bit for bit.
+ * One host thread per GPU issues that GPU's work. */
 void terra_b200_scene_set_devices(HTerraScene scene, const int* device_ids, int count);
 int  terra_b200_scene_device_count(HTerraScene scene);
 void terra_b200_set_fanout_min_paths(HTerraScene scene, size_t min_paths);
+void terra_b200_set_fanout_chunk_paths(HTerraScene scene, size_t chunk_paths);
 void terra_b200_set_seed(HTerraScene scene, uint64_t seed);   /* default: time based, like the reference */
 void terra_b200_get_stats(HTerraScene scene, TerraB200Stats* out);
 void terra_b200_reset_stats(HTerraScene scene);

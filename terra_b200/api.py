@@ -172,6 +172,7 @@ class TerraLib:
             sig("terra_b200_scene_set_devices", None, _vp, C.POINTER(C.c_int), C.c_int)
             sig("terra_b200_scene_device_count", C.c_int, _vp)
             sig("terra_b200_set_fanout_min_paths", None, _vp, _sz)
+            sig("terra_b200_set_fanout_chunk_paths", None, _vp, _sz)
             sig("terra_b200_probe_bandwidth", C.c_double, _sz, C.c_int)
             sig("terra_b200_set_env_lit", None, _vp, C.c_int)
             sig("terra_b200_render_async", _vp, C.POINTER(Camera), _vp, C.POINTER(Framebuffer), _sz, _sz, _sz, _sz, _sz, _vp, _vp, _vp)

@@ -19,6 +19,8 @@
 #include <algorithm>
 #include <chrono>
 #include <atomic>
+#include <condition_variable>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -255,6 +257,48 @@ struct TbLightHost {                 // reference TerraLight, src/TerraPrivate.h
     std::vector<float> triangle_area;
 };
 
+// One issuing thread per device of a multi-GPU scene. A fanned-out terra_render launches ~45 kernels per device; issued
+// from one host thread, device 7 of 8 started 1.3 ms after device 0 (r2m: e2e 13.8 ms against 12.3 ms of device work on
+// C2 at N = 8). The threads live as long as the scene; run() hands every thread the same job and returns when all are done.
+struct TbFanPool {
+    std::vector<std::thread> threads;
+    std::mutex m;
+    std::condition_variable go, done;
+    std::function<void(int)> job;
+    uint64_t generation;
+    int pending;
+    bool quit;
+    explicit TbFanPool(int n) : generation(0), pending(0), quit(false) {
+        for (int g = 0; g < n; ++g) threads.emplace_back([this, g] { main(g); });
+    }
+    ~TbFanPool() {
+        { std::lock_guard<std::mutex> l(m); quit = true; }
+        go.notify_all();
+        for (std::thread& t : threads) t.join();
+    }
+    void main(int g) {
+        uint64_t seen = 0;
+        std::unique_lock<std::mutex> l(m);
+        while (true) {
+            go.wait(l, [&] { return quit || generation != seen; });
+            if (quit) return;
+            seen = generation;
+            l.unlock();
+            job(g);
+            l.lock();
+            if (--pending == 0) done.notify_one();
+        }
+    }
+    void run(const std::function<void(int)>& f) {
+        std::unique_lock<std::mutex> l(m);
+        job = f;
+        pending = (int)threads.size();
+        ++generation;
+        go.notify_all();
+        done.wait(l, [&] { return pending == 0; });
+    }
+};
+
 struct TbScene {
     TerraSceneOptions opts;          // committed
     TerraSceneOptions new_opts;      // what terra_scene_get_options hands out (Terra.c:24-43)
@@ -276,6 +320,8 @@ struct TbScene {
     std::vector<TbDevice*> devs;      // one per device_ids entry once committed; devs[0] == dev
     bool              peers_ok;       // every pair of the scene's devices can map the other's memory
     size_t            fanout_min_paths;   // terra_render calls of at least this many paths are split over the devices
+    TbFanPool*        fan;            // issuing threads of the fan-out, created by the first call that fans out
+    size_t            fanout_chunk_paths; // paths per device in one row chunk of a fanned-out call (TERRA_B200_FANOUT_CHUNK)
     uint64_t          seed;
     bool              seed_fixed;
     uint64_t          render_calls;
@@ -339,6 +385,10 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     s->dev = NULL;
     s->device_ids = default_device_ids();
     s->peers_ok = false;
+    s->fan = NULL;
+    s->fanout_chunk_paths = (size_t)1 << 24;
+    if (const char* e = getenv("TERRA_B200_FANOUT_CHUNK")) s->fanout_chunk_paths = (size_t)strtoull(e, NULL, 10);
+    if (s->fanout_chunk_paths < 1) s->fanout_chunk_paths = 1;
     s->fanout_min_paths = (size_t)1 << 24;
     if (const char* e = getenv("TERRA_B200_FANOUT_MIN")) s->fanout_min_paths = (size_t)strtoull(e, NULL, 10);
     s->seed = 0;
@@ -388,6 +438,7 @@ extern "C" void terra_scene_destroy(HTerraScene h) {                            
         terra_free(s->objects[i].properties);
     }
     terra_free(s->objects);
+    delete s->fan;
     for (TbDevice* d : s->devs) tb_device_destroy(d);
     delete s;
 }
@@ -662,14 +713,39 @@ extern "C" void terra_render(const TerraCamera* camera, HTerraScene h, const Ter
         // ---- the multi-GPU splitter behind the reference's call: the scene is replicated, device g
         //      renders sample range g of the whole region, then finalises and returns row band g — a reduce-scatter
         //      over NVLink fused into the accumulate / tonemap kernel, and every PCIe link carries 1/n of the
-        //      framebuffer in each direction (tb_render.cu, tb_device_partial_*). One host thread issues everything:
-        //      nothing below blocks until the waits.
-        std::vector<size_t> row0(n_dev + 1), base(n_dev + 1);
-        for (size_t g = 0; g <= n_dev; ++g) { row0[g] = height * g / n_dev; base[g] = spp * g / n_dev; }
-        for (size_t g = 0; g < n_dev; ++g)
-            tb_device_partial_begin(s->devs[g], &cam, fb, x, y, width, height, row0[g], row0[g + 1] - row0[g], base[g], base[g + 1] - base[g], seed);
-        for (size_t g = 0; g < n_dev; ++g)
-            tb_device_partial_finish(s->devs[g], s->devs.data(), (int)n_dev, fb, x, y, width, height, row0[g], row0[g + 1] - row0[g], spp);
+        //      framebuffer in each direction (tb_render.cu, tb_device_partial_*). One host thread per device issues
+        //      that device's launches (TbFanPool); the second phase starts when every device has RECORDED the event
+        //      the others wait on (a wait on an event not yet recorded would be a no-op).
+        //      A large region goes through as TWO row chunks, the first seven eighths and the rest: the framebuffer
+        //      traffic of the first (PCIe in and out, NVLink reduce) runs beside the rendering of the second, and only
+        //      an eighth of it is left exposed at the end. Device g finalises and returns slice g of each chunk.
+        //      (Measured on C2, r2o: a chunk costs ~0.2 ms of launch tails, so equal chunks of 16M paths lost more
+        //      than they hid — 50.5 against 49.0 ms at N = 2.)
+        std::vector<size_t> base(n_dev + 1);
+        for (size_t g = 0; g <= n_dev; ++g) base[g] = spp * g / n_dev;
+        std::vector<size_t> crow;
+        crow.push_back(0);
+        if (width * height * spp / n_dev >= 2 * s->fanout_chunk_paths && height >= 16) {
+            size_t tail = (height / 8 + 3) & ~(size_t)3;                                  // 8x4 pixel tiles stay whole
+            crow.push_back(height - tail);
+        }
+        crow.push_back(height);
+        const size_t n_chunks = crow.size() - 1;
+        size_t stage_px = 0;                                                              // slices of one device, all chunks
+        for (size_t c = 0; c < n_chunks; ++c) stage_px += ((crow[c + 1] - crow[c]) / n_dev + 1) * width;
+        if (!s->fan || s->fan->threads.size() != n_dev) { delete s->fan; s->fan = new TbFanPool((int)n_dev); }
+        for (size_t c = 0; c < n_chunks; ++c) {
+            const size_t rows = crow[c + 1] - crow[c];
+            auto slice0 = [&](size_t g) { return crow[c] + rows * g / n_dev; };
+            s->fan->run([&](int g) {
+                tb_device_partial_begin(s->devs[g], &cam, fb, x, y, width, height, c, crow[c], rows, slice0(g), slice0(g + 1) - slice0(g),
+                                        stage_px, base[g], base[g + 1] - base[g], seed);
+            });
+            s->fan->run([&](int g) {
+                tb_device_partial_finish(s->devs[g], s->devs.data(), (int)n_dev, fb, x, y, width, height, slice0(g), slice0(g + 1) - slice0(g),
+                                         spp, c + 1 == n_chunks);
+            });
+        }
         for (size_t g = 0; g < n_dev; ++g) tb_device_partial_wait(s->devs[g], s->devs.data(), (int)n_dev);
         return;
     }
@@ -764,6 +840,7 @@ extern "C" void terra_b200_scene_set_devices(HTerraScene h, const int* device_id
 }
 extern "C" int terra_b200_scene_device_count(HTerraScene h) { return (int)((TbScene*)h)->device_ids.size(); }
 extern "C" void terra_b200_set_fanout_min_paths(HTerraScene h, size_t min_paths) { ((TbScene*)h)->fanout_min_paths = min_paths; }
+extern "C" void terra_b200_set_fanout_chunk_paths(HTerraScene h, size_t paths) { ((TbScene*)h)->fanout_chunk_paths = paths ? paths : 1; }
 extern "C" void terra_b200_distribution_2d_sample(HTerraScene h, const float* f, size_t nx, size_t ny, size_t n,
                                                   const float* e1, const float* e2, float* out4) {
     TbScene* s = committed(h, "terra_b200_distribution_2d_sample");

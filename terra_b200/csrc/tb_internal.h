@@ -134,9 +134,10 @@ void      tb_device_render_resident(TbDevice* dev, const TbCameraFrame* cam, siz
                                     size_t x, size_t y, size_t w, size_t h, size_t sample_base, size_t spp,
                                     uint64_t seed, void* d_results, void* stream);
 void      tb_device_partial_begin(TbDevice* dev, const TbCameraFrame* cam, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
-                                  size_t band_row0, size_t band_rows, size_t sample_base, size_t spp, uint64_t seed);
+                                  size_t chunk, size_t chunk_row0, size_t chunk_rows, size_t slice_row0, size_t slice_rows,
+                                  size_t stage_px, size_t sample_base, size_t spp, uint64_t seed);
 void      tb_device_partial_finish(TbDevice* dev, TbDevice* const* devs, int n_dev, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
-                                   size_t band_row0, size_t band_rows, size_t spp_total);
+                                   size_t slice_row0, size_t slice_rows, size_t spp_total, int last);
 void      tb_device_partial_wait(TbDevice* dev, TbDevice* const* devs, int n_dev);
 int       tb_device_enable_peers(TbDevice* const* devs, int n_dev);
 void      tb_device_clone_geometry(TbDevice* dst, const TbDevice* src);

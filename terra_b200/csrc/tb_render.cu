@@ -171,6 +171,8 @@ struct TbDevice {
     size_t       ev_used;
     cudaEvent_t  ev_call_a, ev_call_b, ev_legacy;
     cudaEvent_t  ev_partial, ev_band;      // multi-device terra_render: this device's accumulator is complete / its band is finalised
+    cudaEvent_t  ev_slice_in;              // ... its slice of the caller's results[] has arrived
+    size_t       stage_off;                // ... pixels of d_results / d_pixels the slices of this call have taken so far
     int          counting;     // use the counting variant of k_trace (work counters for the roofline)
     int          exact_boxes;  // reference tree: reference box arithmetic
     int          trace_kind;   // TB_K_* forced by TERRA_B200_TRACE, or TB_K_AUTO
@@ -271,7 +273,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     d->d_env_f = d->d_env_cdf = d->d_env_rows = d->d_env_marg = NULL;
     d->graph_epoch = 1; d->graph_clock = 0; d->capturing = false; d->env_mode = 0;
     d->d_call = tb_alloc<TbCallParams>(1);
-    TB_CUDA(cudaHostAlloc((void**)&d->h_call, sizeof(TbCallParams), cudaHostAllocDefault));
+    TB_CUDA(cudaHostAlloc((void**)&d->h_call, 8 * sizeof(TbCallParams), cudaHostAllocDefault));      // TB_CALL_SLOTS
     for (int k = 0; k < 2; ++k) { d->d_pipe_o3[k] = d->d_pipe_d3[k] = NULL; d->d_pipe_hit[k] = NULL; }
     d->stage_capacity = 0;
     for (int k = 0; k < 2; ++k) { d->h_stage_o3[k] = d->h_stage_d3[k] = NULL; d->h_stage_hit[k] = NULL; }
@@ -304,6 +306,8 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaEventCreateWithFlags(&d->ev_legacy, cudaEventDisableTiming));
     TB_CUDA(cudaEventCreateWithFlags(&d->ev_partial, cudaEventDisableTiming));
     TB_CUDA(cudaEventCreateWithFlags(&d->ev_band, cudaEventDisableTiming));
+    TB_CUDA(cudaEventCreateWithFlags(&d->ev_slice_in, cudaEventDisableTiming));
+    d->stage_off = 0;
     return d;
 }
 
@@ -343,6 +347,7 @@ extern "C" void tb_device_destroy(TbDevice* d) {
     cudaEventDestroy(d->ev_legacy);
     cudaEventDestroy(d->ev_partial);
     cudaEventDestroy(d->ev_band);
+    cudaEventDestroy(d->ev_slice_in);
     cudaStreamDestroy(d->stream);
     delete d;
 }
@@ -1495,6 +1500,11 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, size_t w, size_t h, s
     const size_t cap = tb_batch_capacity();
     const size_t px_per_wave = npx < cap ? npx : cap;
     size_t s_per_wave = npx < cap ? cap / npx : 1;
+    // a warp of the camera-ray packet kernel holds `sub` samples of one pixel, a power of two that divides the wave's
+    // sample count: keep that count a multiple of 32 (or a power of two below 32). 37 samples per wave instead of 32
+    // cost the C2 frame 9 % (r2o: packets of 32 different pixels instead of 32 samples of one)
+    if (s_per_wave >= 32) s_per_wave &= ~(size_t)31;
+    else while (s_per_wave & (s_per_wave - 1)) s_per_wave &= s_per_wave - 1;
     if (s_per_wave > spp) s_per_wave = spp;
     if (s_per_wave < 1) s_per_wave = 1;
     if (d->wave.capacity < px_per_wave * s_per_wave) d->graph_epoch++;       // the wave buffers move: graphs that baked their addresses are stale
@@ -1606,10 +1616,11 @@ static void tb_render_region(TbDevice* d, cudaStream_t st, size_t w, size_t h, s
 }
 
 // The per-call values of a render call, written to device memory before its kernels (direct launches and graph
-// replays alike). h_call is page-locked and reused: the calls are synchronous, so the copy has run before the next one.
+// replays alike). h_call is page-locked and reused: the calls are synchronous, so the copy has run before the next one
+// (the chunks of a fanned-out call are not: each takes its own slot of h_call).
 static void tb_set_call(TbDevice* d, cudaStream_t st, const TbCameraFrame* cam, size_t fbw, size_t fbh, size_t x, size_t y,
-                        size_t sample_base, uint64_t seed, void* d_results) {
-    TbCallParams* hp = d->h_call;
+                        size_t sample_base, uint64_t seed, void* d_results, int slot = 0) {
+    TbCallParams* hp = d->h_call + slot;
     memset(hp, 0, sizeof *hp);
     hp->cam = *cam;
     hp->x = (int)x; hp->y = (int)y; hp->fbw = (int)fbw; hp->fbh = (int)fbh;
@@ -1790,63 +1801,94 @@ extern "C" void tb_device_render_resident(TbDevice* d, const TbCameraFrame* cam,
     tb_finish_call(d, st, true);
 }
 
+// The copy-in and copy-out streams beside the compute stream (host-buffer ray batches, fanned-out terra_render), made on first use.
+static void tb_pipe_streams(TbDevice* d) {
+    if (d->st_in) return;
+    {
+        TB_CUDA(cudaStreamCreateWithFlags(&d->st_in, cudaStreamNonBlocking));
+        TB_CUDA(cudaStreamCreateWithFlags(&d->st_out, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_in[k], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_pack[k], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_trace[k], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&d->ev_out[k], cudaEventDisableTiming));
+        }
+    }
+}
+
 // ---- multi-device terra_render (tb_host.cpp fans a large call out over the scene's devices) -----------------
-// 1. tb_device_partial_begin on every device: upload the device's row band of the caller's results[], render the
-//    device's sample range of the whole region into its accumulator, record an event. Nothing blocks.
-// 2. tb_device_partial_finish on every device: wait for ALL devices' events, finalise the band from all
-//    accumulators (k_finalize_peers), copy the band back to the caller's framebuffer. Nothing blocks.
-// 3. tb_device_partial_wait on every device.
+// The region is cut into row CHUNKS; inside a chunk, device g owns SLICE g of the rows. Per chunk:
+// 1. tb_device_partial_begin on every device: upload the slice of the caller's results[] (copy-in stream), render the
+//    device's sample range of the CHUNK into its accumulator (compute stream), record an event. Nothing blocks.
+// 2. tb_device_partial_finish on every device: on the copy-out stream, wait for ALL devices' events, finalise the slice
+//    from all accumulators (k_finalize_peers) and copy it back to the caller's framebuffer — while the compute stream
+//    is already rendering the next chunk. Only the last chunk's transfers are exposed (r2n: one chunk per call left
+//    0.85 ms of PCIe time behind 12.3 ms of rendering on C2 at N = 8).
+// 3. tb_device_partial_wait on every device, once per call.
+#define TB_CALL_SLOTS 8      /* page-locked TbCallParams of the chunks of one call in flight (tb_set_call) */
 extern "C" void tb_device_partial_begin(TbDevice* d, const TbCameraFrame* cam, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
-                                        size_t band_row0, size_t band_rows, size_t sample_base, size_t spp, uint64_t seed) {
+                                        size_t chunk, size_t chunk_row0, size_t chunk_rows, size_t slice_row0, size_t slice_rows,
+                                        size_t stage_px, size_t sample_base, size_t spp, uint64_t seed) {
     TB_CUDA(cudaSetDevice(d->index));
     cudaStream_t st = d->stream;
-    const size_t npx = w * h, band_px = band_rows * w;
-    if (band_px > d->fb_capacity) {
-        d->graph_epoch++;
-        tb_free(d->d_results); tb_free(d->d_pixels);
-        d->d_results = tb_alloc<TerraRawIntegrationResult>(band_px);
-        d->d_pixels = tb_alloc<float>(band_px * 3);
-        d->fb_capacity = band_px;
+    const size_t npx = w * h, slice_px = slice_rows * w;
+    if (chunk == 0) {
+        if (stage_px > d->fb_capacity) {
+            d->graph_epoch++;
+            tb_free(d->d_results); tb_free(d->d_pixels);
+            d->d_results = tb_alloc<TerraRawIntegrationResult>(stage_px);
+            d->d_pixels = tb_alloc<float>(stage_px * 3);
+            d->fb_capacity = stage_px;
+        }
+        tb_acc_reserve(d, npx);
+        tb_pipe_streams(d);
+        d->stage_off = 0;
+        TB_CUDA(cudaEventRecord(d->ev_call_a, st));
+        TB_CUDA(cudaStreamWaitEvent(d->st_in, d->ev_call_a, 0));          // the staging buffers may just have been reallocated on st's clock
     }
-    tb_acc_reserve(d, npx);
-    TB_CUDA(cudaEventRecord(d->ev_call_a, st));
-    if (band_rows) {
-        TB_CUDA(cudaMemcpy2DAsync(d->d_results, w * sizeof(TerraRawIntegrationResult),
-                                  fb->results + (y + band_row0) * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
-                                  w * sizeof(TerraRawIntegrationResult), band_rows, cudaMemcpyHostToDevice, st));
-        d->stats.h2d_bytes += band_px * sizeof(TerraRawIntegrationResult);
+    if (slice_px) {
+        TB_CUDA(cudaMemcpy2DAsync(d->d_results + d->stage_off, w * sizeof(TerraRawIntegrationResult),
+                                  fb->results + (y + slice_row0) * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
+                                  w * sizeof(TerraRawIntegrationResult), slice_rows, cudaMemcpyHostToDevice, d->st_in));
+        d->stats.h2d_bytes += slice_px * sizeof(TerraRawIntegrationResult);
     }
-    TB_CUDA(cudaMemsetAsync(d->d_acc, 0, npx * sizeof(float4), st));
-    tb_set_call(d, st, cam, fb->width, fb->height, x, y, sample_base, seed, NULL);
-    if (spp) tb_render_region(d, st, w, h, spp, d->d_acc);
+    TB_CUDA(cudaEventRecord(d->ev_slice_in, d->st_in));
+    float4* acc = d->d_acc + chunk_row0 * w;
+    TB_CUDA(cudaMemsetAsync(acc, 0, chunk_rows * w * sizeof(float4), st));
+    tb_set_call(d, st, cam, fb->width, fb->height, x, y + chunk_row0, sample_base, seed, NULL, (int)(chunk % TB_CALL_SLOTS));
+    if (spp && chunk_rows) tb_render_region(d, st, w, chunk_rows, spp, acc);
     TB_CUDA(cudaEventRecord(d->ev_partial, st));
 }
 
 extern "C" void tb_device_partial_finish(TbDevice* d, TbDevice* const* devs, int n_dev, const TerraFramebuffer* fb, size_t x, size_t y, size_t w, size_t h,
-                                         size_t band_row0, size_t band_rows, size_t spp_total) {
+                                         size_t slice_row0, size_t slice_rows, size_t spp_total, int last) {
     TB_CUDA(cudaSetDevice(d->index));
-    cudaStream_t st = d->stream;
-    for (int g = 0; g < n_dev; ++g)
-        if (devs[g] != d) TB_CUDA(cudaStreamWaitEvent(st, devs[g]->ev_partial, 0));
-    if (band_rows) {
+    cudaStream_t so = d->st_out;
+    for (int g = 0; g < n_dev; ++g) TB_CUDA(cudaStreamWaitEvent(so, devs[g]->ev_partial, 0));
+    TB_CUDA(cudaStreamWaitEvent(so, d->ev_slice_in, 0));
+    if (slice_rows) {
         TbPeerFinalizeArgs fa;
         memset(&fa, 0, sizeof fa);
         for (int g = 0; g < n_dev; ++g) fa.acc[g] = devs[g]->d_acc;
         fa.n_dev = n_dev;
-        fa.p0 = (int)(band_row0 * w); fa.n_px = (int)(band_rows * w);
-        fa.results = d->d_results; fa.pixels = d->d_pixels;
+        fa.p0 = (int)(slice_row0 * w); fa.n_px = (int)(slice_rows * w);
+        fa.results = d->d_results + d->stage_off; fa.pixels = d->d_pixels + d->stage_off * 3;
         fa.spp = (int)spp_total; fa.tonemap = d->sc.tonemap; fa.exposure = d->sc.exposure; fa.inv_gamma = d->sc.inv_gamma;
-        k_finalize_peers<<<d->sm_count * 4, 256, 0, st>>>(fa);
+        k_finalize_peers<<<d->sm_count * 4, 256, 0, so>>>(fa);
         d->stats.kernel_launches += 1;
-        TB_CUDA(cudaMemcpy2DAsync(fb->results + (y + band_row0) * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
-                                  d->d_results, w * sizeof(TerraRawIntegrationResult),
-                                  w * sizeof(TerraRawIntegrationResult), band_rows, cudaMemcpyDeviceToHost, st));
-        TB_CUDA(cudaMemcpy2DAsync(fb->pixels + (y + band_row0) * fb->width + x, fb->width * sizeof(TerraFloat3),
-                                  d->d_pixels, w * sizeof(TerraFloat3), w * sizeof(TerraFloat3), band_rows, cudaMemcpyDeviceToHost, st));
-        d->stats.d2h_bytes += band_rows * w * (sizeof(TerraRawIntegrationResult) + sizeof(TerraFloat3));
+        TB_CUDA(cudaMemcpy2DAsync(fb->results + (y + slice_row0) * fb->width + x, fb->width * sizeof(TerraRawIntegrationResult),
+                                  d->d_results + d->stage_off, w * sizeof(TerraRawIntegrationResult),
+                                  w * sizeof(TerraRawIntegrationResult), slice_rows, cudaMemcpyDeviceToHost, so));
+        TB_CUDA(cudaMemcpy2DAsync(fb->pixels + (y + slice_row0) * fb->width + x, fb->width * sizeof(TerraFloat3),
+                                  d->d_pixels + d->stage_off * 3, w * sizeof(TerraFloat3), w * sizeof(TerraFloat3), slice_rows, cudaMemcpyDeviceToHost, so));
+        d->stats.d2h_bytes += slice_rows * w * (sizeof(TerraRawIntegrationResult) + sizeof(TerraFloat3));
+        d->stage_off += slice_rows * w;
     }
-    // the other devices read this device's accumulator: the next call must not reset it before they are done
-    TB_CUDA(cudaEventRecord(d->ev_band, st));
+    if (last) {
+        // the other devices read this device's accumulator: the next call must not reset it before they are done
+        TB_CUDA(cudaEventRecord(d->ev_band, so));
+        TB_CUDA(cudaStreamWaitEvent(d->stream, d->ev_band, 0));      // the call ends on the compute stream (tb_finish_call)
+    }
 }
 
 extern "C" void tb_device_partial_wait(TbDevice* d, TbDevice* const* devs, int n_dev) {
@@ -1961,16 +2003,7 @@ extern "C" void tb_device_trace_resident(TbDevice* d, size_t n, const void* d_o,
 // (terra_b200_host_alloc); with pageable memory the driver stages every copy and the calls serialise, the
 // results are the same. TERRA_B200_IO_CHUNK sets the chunk (rays).
 static void tb_pipe_reserve(TbDevice* d, size_t chunk) {
-    if (!d->st_in) {
-        TB_CUDA(cudaStreamCreateWithFlags(&d->st_in, cudaStreamNonBlocking));
-        TB_CUDA(cudaStreamCreateWithFlags(&d->st_out, cudaStreamNonBlocking));
-        for (int k = 0; k < 2; ++k) {
-            TB_CUDA(cudaEventCreateWithFlags(&d->ev_in[k], cudaEventDisableTiming));
-            TB_CUDA(cudaEventCreateWithFlags(&d->ev_pack[k], cudaEventDisableTiming));
-            TB_CUDA(cudaEventCreateWithFlags(&d->ev_trace[k], cudaEventDisableTiming));
-            TB_CUDA(cudaEventCreateWithFlags(&d->ev_out[k], cudaEventDisableTiming));
-        }
-    }
+    tb_pipe_streams(d);
     if (chunk <= d->pipe_capacity) return;
     for (int k = 0; k < 2; ++k) {
         tb_free(d->d_pipe_o3[k]); tb_free(d->d_pipe_d3[k]); tb_free(d->d_pipe_hit[k]);
