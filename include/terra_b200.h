@@ -312,9 +312,10 @@ void terra_b200_set_device(int device);              /* before terra_scene_commi
  * returns row band g of it, summing the band over all GPUs' accumulators through peer-mapped memory inside the
  * accumulate / tonemap kernel. Smaller calls, and every other entry point, run on the first device. Sample ranges
  * use the same counter-based random numbers as one GPU; the per-pixel float sum re-associates.
- * A split call of at least 2 x chunk_paths (pixel, sample) pairs per GPU (default 16M) goes through as two row chunks,
- * the first seven eighths of the region and the rest: the framebuffer traffic of the first chunk (PCIe in and out,
- * NVLink reduce) runs beside the rendering of the second. The image does not depend on the chunking, bit for bit.
+ * Optional (off by default: it measured 1 % slower on the 1080p benchmark frame at 2 and at 8 GPUs): a split call of at
+ * least 2 x chunk_paths (pixel, sample) pairs per GPU goes through as two row chunks, the first seven eighths of the
+ * region and the rest, and the framebuffer traffic of the first chunk (PCIe in and out, NVLink reduce) runs beside the
+ * rendering of the second. The image does not depend on the chunking, bit for bit.
  * One host thread per GPU issues that GPU's work. */
 void terra_b200_scene_set_devices(HTerraScene scene, const int* device_ids, int count);
 int  terra_b200_scene_device_count(HTerraScene scene);

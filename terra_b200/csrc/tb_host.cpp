@@ -386,7 +386,7 @@ extern "C" HTerraScene terra_scene_create(void) {                               
     s->device_ids = default_device_ids();
     s->peers_ok = false;
     s->fan = NULL;
-    s->fanout_chunk_paths = (size_t)1 << 24;
+    s->fanout_chunk_paths = (size_t)1 << 40;            // off: see terra_render
     if (const char* e = getenv("TERRA_B200_FANOUT_CHUNK")) s->fanout_chunk_paths = (size_t)strtoull(e, NULL, 10);
     if (s->fanout_chunk_paths < 1) s->fanout_chunk_paths = 1;
     s->fanout_min_paths = (size_t)1 << 24;
@@ -719,8 +719,10 @@ extern "C" void terra_render(const TerraCamera* camera, HTerraScene h, const Ter
         //      A large region goes through as TWO row chunks, the first seven eighths and the rest: the framebuffer
         //      traffic of the first (PCIe in and out, NVLink reduce) runs beside the rendering of the second, and only
         //      an eighth of it is left exposed at the end. Device g finalises and returns slice g of each chunk.
-        //      (Measured on C2, r2o: a chunk costs ~0.2 ms of launch tails, so equal chunks of 16M paths lost more
-        //      than they hid — 50.5 against 49.0 ms at N = 2.)
+        //      OFF by default (terra_b200_set_fanout_chunk_paths / TERRA_B200_FANOUT_CHUNK turn it on). Measured on C2,
+        //      r2o: a chunk costs ~0.2 ms of launch tails and short last-bounce waves, which is what the hidden
+        //      transfers are worth — two chunks 49.02 against 48.91 ms at N = 2, 13.36 against 13.20 ms at N = 8
+        //      (equal chunks of 16M paths: 50.5 ms at N = 2).
         std::vector<size_t> base(n_dev + 1);
         for (size_t g = 0; g <= n_dev; ++g) base[g] = spp * g / n_dev;
         std::vector<size_t> crow;
