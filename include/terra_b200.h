@@ -418,6 +418,19 @@ void terra_b200_trace_rays(HTerraScene scene, size_t n, const float* origins, co
 /* Device buffers: float4 per ray (xyz used), caller's stream (cudaStream_t as void*). */
 void terra_b200_trace_rays_device(HTerraScene scene, size_t n, const void* d_origins, const void* d_directions,
                                   void* d_hits_out, void* stream);
+/* No counterpart in the reference: added for callers that cannot allocate device
+ * memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). Closest hits of a DEVICE
+ * batch of packed rays — n x 3 floats each for origins and directions, the layout terra_b200_trace_rays takes from the
+ * host — into n TerraB200Hit on the device, on the caller's stream (NULL: the library's); returns when the hits are
+ * final, like terra_b200_trace_rays_device, and gives the same hits bit for bit. The call allocates nothing: the
+ * float4 ray records and the fetch cursor the kernels need live in a file-scope device array of
+ * 256 + 32 x TERRA_B200_NOALLOC_MAX_RAYS bytes (8 MB) that every GPU holds from the moment the library is loaded.
+ * Returns 0, or -1 (and logs, writes nothing) when n exceeds TERRA_B200_NOALLOC_MAX_RAYS. Runs on the scene's first
+ * device. All calls of a process share the one array per GPU: it keeps the previous call's contents (each call clears
+ * what must start at zero), and two calls that overlap on the same GPU — other scenes, other streams — race. */
+#define TERRA_B200_NOALLOC_MAX_RAYS 262144
+int  terra_b200_trace_rays_packed_noalloc(HTerraScene scene, size_t n, const float* d_origins_xyz, const float* d_directions_xyz,
+                                          void* d_hits_out, void* stream);
 /* Primary camera rays at subpixel_jitter = 0, one per pixel, row-major. */
 void terra_b200_primary_hits(const TerraCamera* camera, HTerraScene scene, size_t width, size_t height,
                              TerraB200Hit* hits_out);

@@ -198,6 +198,7 @@ class TerraLib:
             sig("terra_b200_set_bvh_mode", None, C.c_int)
             sig("terra_b200_trace_rays", None, _vp, _sz, _vp, _vp, _vp)
             sig("terra_b200_trace_rays_device", None, _vp, _sz, _vp, _vp, _vp, _vp)
+            sig("terra_b200_trace_rays_packed_noalloc", C.c_int, _vp, _sz, _vp, _vp, _vp, _vp)
             sig("terra_b200_primary_hits", None, C.POINTER(Camera), _vp, _sz, _sz, _vp)
             sig("terra_b200_render_device", None, C.POINTER(Camera), _vp, _sz, _sz, _sz, _sz, _sz, _sz, _sz, _sz, _vp, _vp)
             sig("terra_b200_resolve_device", None, _vp, _sz, _sz, _vp, _vp, _vp)

@@ -932,6 +932,11 @@ extern "C" void terra_b200_trace_rays_device(HTerraScene h, size_t n, const void
     std::lock_guard<std::mutex> guard(s->lock);
     tb_device_trace_resident(s->dev, n, d_o, d_d, d_hits, stream);
 }
+extern "C" int terra_b200_trace_rays_packed_noalloc(HTerraScene h, size_t n, const float* d_o3, const float* d_d3, void* d_hits, void* stream) {
+    TbScene* s = committed(h, "terra_b200_trace_rays_packed_noalloc");
+    std::lock_guard<std::mutex> guard(s->lock);
+    return tb_device_trace_packed_noalloc(s->dev, n, d_o3, d_d3, d_hits, stream);
+}
 extern "C" void terra_b200_primary_hits(const TerraCamera* camera, HTerraScene h, size_t width, size_t height, TerraB200Hit* hits_out) {
     TbScene* s = committed(h, "terra_b200_primary_hits");
     std::lock_guard<std::mutex> guard(s->lock);

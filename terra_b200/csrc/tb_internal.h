@@ -147,6 +147,7 @@ void      tb_device_trace_resident(TbDevice* dev, size_t n, const void* d_o, con
 void      tb_device_primary_hits(TbDevice* dev, const TbCameraFrame* cam, size_t w, size_t h, TerraB200Hit* out);
 void      tb_device_bsdf_kat(TbDevice* dev, size_t object_idx, size_t n, const float* e123, const float* wo,
                              const float* normal, float* out);
+int       tb_device_trace_packed_noalloc(TbDevice* dev, size_t n, const float* d_o3, const float* d_d3, void* d_hits, void* stream);
 void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_round_stats(TbDevice* dev, uint64_t* out10);
 void      tb_device_reset_stats(TbDevice* dev);

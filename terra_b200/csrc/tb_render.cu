@@ -191,6 +191,7 @@ struct TbDevice {
     bool         capturing;
     int          env_mode;                  // what terra_b200_set_env_lit asked for (0 / 1 / 2), re-applied at every commit
     TbCallParams *d_call, *h_call;
+    unsigned char* noalloc_scratch;         // device address of g_noalloc_scratch ON THIS DEVICE (cudaGetSymbolAddress in tb_device_create)
 };
 
 static void tb_free(void* p) { if (p) TB_CUDA(cudaFree(p)); }
@@ -244,6 +245,22 @@ static void tb_wave_reserve(TbWave* w, size_t capacity) {
     w->auxq = tb_alloc<int>(capacity * 3);
 }
 
+// Scratch of terra_b200_trace_rays_packed_noalloc: a fetch cursor (first 256 bytes) and the float4 origins / directions of up
+// to TB_NOALLOC_MAX_RAYS rays. File-scope device memory: every GPU that loads the library holds these 8 MB until the
+// process exits. ONE array per device shared by every call: it keeps the last call's contents (the cursor is cleared by
+// every call, the ray slots are overwritten), and two calls that overlap on one GPU race.
+#define TB_NOALLOC_MAX_RAYS 262144          /* = TERRA_B200_NOALLOC_MAX_RAYS, include/terra_b200.h */
+#define TB_NOALLOC_HEADER   256
+static __device__ __align__(256) unsigned char g_noalloc_scratch[TB_NOALLOC_HEADER + (size_t)TB_NOALLOC_MAX_RAYS * 32];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes
+// from cudaGetSymbolAddress, per device, with that device current.
+static unsigned char* tb_noalloc_scratch_address() {
+    unsigned char* p = NULL;
+    TB_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    return p;
+}
+
 extern "C" TbDevice* tb_device_create(int device_index) {
     int n = tb_cuda_device_count();
     if (n <= 0) {
@@ -259,6 +276,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     TB_CUDA(cudaGetDeviceProperties(&prop, device_index));
     d->sm_count = prop.multiProcessorCount;
     TB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    d->noalloc_scratch = tb_noalloc_scratch_address();      // this device is current: the symbol resolves to ITS copy of the array
     memset(&d->sc, 0, sizeof d->sc);
     d->d_nodes = d->d_tris = d->d_props = NULL;
     d->d_qnodes = NULL;
@@ -732,6 +750,16 @@ __global__ void __launch_bounds__(256) k_primary_rays(TbCameraFrame cam, int w, 
 }
 
 __global__ void __launch_bounds__(256) k_pack_rays(size_t n, const float* o3, const float* d3, float4* ray_o, float4* ray_d) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        ray_o[i] = make_float4(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2], 0.f);
+        ray_d[i] = make_float4(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2], 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pack_rays_noalloc(size_t n, const float* __restrict__ o3, const float* __restrict__ d3) {
+    float4* ray_o = (float4*)(g_noalloc_scratch + TB_NOALLOC_HEADER);
+    float4* ray_d = ray_o + TB_NOALLOC_MAX_RAYS;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *(int*)g_noalloc_scratch = 0;      // the trace kernel's fetch cursor must start at zero
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         ray_o[i] = make_float4(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2], 0.f);
         ray_d[i] = make_float4(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2], 0.f);
@@ -1992,6 +2020,40 @@ extern "C" void tb_device_trace_resident(TbDevice* d, size_t n, const void* d_o,
         tb_trace_generic(d, st, m, (const float4*)d_o + at, (const float4*)d_d + at, (float4*)d_hits + at);
     }
     tb_finish_call(d, st, false);
+}
+
+// terra_b200_trace_rays_packed_noalloc: closest hits of a DEVICE batch of packed xyz rays (the layout terra_b200_trace_rays
+// takes from the host) without a single allocation — for callers that cannot allocate (CUDA graph capture, serving loops).
+// k_pack_rays_noalloc is k_pack_rays writing into g_noalloc_scratch (it names the array directly: device code may) and
+// clearing the fetch cursor the trace kernel starts from; the trace kernel gets the array through the address
+// tb_device_create took with cudaGetSymbolAddress. No cudaMalloc / cudaFree / event creation on this path: it does not
+// go through tb_launch_trace (per-launch timing events) and touches none of the growable buffers.
+extern "C" int tb_device_trace_packed_noalloc(TbDevice* d, size_t n, const float* d_o3, const float* d_d3, void* d_hits, void* stream) {
+    if (n > TB_NOALLOC_MAX_RAYS) {
+        terra_log("terra_b200: terra_b200_trace_rays_packed_noalloc: %zu rays exceed the static scratch (TERRA_B200_NOALLOC_MAX_RAYS = %d); "
+                  "split the batch or use terra_b200_trace_rays_device\n", n, TB_NOALLOC_MAX_RAYS);
+        return -1;
+    }
+    if (n == 0) return 0;
+    TB_CUDA(cudaSetDevice(d->index));
+    cudaStream_t st = tb_call_stream(d, stream);
+    float4* ray_o = (float4*)(d->noalloc_scratch + TB_NOALLOC_HEADER);
+    float4* ray_d = ray_o + TB_NOALLOC_MAX_RAYS;
+    int grid = (int)((n + 255) / 256);
+    if (grid > d->sm_count * 8) grid = d->sm_count * 8;
+    k_pack_rays_noalloc<<<grid, 256, 0, st>>>(n, d_o3, d_d3);
+    TbTraceArgs ta;
+    memset(&ta, 0, sizeof ta);
+    ta.nodes = d->sc.nodes; ta.tris = d->sc.tris;
+    ta.ray_o = ray_o; ta.ray_d = ray_d;
+    ta.count = (int)n; ta.cursor = (int*)d->noalloc_scratch;
+    ta.hit_out = (float4*)d_hits;
+    ta.emit_prim = 1;
+    ta.tri_min = d->tri_min; ta.refetch_below = d->refetch_below;
+    tb_launch_trace_kernel<false>(d, st, ta, tb_trace_kind(d, false), NULL);
+    d->stats.kernel_launches += 2;
+    tb_finish_call(d, st, false);
+    return 0;
 }
 
 // Host-buffer ray batches (terra_b200_trace_rays). The batch moves through three streams in chunks:
