@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")/terra_b200/csrc"
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false -std=c++17 \
-     -Xcompiler -fPIC,-O2,-Wall ${TB_NVCC_EXTRA} -shared -o ../libterra_b200.so tb_render.cu tb_lbvh.cu tb_host.cpp tb_bvh.cpp tb_bvh8.cpp
+     -Xcompiler -fPIC,-O2,-Wall ${TB_NVCC_EXTRA} -shared -o ../libterra_b200.so tb_render.cu tb_lbvh.cu tb_host.cpp tb_bvh.cpp
 # headless front-end: the same C source against the product and, where the reference was
 # compiled (oracle/_ref), against the unmodified reference — Terra API only.
 cd ../..

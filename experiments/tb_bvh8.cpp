@@ -32,7 +32,15 @@
 #include <algorithm>
 #include <vector>
 
-#include "tb_bvh.h"
+#include "tb_bvh.h"    // terra_b200/csrc
+
+// 8-wide tree derived from the binary one (tb_bvh8.cpp): 24 words per node.
+struct TbWideBvh {
+    std::vector<uint32_t> nodes;
+    std::vector<int32_t>  leaf_rank;     // [binary node * 2 + child] -> rank, for tb_bvh_flatten
+    int                   depth;         // wide nodes on the deepest root->leaf path
+};
+void tb_bvh8_build(const std::vector<TbHostNode>& nodes, TbWideBvh* out);
 
 namespace {
 

@@ -46,9 +46,13 @@ l1tex__data_pipe_lsu_wavefronts.avg l1tex__data_pipe_lsu_wavefronts_mem_shared.a
 l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum smsp__inst_executed_pipe_alu.sum smsp__inst_executed_pipe_fma.sum smsp__inst_executed_pipe_lsu.sum""".split()
 for rep in reps:
     p = REPO / "gpurun_out" / f"{tag}_{rep}.ncu-rep"
-    if not p.exists():
+    c = REPO / "gpurun_out" / f"{tag}_{rep}_raw.csv"          # made on the GPU box when the report is too large to bring back
+    if c.exists():
+        raw = c.read_text()
+    elif p.exists():
+        raw = subprocess.run(["ncu", "-i", str(p), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    else:
         continue
-    raw = subprocess.run(["ncu", "-i", str(p), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
     with open(out / f"{tag}_{rep}_metrics.md", "w") as f:

@@ -24,14 +24,7 @@ void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbH
 // Conventional binned-SAH tree over x, y and z in the same node format (see tb_bvh.cpp).
 void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
 // leaf_rank: NULL = rank by the reference traversal's leaf visiting order; else the rank of child c of node n at
-// [n * 2 + c] (the wide tree's order, tb_bvh8.cpp).
+// [n * 2 + c] (any fixed order gives the same hits outside exact-t ties).
 void tb_bvh_flatten(const std::vector<TbHostNode>& nodes, const TerraObject* objects, int objects_count, TbFlatBvh* out,
                     const std::vector<int32_t>* leaf_rank = NULL);
 
-// 8-wide tree derived from the binary one (tb_bvh8.cpp): 24 words per node.
-struct TbWideBvh {
-    std::vector<uint32_t> nodes;
-    std::vector<int32_t>  leaf_rank;     // [binary node * 2 + child] -> rank, for tb_bvh_flatten
-    int                   depth;         // wide nodes on the deepest root->leaf path
-};
-void tb_bvh8_build(const std::vector<TbHostNode>& nodes, TbWideBvh* out);
