@@ -403,6 +403,12 @@ float       terra_b200_refit(HTerraScene scene);
  * TERRA_B200_GRAPH_PATHS; 0 = never). Per-kernel trace timings in TerraB200Stats are not taken on replayed calls. */
 void        terra_b200_set_graph_paths(HTerraScene scene, size_t max_paths);
 
+/* Host-only (tests): the 4-wide tree terra_scene_commit derives for the incoherent-ray kernel from the tree of `mode`
+ * (16 words per node: 4 child boxes x 3 words lo | hi << 16, 4 refs), where each slot's box comes from
+ * (binary node * 2 + child, -1 = empty) and the quantised binary nodes themselves (8 words each). Returns the wide
+ * node count; writes at most `cap` wide nodes. */
+int terra_b200_build_host_bvh4(HTerraScene scene, int mode, uint32_t* q4nodes_out, int32_t* src_out, uint32_t* qnodes_out,
+                               int cap, int* stack_bound_out);
 /* Page-locked host memory for large ray batches (and anything else handed to the entry points below):
  * copies from / to it run at PCIe speed and overlap the kernels. NULL when no CUDA device is visible.
  * Framebuffers made by terra_framebuffer_create are page-locked already. */

@@ -20,14 +20,18 @@ REPO = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(REPO))
 
 C3_VARIANTS = [
-    ("v6 (default)", dict()),
-    ("v6 refetch 26", dict(TERRA_B200_REFETCH="26")),
-    ("v6 stack 16 rows + spill", dict(TERRA_B200_STACK_SMEM="16")),
-    ("v6 tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
+    ("v7 (default: 4-wide tree, 16 rows + spill)", dict()),
+    ("v6 (binary tree)", dict(TERRA_B200_INCOHERENT="v6")),
+    ("v7 stack 12 rows", dict(TERRA_B200_STACK_SMEM="12")),
+    ("v7 stack 24 rows", dict(TERRA_B200_STACK_SMEM="24")),
+    ("v7 refetch 18", dict(TERRA_B200_REFETCH="18")),
+    ("v7 refetch 26", dict(TERRA_B200_REFETCH="26")),
+    ("v7 tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
+    ("v7 tri_min 12", dict(TERRA_B200_TRI_MIN="12")),
 ]
 C2_VARIANTS = [
-    ("default (v6 + fused raygen)", dict()),
-    ("k_raygen instead of fused generation", dict(TERRA_B200_FUSED_RAYGEN="0")),
+    ("default (v7 + fused raygen)", dict()),
+    ("v6 (binary tree)", dict(TERRA_B200_INCOHERENT="v6")),
 ]
 SWITCHES = ["TERRA_B200_INCOHERENT", "TERRA_B200_COHERENT", "TERRA_B200_V6_OPT", "TERRA_B200_STACK_SMEM", "TERRA_B200_TRI_MIN",
             "TERRA_B200_REFETCH", "TERRA_B200_FUSED_RAYGEN", "TERRA_B200_NODE_ORDER"]
@@ -99,7 +103,7 @@ def main():
                 want = got
             # work counters on a 1M-ray sample
             lib.terra_b200_reset_stats(s.h)
-            lib.terra_b200_set_counting(s.h, 1)
+            lib.terra_b200_set_counting(s.h, 2)          # the kernel's own fetches (1 = the canonical binary walk)
             m = min(n, 1 << 20)
             lib.terra_b200_trace_rays_device(s.h, m, C.c_void_p(o4.data_ptr()), C.c_void_p(d4.data_ptr()), C.c_void_p(hits.data_ptr()), sp)
             torch.cuda.synchronize()

@@ -50,7 +50,7 @@ def main():
     d4[:, :3] = d / d.norm(dim=1, keepdim=True)
     hits = torch.empty(n, 4, device="cuda")
     s, _ = scenes.terrain(lib, n_tris=args.tris, extent=extent, lights=False)
-    lib.terra_b200_set_counting(s.h, 1)
+    lib.terra_b200_set_counting(s.h, 2)
     lib.terra_b200_reset_stats(s.h)
     lib.terra_b200_trace_rays_device(s.h, n, C.c_void_p(o4.data_ptr()), C.c_void_p(d4.data_ptr()), C.c_void_p(hits.data_ptr()), None)
     torch.cuda.synchronize()
@@ -59,7 +59,7 @@ def main():
     # C2 frame: bounce rays only (the camera rays run the packet kernel, which keeps no such counters)
     w, h, spp = 1920, 1080, 4
     s, cam = scenes.sphere_field(lib, spp=spp, bounces=4, ggx=True)
-    lib.terra_b200_set_counting(s.h, 1)
+    lib.terra_b200_set_counting(s.h, 2)
     lib.terra_b200_reset_stats(s.h)
     res = torch.zeros(w * h * 4, dtype=torch.float32, device="cuda")
     lib.terra_b200_render_device(C.byref(cam), s.h, w, h, 0, 0, w, h, 0, spp, C.c_void_p(res.data_ptr()), None)

@@ -196,6 +196,7 @@ class TerraLib:
             sig("terra_b200_bvh_stack_bound", C.c_int, _vp)
             sig("terra_b200_build_host_bvh", C.c_int, _vp, C.c_int, _vp, _vp)
             sig("terra_b200_set_bvh_mode", None, C.c_int)
+            sig("terra_b200_build_host_bvh4", C.c_int, _vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp)
             sig("terra_b200_trace_rays", None, _vp, _sz, _vp, _vp, _vp)
             sig("terra_b200_trace_rays_device", None, _vp, _sz, _vp, _vp, _vp, _vp)
             sig("terra_b200_trace_rays_packed_noalloc", C.c_int, _vp, _sz, _vp, _vp, _vp, _vp)

@@ -620,3 +620,68 @@ void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out) {
     }
     });
 }
+
+// ---- 4-wide collapse (k_trace_v7). A wide node starts as the two children of a binary node and, while it has fewer
+// than four, replaces its inner child of largest surface area by that child's two children (greedy surface-area collapse).
+// Wide nodes are numbered breadth-first (a child's index is larger than its parent's).
+void tb_bvh4_build(const TbFlatBvh& flat, const TbQuantBvh& quant, TbQuadBvh* out) {
+    const size_t n_bin = flat.nodes.size() / 16;
+    out->nodes.clear(); out->src.clear(); out->stack_bound = 0;
+    if (n_bin == 0) return;
+    out->nodes.reserve(n_bin / 2 * 16);
+    out->src.reserve(n_bin / 2 * 4);
+    std::vector<int32_t> todo;                 // wide node i stands for binary node todo[i]
+    todo.reserve(n_bin / 2);
+    todo.push_back(0);
+    auto ref_of = [&](int32_t e) { int32_t r; memcpy(&r, &flat.nodes[(size_t)(e >> 1) * 16 + 12 + (e & 1)], 4); return r; };
+    auto area_of = [&](int32_t e) {
+        const float* q = &flat.nodes[(size_t)(e >> 1) * 16 + 6 * (e & 1)];
+        const double dx = (double)q[3] - q[0], dy = (double)q[4] - q[1], dz = (double)q[5] - q[2];
+        return dx * dy + dy * dz + dz * dx;
+    };
+    for (size_t w = 0; w < todo.size(); ++w) {
+        int32_t ch[4];                         // binary node * 2 + child
+        int cnt = 2;
+        ch[0] = todo[w] * 2; ch[1] = todo[w] * 2 + 1;
+        while (cnt < 4) {
+            int pick = -1; double best = -1.0;
+            for (int i = 0; i < cnt; ++i) if (ref_of(ch[i]) >= 0) { const double a = area_of(ch[i]); if (a > best) { best = a; pick = i; } }
+            if (pick < 0) break;
+            const int32_t b = ref_of(ch[pick]);
+            ch[pick] = b * 2;
+            ch[cnt++] = b * 2 + 1;
+        }
+        uint32_t wd[16];
+        int32_t sr[4];
+        for (int j = 0; j < 4; ++j) {
+            if (j >= cnt) {                    // empty slot: lo = 0xffff, hi = 0 on every axis -> no ray enters; the ref is never read
+                wd[3 * j] = wd[3 * j + 1] = wd[3 * j + 2] = 0x0000ffffu;
+                wd[12 + j] = 0x80000001u;      // TB_REF_POP
+                sr[j] = -1;
+                continue;
+            }
+            const uint32_t* q = &quant.nodes[(size_t)(ch[j] >> 1) * 8 + 3 * (ch[j] & 1)];
+            wd[3 * j] = q[0]; wd[3 * j + 1] = q[1]; wd[3 * j + 2] = q[2];
+            const int32_t r = ref_of(ch[j]);
+            if (r >= 0) { wd[12 + j] = (uint32_t)todo.size(); todo.push_back(r); }
+            else wd[12 + j] = (uint32_t)r;
+            sr[j] = ch[j];
+        }
+        out->nodes.insert(out->nodes.end(), wd, wd + 16);
+        out->src.insert(out->src.end(), sr, sr + 4);
+    }
+    // stack bound, children before parents
+    const size_t n = todo.size();
+    std::vector<int32_t> bound(n, 0);
+    for (size_t i = n; i-- > 0;) {
+        int cnt = 0, deepest = 0;
+        for (int j = 0; j < 4; ++j) {
+            if (out->src[i * 4 + j] < 0) continue;
+            ++cnt;
+            const int32_t r = (int32_t)out->nodes[i * 16 + 12 + j];
+            if (r >= 0 && bound[(size_t)r] > deepest) deepest = bound[(size_t)r];
+        }
+        bound[i] = cnt - 1 + deepest;
+    }
+    out->stack_bound = bound[0] + 1;
+}

@@ -20,6 +20,17 @@ struct TbQuantBvh {
 };
 void tb_bvh_quantize(const TbFlatBvh& flat, TbQuantBvh* out);
 
+// 4-wide tree of the incoherent-ray kernel k_trace_v7 (tb_trace_v7.cuh), derived from the binary tree: same child boxes
+// (the quantised words are COPIED from the binary nodes, so every box a ray is tested against is one it would also meet
+// in the binary walk), same leaves, same ranks. 16 words per node: word 3 c + k = lo | hi << 16 of child c on axis k
+// (c = 0..3), words 12..15 = child refs (>= 0: wide node index, < 0: leaf ~rank; empty slot: an inverted box).
+struct TbQuadBvh {
+    std::vector<uint32_t> nodes;              // 16 words per node
+    std::vector<int32_t>  src;                // 4 per node: binary node * 2 + child the slot's box comes from, or -1 (refit re-copies them)
+    int                   stack_bound;        // worst-case stack entries of a near-first walk: sum over a path of (children - 1)
+};
+void tb_bvh4_build(const TbFlatBvh& flat, const TbQuantBvh& quant, TbQuadBvh* out);
+
 void tb_bvh_build(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);
 // Conventional binned-SAH tree over x, y and z in the same node format (see tb_bvh.cpp).
 void tb_bvh_build_sah3(const TerraObject* objects, int objects_count, std::vector<TbHostNode>& nodes);

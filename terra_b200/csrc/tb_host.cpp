@@ -610,6 +610,12 @@ extern "C" void terra_scene_commit(HTerraScene h) {                             
             memcpy(up.grid_lo, quant.grid_lo, sizeof up.grid_lo);
             memcpy(up.grid_cell, quant.grid_cell, sizeof up.grid_cell);
         }
+        TbQuadBvh quad;
+        if (!up.exact_boxes && s->nodes.size() > 0) {
+            tb_bvh4_build(flat, quant, &quad);
+            up.q4nodes = quad.nodes.data(); up.q4src = quad.src.data();
+            up.n_q4 = quad.src.size() / 4; up.stack_bound4 = quad.stack_bound;
+        }
         s->commit_ms[2] = ms_since(t0);
         t0 = Clock::now();
         tb_device_upload_geometry(s->dev, &up);
@@ -918,6 +924,28 @@ extern "C" int terra_b200_build_host_bvh(HTerraScene h, int mode, float* flat_no
     if (flat_nodes_out) memcpy(flat_nodes_out, flat.nodes.data(), flat.nodes.size() * sizeof(float));
     if (flat_tris_out) memcpy(flat_tris_out, flat.tris.data(), flat.tris.size() * sizeof(float));
     return (int)s->nodes.size();
+}
+
+// Host-only: the 4-wide tree terra_scene_commit derives for k_trace_v7 (tb_bvh4_build) from the tree built with `mode`,
+// with the quantised binary nodes it copies its boxes from. Returns the number of wide nodes; fills at most `cap` of them.
+extern "C" int terra_b200_build_host_bvh4(HTerraScene h, int mode, uint32_t* q4nodes_out, int32_t* src_out, uint32_t* qnodes_out, int cap, int* stack_bound_out) {
+    TbScene* s = (TbScene*)h;
+    std::lock_guard<std::mutex> guard(s->lock);
+    build_bvh(s, mode);
+    s->has_bvh = false;
+    TbFlatBvh flat;
+    tb_bvh_flatten(s->nodes, s->objects, (int)s->objects_pop, &flat);
+    TbQuantBvh quant;
+    tb_bvh_quantize(flat, &quant);
+    TbQuadBvh quad;
+    tb_bvh4_build(flat, quant, &quad);
+    const int n = (int)(quad.src.size() / 4);
+    const int m = n < cap ? n : cap;
+    if (q4nodes_out) memcpy(q4nodes_out, quad.nodes.data(), (size_t)m * 64);
+    if (src_out) memcpy(src_out, quad.src.data(), (size_t)m * 16);
+    if (qnodes_out) memcpy(qnodes_out, quant.nodes.data(), quant.nodes.size() * 4);
+    if (stack_bound_out) *stack_bound_out = quad.stack_bound;
+    return n;
 }
 
 extern "C" void* terra_b200_host_alloc(size_t bytes) { return tb_host_alloc_pinned(bytes ? bytes : 1); }

@@ -115,6 +115,10 @@ struct TbFlatScene {          // host staging of everything the device needs
     TbDevAttr            env;
     int                  stack_bound;
     const uint32_t*      qnodes;          // 8 words per node, or NULL (reference tree: float boxes only)
+    const uint32_t*      q4nodes;         // 4-wide tree (tb_bvh4_build): 16 words per node, or NULL
+    const int32_t*       q4src;           // 4 per wide node
+    size_t               n_q4;
+    int                  stack_bound4;
     float                grid_lo[3], grid_cell[3];
     int                  exact_boxes;     // 1: reference tree -> reference box arithmetic in k_trace (tb_trace.cuh)
 };

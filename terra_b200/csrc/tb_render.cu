@@ -61,6 +61,10 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_QUEUE_SENTINEL     0x7fffffff
 #define TB_K_V6_ID            2            // = TB_K_V6 / TB_K_PACKET below (the device is created before the enum is seen)
 #define TB_K_PACKET_ID        3
+#define TB_K_V7_ID            4
+#define TB_V7_MIN_MB          100          // k_trace_v7 by default for scenes whose nodes + triangles exceed this (L2: 126 MB)
+#define TB_V7_SMEM_DEPTH      16           // k_trace_v7: rows of the shared stack ...
+#define TB_V7_LOCAL           48           // ... and entries beyond them in local memory; deeper 4-wide trees are not uploaded (the scene runs k_trace_v6)
 
 // ------------------------------------------------------------------------------------ RNG
 // Counter-based: splitmix64 over (path key, dimension). The reference draws BSDF/RR numbers from
@@ -133,6 +137,10 @@ struct TbDevice {
     // owned device memory
     float4 *d_nodes, *d_tris, *d_props;
     uint4*  d_qnodes;
+    uint4*  d_q4nodes;         // 4-wide tree of k_trace_v7 (4 x uint4 per node) and, for refits, where each slot's box comes from
+    int*    d_q4src;
+    size_t  n_q4;
+    int     stack_bound4;
     float   grid_lo[3], grid_cell[3];
     TbDevMaterial* d_mats;
     TbDevTexture*  d_texs;
@@ -179,6 +187,7 @@ struct TbDevice {
     int          fused_raygen;      // 1: camera rays are generated inside the packet kernel (no k_raygen, no ray arrays for bounce 0)
     int          coherent_kind;     // TB_K_* used for camera-ray launches when trace_kind is auto
     int          incoherent_kind;   // TB_K_* used for incoherent launches when trace_kind is auto
+    size_t       v7_min_bytes;      // auto: k_trace_v7 when quantised nodes + triangle records are at least this large
     int          warp_samples; // at most this many samples of one pixel share a warp (TERRA_B200_WARP_SAMPLES, default 32)
     int          tile_pixels;  // 1: waves walk the region in 8x4 pixel tiles (TERRA_B200_TILE=0 turns it off)
     int          tri_min, refetch_below;
@@ -280,6 +289,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
     memset(&d->sc, 0, sizeof d->sc);
     d->d_nodes = d->d_tris = d->d_props = NULL;
     d->d_qnodes = NULL;
+    d->d_q4nodes = NULL; d->d_q4src = NULL; d->n_q4 = 0; d->stack_bound4 = 0;
     d->d_mats = NULL; d->d_texs = NULL; d->d_lights = NULL; d->d_light_area = NULL; d->d_light_rank = NULL;
     d->stack_bound = 0;
     memset(&d->wave, 0, sizeof d->wave);
@@ -303,14 +313,16 @@ extern "C" TbDevice* tb_device_create(int device_index) {
         // A/B switches: TERRA_B200_TRACE forces one kernel for every launch; TERRA_B200_INCOHERENT / TERRA_B200_COHERENT
         // choose it for bounce / visibility / API rays and for camera rays. walk = per-ray while-while (the work
         // counters' kernel), v6 = rounds kernel (tb_trace_v6.cuh), packet = one warp per 32-ray packet.
-        static const char* names[] = { "auto", "walk", "v6", "packet" };
+        // v7 = the rounds kernel on the 4-wide tree (tb_trace_v7.cuh); a scene without that tree (reference mode) runs v6.
+        static const char* names[] = { "auto", "walk", "v6", "packet", "v7" };
         auto kind_of = [&](const char* env, int dflt) {
             const char* e = getenv(env);
-            for (int k = 0; e && k < 4; ++k) if (strcmp(e, names[k]) == 0) return k;
+            for (int k = 0; e && k < 5; ++k) if (strcmp(e, names[k]) == 0) return k;
             return dflt;
         };
         d->trace_kind = kind_of("TERRA_B200_TRACE", 0);
-        d->incoherent_kind = kind_of("TERRA_B200_INCOHERENT", TB_K_V6_ID);
+        d->incoherent_kind = kind_of("TERRA_B200_INCOHERENT", 0);
+        const char* wm = getenv("TERRA_B200_V7_MIN_MB"); d->v7_min_bytes = (size_t)(wm ? atof(wm) : TB_V7_MIN_MB) << 20;
         d->coherent_kind = kind_of("TERRA_B200_COHERENT", TB_K_PACKET_ID);
         const char* t = getenv("TERRA_B200_TRI_MIN"); d->tri_min = t ? atoi(t) : TB_TRI_MIN;
         const char* tp = getenv("TERRA_B200_TILE"); d->tile_pixels = tp ? atoi(tp) : 1;
@@ -332,6 +344,7 @@ extern "C" TbDevice* tb_device_create(int device_index) {
 static void tb_scene_free(TbDevice* d) {
     tb_free(d->d_nodes); tb_free(d->d_tris); tb_free(d->d_props); tb_free(d->d_mats); tb_free(d->d_texs);
     tb_free(d->d_qnodes); d->d_qnodes = NULL;
+    tb_free(d->d_q4nodes); tb_free(d->d_q4src); d->d_q4nodes = NULL; d->d_q4src = NULL; d->n_q4 = 0;
     tb_free(d->d_lights); tb_free(d->d_light_area); tb_free(d->d_light_rank);
     for (void* p : d->tex_pixels) tb_free(p);
     d->tex_pixels.clear();
@@ -396,6 +409,13 @@ extern "C" void tb_device_upload_geometry(TbDevice* d, const TbFlatScene* f) {
         memcpy(d->grid_cell, f->grid_cell, sizeof d->grid_cell);
     }
     d->d_props = (float4*)tb_upload(f->props, f->n_tris * 16, d);
+    tb_free(d->d_q4nodes); tb_free(d->d_q4src);
+    d->d_q4nodes = NULL; d->d_q4src = NULL; d->n_q4 = 0; d->stack_bound4 = 0;
+    if (f->q4nodes && f->n_q4 && f->stack_bound4 <= TB_V7_SMEM_DEPTH + TB_V7_LOCAL) {
+        d->d_q4nodes = (uint4*)tb_upload(f->q4nodes, f->n_q4 * 16, d);
+        d->d_q4src = (int*)tb_upload(f->q4src, f->n_q4 * 4, d);
+        d->n_q4 = f->n_q4; d->stack_bound4 = f->stack_bound4;
+    }
     d->stack_bound = f->stack_bound;
     d->exact_boxes = f->exact_boxes;
     TbDevScene& sc = d->sc;
@@ -593,6 +613,7 @@ struct TbTraceArgs {
     int           tri_min, refetch_below;   // rounds kernels: parked leaves needed for a triangle round; refill below this many live lanes
     int           stack_smem;               // k_trace_v6: stack entries per lane held in (dynamic) shared memory
     float4*       lo;                       // fused ray generation: zeroed for the paths that leave the scene (k_trace_packet<.., GEN>)
+    const uint4*  q4nodes;                  // k_trace_v7: the 4-wide tree, 4 x uint4 per node
     unsigned long long* round_stats;        // COUNT: lane-rounds by state, see terra_b200_round_stats
 };
 
@@ -722,6 +743,7 @@ __device__ __forceinline__ V3 tb_gen_ray(const TbGenArgs& g, int slot, uint64_t*
 
 #include "tb_trace.cuh"
 #include "tb_trace_v6.cuh"
+#include "tb_trace_v7.cuh"
 #include "tb_trace_packet.cuh"
 
 // ==================================================================================== K1: ray generation kernel
@@ -1431,8 +1453,8 @@ static void tb_drain_events(TbDevice* d) {
 // warp-synchronous rounds over 32-byte quantised nodes (k_trace_v6). The work counters of SURVEY §8(d) mean the
 // per-ray walk: a counting camera launch runs k_trace<COUNT> (a packet would count the union over its 32 rays).
 // Earlier structures and the options that lost their A/B live in experiments/ (not built).
-enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V6, TB_K_PACKET };
-static_assert(TB_K_V6 == TB_K_V6_ID && TB_K_PACKET == TB_K_PACKET_ID, "kernel ids used by tb_device_create");
+enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V6, TB_K_PACKET, TB_K_V7 };
+static_assert(TB_K_V6 == TB_K_V6_ID && TB_K_PACKET == TB_K_PACKET_ID && TB_K_V7 == TB_K_V7_ID, "kernel ids used by tb_device_create");
 
 template <bool COUNT>
 static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind, const TbGenArgs* gen) {
@@ -1461,7 +1483,28 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         else       k_trace<COUNT, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
         return;
     }
-    // TB_K_V6: the rounds kernel
+    if (kind == TB_K_V7 && d->d_q4nodes && !exact && (!COUNT || d->counting == 2)) {
+        // the rounds kernel on the 4-wide tree. Work counters (counting == 1) mean the canonical per-ray walk of the
+        // binary tree, as for camera rays: a 4-wide node is not the 64-byte node SURVEY 8(d) counts. counting == 2
+        // counts this kernel's own fetches and lane states (terra_b200_round_stats).
+        const int forced7 = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
+        int rows7 = forced7 > 0 ? forced7 : TB_V7_SMEM_DEPTH;
+        if (rows7 > TB_V6_MAX_SMEM_DEPTH) rows7 = TB_V6_MAX_SMEM_DEPTH;
+        if (rows7 > d->stack_bound4) rows7 = d->stack_bound4 > 1 ? d->stack_bound4 : 1;
+        const bool spill7 = rows7 < d->stack_bound4;
+        c.stack_smem = rows7;
+        c.q4nodes = d->d_q4nodes;
+        const size_t smem7 = (size_t)(rows7 + 3) * TB_TRACE_THREADS * 8;
+        const int grid7 = d->sm_count * TB_V7_CTAS_PER_SM;
+        if (spill7) k_trace_v7<COUNT, true><<<grid7, TB_TRACE_THREADS, smem7, st>>>(c);
+        else        k_trace_v7<COUNT, false><<<grid7, TB_TRACE_THREADS, smem7, st>>>(c);
+        return;
+    }
+    if (kind == TB_K_V7 && COUNT && !exact && d->d_q4nodes && d->counting != 2) {
+        k_trace<COUNT, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
+        return;
+    }
+    // TB_K_V6: the rounds kernel (also what TB_K_V7 falls back to without a 4-wide tree)
     const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
     int rows = d->stack_bound > 1 ? d->stack_bound : 1;
     if (forced > 0 && forced < rows) rows = forced;
@@ -1483,7 +1526,11 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
 static int tb_trace_kind(const TbDevice* d, bool coherent) {
     int kind = d->trace_kind;
     if (kind == TB_K_AUTO) kind = coherent ? d->coherent_kind : d->incoherent_kind;
-    if (kind == TB_K_AUTO) kind = coherent ? TB_K_PACKET : TB_K_V6;
+    // incoherent rays: the 4-wide tree pays when the geometry does not fit L2 and a node fetch is a DRAM round trip
+    // (r2s A/B, 1M / 3M / 10M triangles: -5 % / +6.5 % / +15.5 % against the binary tree)
+    if (kind == TB_K_AUTO && !coherent)
+        kind = d->d_q4nodes && (size_t)d->sc.n_nodes * 32 + (size_t)d->sc.n_tris * 48 >= d->v7_min_bytes ? TB_K_V7 : TB_K_V6;
+    if (kind == TB_K_AUTO) kind = TB_K_PACKET;
     return kind;
 }
 
@@ -1971,6 +2018,16 @@ extern "C" void tb_device_clone_geometry(TbDevice* dst, const TbDevice* src) {
         memcpy(dst->grid_lo, src->grid_lo, sizeof dst->grid_lo);
         memcpy(dst->grid_cell, src->grid_cell, sizeof dst->grid_cell);
     }
+    tb_free(dst->d_q4nodes); tb_free(dst->d_q4src);
+    dst->d_q4nodes = NULL; dst->d_q4src = NULL; dst->n_q4 = 0; dst->stack_bound4 = 0;
+    if (src->d_q4nodes) {
+        dst->d_q4nodes = tb_alloc<uint4>(src->n_q4 * 4);
+        dst->d_q4src = tb_alloc<int>(src->n_q4 * 4);
+        TB_CUDA(cudaMemcpyPeerAsync(dst->d_q4nodes, dst->index, src->d_q4nodes, src->index, src->n_q4 * 64, dst->stream));
+        TB_CUDA(cudaMemcpyPeerAsync(dst->d_q4src, dst->index, src->d_q4src, src->index, src->n_q4 * 16, dst->stream));
+        dst->n_q4 = src->n_q4; dst->stack_bound4 = src->stack_bound4;
+        dst->stats.p2p_bytes += src->n_q4 * 80;
+    }
     TB_CUDA(cudaStreamSynchronize(dst->stream));
     dst->stats.p2p_bytes += n_nodes * (64 + (src->d_qnodes ? 32 : 0)) + n_tris * 112;
     dst->stack_bound = src->stack_bound;
@@ -2344,6 +2401,17 @@ __global__ void __launch_bounds__(256) k_refit_fit(float4* nodes, const float4* 
         i = p;
     }
 }
+// The 4-wide tree after a refit: every slot's box words are copied again from the binary node they came from.
+__global__ void __launch_bounds__(256) k_refit_quad(const uint32_t* __restrict__ qnodes, const int* __restrict__ src, uint32_t* q4, int n_q4) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_q4 * 4; i += gridDim.x * blockDim.x) {
+        const int s = src[i];
+        if (s < 0) continue;
+        const uint32_t* q = qnodes + (size_t)(s >> 1) * 8 + 3 * (s & 1);
+        uint32_t* w = q4 + (size_t)(i >> 2) * 16 + 3 * (i & 3);
+        w[0] = q[0]; w[1] = q[1]; w[2] = q[2];
+    }
+}
+
 __global__ void __launch_bounds__(256) k_refit_quantise(const float4* __restrict__ nodes, uint4* qnodes, int n_nodes,
                                                         float l0, float l1, float l2, float c0, float c1, float c2) {
     const double gl[3] = { (double)l0, (double)l1, (double)l2 }, gc[3] = { (double)c0, (double)c1, (double)c2 };
@@ -2417,6 +2485,10 @@ extern "C" void tb_device_refit(TbDevice* d, const float* const* obj_tris, const
         k_refit_quantise<<<d->sm_count * 8, 256, 0, st>>>(d->d_nodes, d->d_qnodes, n_nodes, d->grid_lo[0], d->grid_lo[1], d->grid_lo[2],
                                                           d->grid_cell[0], d->grid_cell[1], d->grid_cell[2]);
         d->stats.kernel_launches += 1;
+        if (d->d_q4nodes) {
+            k_refit_quad<<<d->sm_count * 8, 256, 0, st>>>((const uint32_t*)d->d_qnodes, d->d_q4src, (uint32_t*)d->d_q4nodes, (int)d->n_q4);
+            d->stats.kernel_launches += 1;
+        }
     }
     TB_CUDA(cudaEventRecord(e1, st));
     if (n_lights) {

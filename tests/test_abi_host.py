@@ -228,3 +228,45 @@ def test_sah3_and_reference_trees_give_identical_hits(api, scenes, prod, oracle,
     assert np.array_equal(a["t"].view(np.uint32), b["t"].view(np.uint32))
     assert (a["prim"] != b["prim"]).mean() < 0.01
     osc.destroy()
+
+
+def test_quad_tree_is_the_binary_tree_regrouped(api, host_scene):
+    """tb_bvh4_build (the 4-wide tree of k_trace_v7): every slot's box is the quantised box of one binary child, copied
+    word for word; every leaf rank appears exactly once; every binary inner node is either a wide node or was absorbed
+    into one; the stack bound covers the worst near-first walk."""
+    name, s, n_tris = host_scene
+    flat_nodes, _ = s.build_host_bvh(n_tris, api.BVH_SAH3)
+    n_bin = n_tris - 1
+    q4 = np.zeros((n_bin + 1, 16), np.uint32)
+    src = np.full((n_bin + 1, 4), -2, np.int32)
+    qn = np.zeros((n_bin + 1, 8), np.uint32)
+    bound = C.c_int(0)
+    n = s.lib.terra_b200_build_host_bvh4(s.h, api.BVH_SAH3, q4.ctypes.data, src.ctypes.data, qn.ctypes.data, n_bin + 1, C.byref(bound))
+    assert 0 < n <= n_bin
+    q4, src, qn = q4[:n], src[:n], qn[:n_bin]
+    refs = q4[:, 12:16].view(np.int32)
+    used = src >= 0
+    assert used[:, :2].all()                                            # at least the two children of the binary node
+    # boxes: copied from the binary child they name; empty slots are inverted boxes
+    b, c = src[used] >> 1, src[used] & 1
+    boxes = q4[:, :12].reshape(n, 4, 3)
+    want = qn[b][np.arange(b.size)[:, None], (3 * c)[:, None] + np.arange(3)[None, :]]
+    assert np.array_equal(boxes[used], want)
+    assert (boxes[~used] == 0x0000ffff).all()
+    # refs: leaves keep the binary ref (~rank), inner slots point at a LATER wide node (breadth-first numbering)
+    bin_ref = qn[:, 6:8].view(np.int32)[b, c]
+    got = refs[used]
+    leaf = bin_ref < 0
+    assert np.array_equal(got[leaf], bin_ref[leaf])
+    assert np.array_equal(np.sort(~got[leaf]), np.arange(n_tris))       # every triangle exactly once
+    rows = np.nonzero(used)[0]
+    assert (got[~leaf] > rows[~leaf]).all() and (got[~leaf] < n).all()
+    assert np.array_equal(np.sort(got[~leaf]), np.arange(1, n))         # every wide node but the root has exactly one parent
+    # stack bound: sum of (children - 1) along the worst path, + 1
+    depth = np.zeros(n, np.int64)
+    for i in range(n - 1, -1, -1):
+        kids = refs[i][used[i]]
+        inner = kids[kids >= 0]
+        depth[i] = used[i].sum() - 1 + (depth[inner].max() if inner.size else 0)
+    assert bound.value == depth[0] + 1
+    assert n <= (n_bin + 1) // 2 + 1 or n_tris < 8                      # a collapse: at most ~half the binary nodes remain

@@ -102,8 +102,9 @@ def test_lbvh_hits_equal_sah3_hits_on_a_medium_terrain(api, scenes, gpu):
 
 
 # ----------------------------------------------------------------------------- refit (the other half of row N1)
+@pytest.mark.parametrize("kernel", ["auto", "v7"], ids=["default_kernels", "quad_tree_kernel"])
 @pytest.mark.parametrize("mode", [1, 2], ids=["sah3_tree", "gpu_lbvh_tree"])
-def test_refit_gives_the_hits_of_a_fresh_commit(api, scenes, gpu, oracle, mode):
+def test_refit_gives_the_hits_of_a_fresh_commit(api, scenes, gpu, oracle, mode, kernel, monkeypatch):
     """terra_b200_refit after editing vertices in place: the tree keeps its topology, every box is re-fitted on
     the GPU and re-quantised. Closest hits must be those of a fresh commit of the edited geometry (t bit-identical,
     ids modulo exact-t ties, u / v bit-identical where the ids agree) and of the oracle's reference walk; a refit
@@ -111,6 +112,7 @@ def test_refit_gives_the_hits_of_a_fresh_commit(api, scenes, gpu, oracle, mode):
     import ctypes as C
     import cases
     gpu.terra_b200_set_bvh_mode(mode)
+    monkeypatch.setenv("TERRA_B200_INCOHERENT", kernel)      # v7: the 4-wide tree, whose boxes the refit re-copies (k_refit_quad)
     try:
         s, cam, wh = cases.build(scenes, gpu, "field")
         o, d = cases.rays_for(s, api, scenes, 30_000)

@@ -57,6 +57,53 @@ def test_incoherent_hits_vs_reference_fixture(api, scenes, gpu, bvh_mode, name):
     s.destroy()
 
 
+KERNELS = {                # TERRA_B200_INCOHERENT, TERRA_B200_STACK_SMEM (read when a scene's device state is created)
+    "rounds_binary": ("v6", None),
+    "rounds_quad": ("v7", None),              # the 4-wide tree (default only for scenes that do not fit L2)
+    "rounds_quad_spill": ("v7", "2"),         # two shared stack rows: almost every push goes to the local-memory part
+    "per_ray_walk": ("walk", None),
+}
+
+
+@pytest.mark.parametrize("kernel", list(KERNELS))
+@pytest.mark.parametrize("name", list(cases.PRIMARY))
+def test_every_incoherent_kernel_gives_the_fixture_hits(api, scenes, gpu, monkeypatch, name, kernel):
+    """Closest hits do not depend on the kernel or on the tree it walks: binary rounds, 4-wide rounds (boxes copied from
+    the binary tree, up to three pushes per step, shared + local stack), per-ray walk — t, u, v bit-identical to the
+    reference fixture, ids identical between kernels (equal t goes to the smaller rank whatever the visiting order)."""
+    g = golden("geometry.npz")
+    inc, rows = KERNELS[kernel]
+    monkeypatch.setenv("TERRA_B200_INCOHERENT", inc)
+    if rows:
+        monkeypatch.setenv("TERRA_B200_STACK_SMEM", rows)
+    s, cam, wh = cases.build(scenes, gpu, name)
+    o, d = cases.rays_for(s, api, scenes, 4096)
+    got = s.trace_rays(o, d)
+    s.destroy()
+    assert_hits(got, g[f"{name}_rays_hits"], exact_ids=False)
+    monkeypatch.setenv("TERRA_B200_INCOHERENT", "v6")
+    monkeypatch.delenv("TERRA_B200_STACK_SMEM", raising=False)
+    s, cam, wh = cases.build(scenes, gpu, name)
+    base = s.trace_rays(o, d)
+    s.destroy()
+    assert np.array_equal(got.view(np.uint32), base.view(np.uint32))
+
+
+def test_quad_tree_kernel_renders_the_same_image(api, scenes, gpu, monkeypatch):
+    """A whole frame (bounce and visibility rays through k_trace_v7, hits binned per preset) against the binary-tree
+    kernel: same hits -> same paths -> the same framebuffer, bit for bit."""
+    out = []
+    for inc in ("v6", "v7"):
+        monkeypatch.setenv("TERRA_B200_INCOHERENT", inc)
+        s, cam = scenes.sphere_field(gpu, n_spheres=40, n_lat=10, n_lon=12, spp=8, bounces=4, ggx=True, integrator=api.INTEGRATOR_DIRECT)
+        gpu.terra_b200_set_seed(s.h, 5)
+        res, _ = s.render(cam, 160, 90)
+        out.append(res["acc"].copy())
+        s.destroy()
+    assert out[0].sum() > 0
+    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+
+
 def test_triangle_known_answers(api, gpu, bvh_mode):
     """fp64 retry, +0 sign rule, infinite inverse directions, back faces, co-planar rays."""
     tri, o, d = cases.kat_rays()

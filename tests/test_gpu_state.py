@@ -125,7 +125,7 @@ def test_material_edited_in_place_shows_after_commit(api, scenes, gpu):
     assert np.array_equal(edited.view(np.uint32), want.view(np.uint32))
 
 
-def test_multi_device_terra_render_equals_the_sum_of_its_sample_ranges(api, scenes, gpu):
+def test_multi_device_terra_render_equals_the_sum_of_its_sample_ranges(api, scenes, gpu, monkeypatch):
     """Multi-GPU behind terra_render (terra_b200_scene_set_devices / TERRA_B200_DEVICES): the scene is replicated, GPU g
     renders sample range g of the whole region, finalises row band g from ALL accumulators through peer-mapped memory
     and copies its band back. Bit for bit what the ranges give when rendered one by one on a single GPU and summed
@@ -133,6 +133,7 @@ def test_multi_device_terra_render_equals_the_sum_of_its_sample_ranges(api, scen
     n_dev = min(gpu.terra_b200_device_count(), 4)
     if n_dev < 2:
         pytest.skip("one visible GPU")
+    monkeypatch.setenv("TERRA_B200_INCOHERENT", "v7")       # bounce rays on the 4-wide tree: the replicas' copy of it is what renders
     import torch
     w, h, spp = 192, 120, 22            # spp not a multiple of the device count: ranges of different length; 120 rows: ragged bands for 4
     kw = dict(spp=spp, bounces=3, tonemap=api.TONEMAP_REINHARD)
