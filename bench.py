@@ -13,7 +13,8 @@ accumulate -> tonemap). Metric = Mpaths/s (1 path = 1 (pixel, sample) = one terr
   e2e     the reference-facing call: terra_render() on a HOST TerraFramebuffer (H2D of the running
           results[], D2H of results[] + pixels[] inside the timed region)
   roofline  ONE ENTRY PER TRACE KERNEL, the one with more device time named as the dominant one:
-          k_trace_packet (camera rays) and k_trace_v6 (bounce / visibility rays). achieved = algorithmic bytes
+          k_trace_packet (camera rays) and the incoherent-ray kernel the library names (k_trace_v8 on scenes that fit
+          L2, k_trace_v7 beyond; bounce / visibility rays). achieved = algorithmic bytes
           (32 + 16 + 64*nodes + 36*tris per ray; visit counts from the counting variants of the
           kernels, validated against the oracle's canonical walk in tests/) x rays per launch / mean launch time
           (CUDA events the library records around every trace launch on its stream, per kind of launch).
@@ -500,7 +501,8 @@ def run_render_arm(args):
         _, st = timed(lambda: r.render(spp), args.steps, 1)
         lib.terra_b200_set_graph_paths(s.h, 1 << 22)
     # ---- work counters for the rooflines: one small counted frame (never inside a timed region). Camera launches
-    #      count the per-ray walk (k_trace<COUNT>), the others count the rounds kernel's own fetches.
+    #      All launches count the canonical per-ray walk of the binary tree (k_trace<COUNT>): the work the algorithm
+    #      needs, not what a kernel happens to fetch (k_trace_v8 fetches ~5 % more nodes, k_trace_v7 half as many wide ones).
     lib.terra_b200_set_counting(s.h, 1)
     lib.terra_b200_reset_stats(s.h)
     r.render(min(spp, 4 * world))
@@ -519,10 +521,11 @@ def run_render_arm(args):
     coh = kernel_roofline("k_trace_packet (camera rays)", st.coherent_rays, st.coherent_kernel_launches, st.coherent_kernel_ms,
                           stc.coherent_nodes_visited, stc.coherent_tris_tested, stc.coherent_rays,
                           l2_resident, l2_stream, hbm_peak, hbm_src, f"k_trace_packet_{args.workload}")
-    inc = kernel_roofline("k_trace_v6 (bounce / visibility rays)", st.rays_traced - st.coherent_rays,
+    inc_kernel = lib.terra_b200_incoherent_kernel(s.h).decode()
+    inc = kernel_roofline(f"{inc_kernel} (bounce / visibility rays)", st.rays_traced - st.coherent_rays,
                           st.trace_kernel_launches - st.coherent_kernel_launches, st.trace_kernel_ms - st.coherent_kernel_ms,
                           stc.nodes_visited - stc.coherent_nodes_visited, stc.tris_tested - stc.coherent_tris_tested,
-                          stc.rays_traced - stc.coherent_rays, l2_resident, l2_stream, hbm_peak, hbm_src, f"k_trace_v6_{args.workload}")
+                          stc.rays_traced - stc.coherent_rays, l2_resident, l2_stream, hbm_peak, hbm_src, f"{inc_kernel}_{args.workload}")
     kernels = [k for k in (coh, inc) if k]
     for k in kernels:
         k["share_of_step"] = k["ms_per_launch"] * k["launches"] / args.steps / ms_dev if ms_dev else None
@@ -660,9 +663,10 @@ def run_traversal_arm(args):
     hbm_peak, hbm_src = measured_peaks()
     l2_stream, l2_gather = l2_probe(lib)
     l2_resident = wl["tris"] <= 2_000_000            # 1M triangles: 32 MB quantised nodes + 48 MB triangles < 126 MB L2
-    roof = kernel_roofline("k_trace_v6 (incoherent rays)", st.rays_traced, st.trace_kernel_launches, st.trace_kernel_ms,
+    inc_kernel = lib.terra_b200_incoherent_kernel(s.h).decode()
+    roof = kernel_roofline(f"{inc_kernel} (incoherent rays)", st.rays_traced, st.trace_kernel_launches, st.trace_kernel_ms,
                            stc.nodes_visited, stc.tris_tested, stc.rays_traced, l2_resident, l2_stream, hbm_peak, hbm_src,
-                           f"k_trace_v6_{args.workload}")
+                           f"{inc_kernel}_{args.workload}")
     line = {
         "metric": "incoherent_mrays_per_s", "value": n_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -673,7 +677,7 @@ def run_traversal_arm(args):
                 "pageable_value": n_e2e / e2e_pageable_s / 1e6},
         "gpu_launches": int(st.kernel_launches), "clocks": clk,
         "roofline": dict(roof or {}, l2_probe={"stream_gbs": l2_stream, "gather_gbs": l2_gather}, kernel_sources_sha=kernel_sources_sha(),
-                         counter="k_trace_v6<COUNT>, 1M-ray sample"),
+                         counter="k_trace<COUNT> (the canonical per-ray walk of the binary tree), 1M-ray sample"),
         "extra": {"scene_commit_s": commit_s, "commit_ms": commit_ms(lib, s)},
     }
     if cpu_info is not None:

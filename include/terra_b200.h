@@ -301,6 +301,10 @@ typedef struct {
  * [5] owned no ray  [6] lanes x triangle rounds (32 each)  [7] lanes that tested a triangle
  * [8] 32 x refills  [9] lanes refilled.  profiles/r2_summary.md reads the kernel's instruction budget from these. */
 void terra_b200_round_stats(HTerraScene scene, uint64_t* out10);
+/* Name of the closest-hit kernel that bounce / visibility / API rays of this (committed) scene run: "k_trace_v8" (binary
+ * tree, scenes that fit L2), "k_trace_v7" (4-wide tree, larger scenes), "k_trace_v6" / "k_trace" under the A/B switches.
+ * Static string. bench.py labels its roofline with it. */
+const char* terra_b200_incoherent_kernel(HTerraScene scene);
 int  terra_b200_device_count(void);
 void terra_b200_set_device(int device);              /* before terra_scene_commit */
 /* Multi-GPU behind terra_render (the splitter of SURVEY 8b / 8e; the reference's own fan-out is one terra_render per

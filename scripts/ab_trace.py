@@ -20,18 +20,21 @@ REPO = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(REPO))
 
 C3_VARIANTS = [
-    ("v7 (default: 4-wide tree, 16 rows + spill)", dict()),
-    ("v6 (binary tree)", dict(TERRA_B200_INCOHERENT="v6")),
-    ("v7 stack 12 rows", dict(TERRA_B200_STACK_SMEM="12")),
-    ("v7 stack 24 rows", dict(TERRA_B200_STACK_SMEM="24")),
-    ("v7 refetch 18", dict(TERRA_B200_REFETCH="18")),
-    ("v7 refetch 26", dict(TERRA_B200_REFETCH="26")),
-    ("v7 tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
-    ("v7 tri_min 12", dict(TERRA_B200_TRI_MIN="12")),
+    ("default (auto: v8 below 100 MB of nodes + triangles, v7 above)", dict()),
+    ("v6 (binary tree, 7 CTAs, 8-byte stack entries)", dict(TERRA_B200_INCOHERENT="v6")),
+    ("v7 forced (4-wide tree at any size)", dict(TERRA_B200_INCOHERENT="v7")),
+    ("v8 forced (binary tree, 8 CTAs, 4-byte stack entries)", dict(TERRA_B200_INCOHERENT="v8")),
+    ("sweep stack 12 rows", dict(TERRA_B200_STACK_SMEM="12")),
+    ("sweep stack 24 rows", dict(TERRA_B200_STACK_SMEM="24")),
+    ("sweep refetch 18", dict(TERRA_B200_REFETCH="18")),
+    ("sweep refetch 26", dict(TERRA_B200_REFETCH="26")),
+    ("sweep tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
+    ("sweep tri_min 12", dict(TERRA_B200_TRI_MIN="12")),
 ]
 C2_VARIANTS = [
-    ("default (v7 + fused raygen)", dict()),
-    ("v6 (binary tree)", dict(TERRA_B200_INCOHERENT="v6")),
+    ("default (v8 + fused raygen)", dict()),
+    ("v6 (binary tree, 7 CTAs)", dict(TERRA_B200_INCOHERENT="v6")),
+    ("v7 (4-wide tree)", dict(TERRA_B200_INCOHERENT="v7")),
 ]
 SWITCHES = ["TERRA_B200_INCOHERENT", "TERRA_B200_COHERENT", "TERRA_B200_V6_OPT", "TERRA_B200_STACK_SMEM", "TERRA_B200_TRI_MIN",
             "TERRA_B200_REFETCH", "TERRA_B200_FUSED_RAYGEN", "TERRA_B200_NODE_ORDER"]
@@ -111,6 +114,7 @@ def main():
             lib.terra_b200_set_counting(s.h, 0)
             print(json.dumps({"ab": "c3", "build": tag, "variant": name, "tris": args.tris, "rays": n, "ms": ms,
                               "mrays_per_s": n / ms / 1e3, "hit_t_same_as_first_variant": same,
+                              "hit_checksum": int(hits.view(torch.int32).to(torch.int64).sum().item()) if st.nodes_visited is not None else None,
                               "nodes_per_ray": st.nodes_visited / m, "tris_per_ray": st.tris_tested / m}), flush=True)
             s.destroy()
     else:

@@ -191,6 +191,7 @@ class TerraLib:
             sig("terra_b200_get_stats", None, _vp, C.POINTER(Stats))
             sig("terra_b200_reset_stats", None, _vp)
             sig("terra_b200_round_stats", None, _vp, C.POINTER(C.c_uint64))
+            sig("terra_b200_incoherent_kernel", C.c_char_p, _vp)
             sig("terra_b200_set_counting", None, _vp, C.c_int)
             sig("terra_b200_bvh_nodes", _vp, _vp, C.POINTER(C.c_int))
             sig("terra_b200_bvh_stack_bound", C.c_int, _vp)

@@ -837,6 +837,7 @@ extern "C" void terra_b200_get_stats(HTerraScene h, TerraB200Stats* out) {      
     }
 }
 extern "C" void terra_b200_round_stats(HTerraScene h, uint64_t* out10) { tb_device_round_stats(committed(h, "terra_b200_round_stats")->dev, out10); }
+extern "C" const char* terra_b200_incoherent_kernel(HTerraScene h) { return tb_device_incoherent_kernel(committed(h, "terra_b200_incoherent_kernel")->dev); }
 extern "C" void terra_b200_reset_stats(HTerraScene h) { for (TbDevice* d : committed(h, "terra_b200_reset_stats")->devs) tb_device_reset_stats(d); }
 extern "C" void terra_b200_set_env_lit(HTerraScene h, int on) { for (TbDevice* d : committed(h, "terra_b200_set_env_lit")->devs) tb_device_set_env_lit(d, on); }
 // Devices of a scene, before its first commit (default: TERRA_B200_DEVICES, else the terra_b200_set_device one).

@@ -154,6 +154,7 @@ void      tb_device_bsdf_kat(TbDevice* dev, size_t object_idx, size_t n, const f
 int       tb_device_trace_packed_noalloc(TbDevice* dev, size_t n, const float* d_o3, const float* d_d3, void* d_hits, void* stream);
 void      tb_device_get_stats(TbDevice* dev, TerraB200Stats* out);
 void      tb_device_round_stats(TbDevice* dev, uint64_t* out10);
+const char* tb_device_incoherent_kernel(TbDevice* dev);
 void      tb_device_reset_stats(TbDevice* dev);
 void      tb_device_set_counting(TbDevice* dev, int on);
 void      tb_device_set_env_lit(TbDevice* dev, int on);

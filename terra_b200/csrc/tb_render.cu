@@ -63,6 +63,9 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_K_PACKET_ID        3
 #define TB_K_V7_ID            4
 #define TB_V7_MIN_MB          100          // k_trace_v7 by default for scenes whose nodes + triangles exceed this (L2: 126 MB)
+#define TB_K_V8_ID            5
+#define TB_V8_SMEM_DEPTH      40           // k_trace_v8: rows of the shared stack, 4 bytes per entry (deeper trees: + local memory)
+#define TB_LEAN_WORDS         10           // k_trace_v7 / v8: words of per-ray state kept in shared memory behind the stack rows
 #define TB_V7_SMEM_DEPTH      16           // k_trace_v7: rows of the shared stack ...
 #define TB_V7_LOCAL           48           // ... and entries beyond them in local memory; deeper 4-wide trees are not uploaded (the scene runs k_trace_v6)
 
@@ -314,10 +317,12 @@ extern "C" TbDevice* tb_device_create(int device_index) {
         // choose it for bounce / visibility / API rays and for camera rays. walk = per-ray while-while (the work
         // counters' kernel), v6 = rounds kernel (tb_trace_v6.cuh), packet = one warp per 32-ray packet.
         // v7 = the rounds kernel on the 4-wide tree (tb_trace_v7.cuh); a scene without that tree (reference mode) runs v6.
-        static const char* names[] = { "auto", "walk", "v6", "packet", "v7" };
+        // v8 = the rounds kernel on the binary tree with 4-byte stack entries and the triangle-round state in shared memory
+        // (tb_trace_v8.cuh): the default for scenes that fit L2.
+        static const char* names[] = { "auto", "walk", "v6", "packet", "v7", "v8" };
         auto kind_of = [&](const char* env, int dflt) {
             const char* e = getenv(env);
-            for (int k = 0; e && k < 5; ++k) if (strcmp(e, names[k]) == 0) return k;
+            for (int k = 0; e && k < 6; ++k) if (strcmp(e, names[k]) == 0) return k;
             return dflt;
         };
         d->trace_kind = kind_of("TERRA_B200_TRACE", 0);
@@ -744,6 +749,7 @@ __device__ __forceinline__ V3 tb_gen_ray(const TbGenArgs& g, int slot, uint64_t*
 #include "tb_trace.cuh"
 #include "tb_trace_v6.cuh"
 #include "tb_trace_v7.cuh"
+#include "tb_trace_v8.cuh"
 #include "tb_trace_packet.cuh"
 
 // ==================================================================================== K1: ray generation kernel
@@ -1453,8 +1459,8 @@ static void tb_drain_events(TbDevice* d) {
 // warp-synchronous rounds over 32-byte quantised nodes (k_trace_v6). The work counters of SURVEY §8(d) mean the
 // per-ray walk: a counting camera launch runs k_trace<COUNT> (a packet would count the union over its 32 rays).
 // Earlier structures and the options that lost their A/B live in experiments/ (not built).
-enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V6, TB_K_PACKET, TB_K_V7 };
-static_assert(TB_K_V6 == TB_K_V6_ID && TB_K_PACKET == TB_K_PACKET_ID && TB_K_V7 == TB_K_V7_ID, "kernel ids used by tb_device_create");
+enum { TB_K_AUTO = 0, TB_K_WALK, TB_K_V6, TB_K_PACKET, TB_K_V7, TB_K_V8 };
+static_assert(TB_K_V6 == TB_K_V6_ID && TB_K_PACKET == TB_K_PACKET_ID && TB_K_V7 == TB_K_V7_ID && TB_K_V8 == TB_K_V8_ID, "kernel ids used by tb_device_create");
 
 template <bool COUNT>
 static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c, int kind, const TbGenArgs* gen) {
@@ -1494,18 +1500,34 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         const bool spill7 = rows7 < d->stack_bound4;
         c.stack_smem = rows7;
         c.q4nodes = d->d_q4nodes;
-        const size_t smem7 = (size_t)(rows7 + 3) * TB_TRACE_THREADS * 8;
+        const size_t smem7 = (size_t)(rows7 + 3) * TB_TRACE_THREADS * 8 + (size_t)TB_LEAN_WORDS * TB_TRACE_THREADS * 4;
         const int grid7 = d->sm_count * TB_V7_CTAS_PER_SM;
         if (spill7) k_trace_v7<COUNT, true><<<grid7, TB_TRACE_THREADS, smem7, st>>>(c);
         else        k_trace_v7<COUNT, false><<<grid7, TB_TRACE_THREADS, smem7, st>>>(c);
         return;
     }
-    if (kind == TB_K_V7 && COUNT && !exact && d->d_q4nodes && d->counting != 2) {
+    if ((kind == TB_K_V7 || kind == TB_K_V8) && COUNT && !exact && d->counting != 2) {
+        // work counters = the canonical per-ray walk of the binary tree (k_trace_v8 also fetches the ~5 % of nodes whose
+        // stack entry the closest hit had culled: its own fetches are counting == 2)
         k_trace<COUNT, false><<<grid, TB_TRACE_THREADS, 0, st>>>(c);
         return;
     }
-    // TB_K_V6: the rounds kernel (also what TB_K_V7 falls back to without a 4-wide tree)
     const int forced = getenv("TERRA_B200_STACK_SMEM") ? atoi(getenv("TERRA_B200_STACK_SMEM")) : 0;   // A/B: rows of shared stack
+    if (kind != TB_K_V6 && !exact) {
+        // TB_K_V8: the rounds kernel on the binary tree, 8 CTAs per SM (also what TB_K_V7 falls back to without a 4-wide
+        // tree). Its stack entries are 4 bytes, so trees up to 40 levels keep the whole stack in shared memory.
+        int rows8 = d->stack_bound > 1 ? d->stack_bound : 1;
+        const int cap8 = forced > 0 ? forced : TB_V8_SMEM_DEPTH;
+        if (rows8 > cap8) rows8 = cap8;
+        const bool spill8 = rows8 < d->stack_bound;
+        c.stack_smem = rows8;
+        const size_t smem8 = (size_t)(rows8 + 3) * TB_TRACE_THREADS * 4 + (size_t)TB_LEAN_WORDS * TB_TRACE_THREADS * 4;
+        const int grid8 = d->sm_count * TB_V8_CTAS_PER_SM;
+        if (spill8) k_trace_v8<COUNT, true><<<grid8, TB_TRACE_THREADS, smem8, st>>>(c);
+        else        k_trace_v8<COUNT, false><<<grid8, TB_TRACE_THREADS, smem8, st>>>(c);
+        return;
+    }
+    // TB_K_V6: round 2's first rounds kernel — the one with the bit-exact float boxes (exact_boxes) and the A/B baseline
     int rows = d->stack_bound > 1 ? d->stack_bound : 1;
     if (forced > 0 && forced < rows) rows = forced;
     const bool spill = rows > TB_V6_MAX_SMEM_DEPTH || rows < d->stack_bound;
@@ -1529,7 +1551,7 @@ static int tb_trace_kind(const TbDevice* d, bool coherent) {
     // incoherent rays: the 4-wide tree pays when the geometry does not fit L2 and a node fetch is a DRAM round trip
     // (r2s A/B, 1M / 3M / 10M triangles: -5 % / +6.5 % / +15.5 % against the binary tree)
     if (kind == TB_K_AUTO && !coherent)
-        kind = d->d_q4nodes && (size_t)d->sc.n_nodes * 32 + (size_t)d->sc.n_tris * 48 >= d->v7_min_bytes ? TB_K_V7 : TB_K_V6;
+        kind = d->d_q4nodes && (size_t)d->sc.n_nodes * 32 + (size_t)d->sc.n_tris * 48 >= d->v7_min_bytes ? TB_K_V7 : TB_K_V8;
     if (kind == TB_K_AUTO) kind = TB_K_PACKET;
     return kind;
 }
@@ -2521,6 +2543,13 @@ extern "C" void tb_device_round_stats(TbDevice* d, uint64_t* out10) {
     TB_CUDA(cudaMemcpy(out10, d->wave.counters + 32, 10 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
 }
 extern "C" void tb_device_set_counting(TbDevice* d, int on) { d->counting = on; d->graph_epoch++; }
+// Name of the closest-hit kernel an incoherent launch (bounce / visibility / API rays) of this device runs right now.
+extern "C" const char* tb_device_incoherent_kernel(TbDevice* d) {
+    const int kind = tb_trace_kind(d, false);
+    if (kind == TB_K_WALK || kind == TB_K_PACKET) return "k_trace";
+    if (d->exact_boxes || kind == TB_K_V6) return "k_trace_v6";
+    return kind == TB_K_V7 && d->d_q4nodes ? "k_trace_v7" : "k_trace_v8";
+}
 extern "C" void tb_device_set_graph_paths(TbDevice* d, size_t max_paths) { d->graph_max_paths = max_paths; }
 // Builds TbDevDist2D over `f` (ny rows of nx, device) into freshly allocated device arrays.
 static void tb_dist2d_build(TbDevice* d, cudaStream_t st, const float* d_f, int nx, int ny, float** cdf_out, float** rows_out,

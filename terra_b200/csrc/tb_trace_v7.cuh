@@ -31,12 +31,13 @@ __device__ __forceinline__ void tb_sts64_if(bool p, unsigned addr, int2 v) {
 }
 
 #ifndef TB_V7_CTAS_PER_SM
-#define TB_V7_CTAS_PER_SM 6
+#define TB_V7_CTAS_PER_SM 7     /* 72 registers, no spills (the ray state a round does not read lives in shared memory, as in
+                                   tb_trace_v8.cuh); +6.3 % over 6 CTAs x 80 registers on the 10M-triangle terrain (profiles/r2v) */
 #endif
 
 template <bool COUNT, bool SPILL>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v7(TbTraceArgs a) {
-    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][TB_TRACE_THREADS] x 8 B
+    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][threads] x 8 B entries, then [TB_LEAN_WORDS][threads] words
     constexpr int ROW = TB_TRACE_THREADS * 8;
     int2 l_stack[SPILL ? TB_V7_LOCAL : 1];
     const int tid = threadIdx.x;
@@ -51,18 +52,17 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
     tb_sts64(bottom - ROW, make_int2(TB_REF_DONE, 0));             // never culled (tmin 0), never overwritten
     const unsigned smem_end = bottom + a.stack_smem * ROW;         // SPILL: entries from this address on live in local memory
 
-    int   slot = -1, cur = TB_REF_DONE, pend = TB_REF_DONE;
-    unsigned sp = bottom;                          // address of the next free entry
-    int   best_rank = -1, best_tag = 0;
+    // what only a triangle round or the retirement of a ray reads lives in shared memory, [word][thread] behind the
+    // stack rows (see tb_trace_v8.cuh): 0-2 offset origin, 3-5 shear constants, 6 kx | ky << 2 | kz << 4, 7 best rank,
+    // 8 best tag, 9 slot
+    constexpr int LW = TB_TRACE_THREADS * 4;
+    const unsigned lean = (unsigned)__cvta_generic_to_shared(s_v6_stack) + (a.stack_smem + 3) * ROW + tid * 4;
+    int   cur = TB_REF_DONE, pend = TB_REF_DONE;
+    unsigned sp = bottom;                          // address of the next free entry; == bottom: the lane owns no ray
     float best_t = FLT_MAX;
-    TbRay r;                                       // kx / ky / kz live packed in `kpack` between triangle rounds
-    r.o = r.inv = v3s(0.f); r.sx = r.sy = r.sz = 0.f; r.kx = r.ky = r.kz = 0;
-    int   kpack = 0;
+    bool  drained = false;                         // the ray queue is empty: nothing to refill with, stay in the rounds to the end
     TbSelRay sr;
-    sr.ix = sr.iy = sr.iz = sr.ox = sr.oy = sr.oz = 0.f;
-    sr.nx = sr.ny = sr.nz = sr.fx = sr.fy = sr.fz = 0u;
-    // bit 8 of kpack: the ray queue is empty — nothing to refill with, stay in the rounds to the end (a flag of its own
-    // was one register too many: the compiler spilled it and re-read it every round)
+    memset(&sr, 0, sizeof sr);
     unsigned n_nodes = 0, n_tris = 0;
     unsigned n_rounds = 0, n_culled = 0, n_second = 0, n_parked = 0, n_empty = 0, n_tri_rounds = 0, n_refills = 0, n_refilled = 0;
 
@@ -70,25 +70,29 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
         // ---- refill idle lanes (warp converged here)
         const bool idle = cur == TB_REF_DONE && pend == TB_REF_DONE;
         const unsigned idle_mask = __ballot_sync(FULL, idle);
-        if (idle_mask && !(kpack & 0x100)) {
+        if (idle_mask && !drained) {
             const int want = __popc(idle_mask);
             const int leader = __ffs(idle_mask) - 1;
             int base = 0;
             if ((int)lane == leader) base = atomicAdd(a.cursor, want);
             base = __shfl_sync(FULL, base, leader);
-            if (base + want >= total) kpack |= 0x100;
+            if (base + want >= total) drained = true;
             if (COUNT) ++n_refills;
             if (idle) {
                 const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
                 if (q < total) {
-                    slot = a.queue ? a.queue[q] : q;
+                    const int slot = a.queue ? a.queue[q] : q;
                     const float4 o4 = tb_ld_stream(a.ray_o + slot), d4 = tb_ld_stream(a.ray_d + slot);
                     const V3 d = v3(d4.x, d4.y, d4.z);
-                    r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
-                    kpack = (kpack & 0x100) | r.kx | (r.ky << 2) | (r.kz << 4);
+                    const TbRay r = tb_ray_setup(v3(o4.x, o4.y, o4.z), d);
                     sr = tb_sel_ray(r, d, a.grid_lo, a.grid_cell);
+                    tb_sts32(lean + 0 * LW, __float_as_int(r.o.x)); tb_sts32(lean + 1 * LW, __float_as_int(r.o.y)); tb_sts32(lean + 2 * LW, __float_as_int(r.o.z));
+                    tb_sts32(lean + 3 * LW, __float_as_int(r.sx));  tb_sts32(lean + 4 * LW, __float_as_int(r.sy));  tb_sts32(lean + 5 * LW, __float_as_int(r.sz));
+                    tb_sts32(lean + 6 * LW, r.kx | (r.ky << 2) | (r.kz << 4));
+                    tb_sts32(lean + 7 * LW, -1);
+                    tb_sts32(lean + 9 * LW, slot);
                     cur = 0; sp = bottom;
-                    best_rank = -1; best_t = FLT_MAX;
+                    best_t = FLT_MAX;
                     if (COUNT) ++n_refilled;
                 }
             }
@@ -194,12 +198,24 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
                 const int rank = ~pend;
                 if (COUNT) ++n_tris;
                 float t, u, v;
+                TbRay r;
+                r.o = v3(__int_as_float(tb_lds32(lean + 0 * LW)), __int_as_float(tb_lds32(lean + 1 * LW)), __int_as_float(tb_lds32(lean + 2 * LW)));
+                r.inv = v3s(0.f);
+                r.sx = __int_as_float(tb_lds32(lean + 3 * LW)); r.sy = __int_as_float(tb_lds32(lean + 4 * LW)); r.sz = __int_as_float(tb_lds32(lean + 5 * LW));
+                const int kpack = tb_lds32(lean + 6 * LW);
                 r.kx = kpack & 3; r.ky = (kpack >> 2) & 3; r.kz = (kpack >> 4) & 3;
                 if (tb_triangle(r, v3(ta.x, ta.y, ta.z), v3(tb.x, tb.y, tb.z), v3(tc.x, tc.y, tc.z), &t, &u, &v)) {
-                    if (t < best_t || (t == best_t && best_rank >= 0 && rank < best_rank)) {
-                        best_t = t; best_rank = rank; best_tag = __float_as_int(tb.w);
+                    bool better = t < best_t;
+                    if (t == best_t) {                                           // exact tie: the smaller rank wins
+                        const int best_rank = tb_lds32(lean + 7 * LW);
+                        better = best_rank >= 0 && rank < best_rank;
+                    }
+                    if (better) {
+                        best_t = t;
+                        tb_sts32(lean + 7 * LW, rank); tb_sts32(lean + 8 * LW, __float_as_int(tb.w));
                         // API rays: object | triangle << 8, u, v; wavefront: rank and the object | preset << 8 tag for the
                         // shade pass (u, v are not used there). A later, closer hit overwrites the record.
+                        const int slot = tb_lds32(lean + 9 * LW);
                         tb_st_stream(a.hit_out + slot, make_float4(t, a.emit_prim ? ta.w : __int_as_float(rank), a.emit_prim ? u : tb.w, v));
                     }
                 }
@@ -207,16 +223,19 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
             }
             // 7. leave the rounds when the warp is done or has too few rays left to be worth a round
             const unsigned live = __ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE);
-            if (live == 0u || (!(kpack & 0x100) && __popc(live) < a.refetch_below)) break;
+            if (live == 0u || (!drained && __popc(live) < a.refetch_below)) break;
         }
 
         // ---- retire finished rays (warp converged)
-        const bool finished = cur == TB_REF_DONE && pend == TB_REF_DONE && slot >= 0;
+        // a ray ends by popping the sentinel below entry 0 (sp == bottom - ROW); a lane without a ray has sp == bottom
+        const bool finished = cur == TB_REF_DONE && pend == TB_REF_DONE && sp != bottom;
         if (__any_sync(FULL, finished)) {
-            int preset = -1;
+            int preset = -1, slot = -1;
             if (finished) {
-                if (best_rank >= 0) preset = (best_tag >> 8) & 0xff;
+                slot = tb_lds32(lean + 9 * LW);
+                if (best_t < FLT_MAX) preset = (tb_lds32(lean + 8 * LW) >> 8) & 0xff;
                 else tb_st_stream(a.hit_out + slot, make_float4(-1.f, __int_as_float(-1), 0.f, 0.f));
+                sp = bottom;
             }
             if (a.matq) {
 #pragma unroll
@@ -231,7 +250,6 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
                     }
                 }
             }
-            if (finished) slot = -1;
         }
     }
     if (COUNT) {

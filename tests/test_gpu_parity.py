@@ -59,6 +59,8 @@ def test_incoherent_hits_vs_reference_fixture(api, scenes, gpu, bvh_mode, name):
 
 KERNELS = {                # TERRA_B200_INCOHERENT, TERRA_B200_STACK_SMEM (read when a scene's device state is created)
     "rounds_binary": ("v6", None),
+    "rounds_binary_lean": ("v8", None),       # 4-byte stack entries, triangle-round state in shared memory (default for scenes that fit L2)
+    "rounds_binary_lean_spill": ("v8", "2"),  # two shared stack rows, the rest in local memory
     "rounds_quad": ("v7", None),              # the 4-wide tree (default only for scenes that do not fit L2)
     "rounds_quad_spill": ("v7", "2"),         # two shared stack rows: almost every push goes to the local-memory part
     "per_ray_walk": ("walk", None),
@@ -93,7 +95,7 @@ def test_quad_tree_kernel_renders_the_same_image(api, scenes, gpu, monkeypatch):
     """A whole frame (bounce and visibility rays through k_trace_v7, hits binned per preset) against the binary-tree
     kernel: same hits -> same paths -> the same framebuffer, bit for bit."""
     out = []
-    for inc in ("v6", "v7"):
+    for inc in ("v6", "v7", "v8"):
         monkeypatch.setenv("TERRA_B200_INCOHERENT", inc)
         s, cam = scenes.sphere_field(gpu, n_spheres=40, n_lat=10, n_lon=12, spp=8, bounces=4, ggx=True, integrator=api.INTEGRATOR_DIRECT)
         gpu.terra_b200_set_seed(s.h, 5)
@@ -102,6 +104,7 @@ def test_quad_tree_kernel_renders_the_same_image(api, scenes, gpu, monkeypatch):
         s.destroy()
     assert out[0].sum() > 0
     assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+    assert np.array_equal(out[0].view(np.uint32), out[2].view(np.uint32))
 
 
 def test_triangle_known_answers(api, gpu, bvh_mode):
@@ -235,5 +238,17 @@ def test_counting_variant_matches_canonical_counter(api, scenes, gpu, oracle):
     assert st.rays_traced == len(o)
     assert abs(st.nodes_visited - n_nodes) <= 0.05 * n_nodes
     assert abs(st.tris_tested - n_tris) <= 0.15 * n_tris
+    # counting == 2: the default incoherent kernel's OWN fetches and lane states (terra_b200_round_stats). k_trace_v8
+    # keeps no distance in its stack entries, so it also fetches the nodes whose entry the closest hit had culled.
+    assert gpu.terra_b200_incoherent_kernel(s.h) == b"k_trace_v8"
+    gpu.terra_b200_set_counting(s.h, 2)
+    gpu.terra_b200_reset_stats(s.h)
+    s.trace_rays(o, d)
+    st2 = s.stats()
+    rs = (C.c_uint64 * 10)()
+    gpu.terra_b200_round_stats(s.h, rs)
+    gpu.terra_b200_set_counting(s.h, 0)
+    assert 0.98 * n_nodes <= st2.nodes_visited <= 1.15 * n_nodes
+    assert rs[1] == st2.nodes_visited and rs[7] == st2.tris_tested and rs[9] == len(o)
     osc.destroy()
     s.destroy()
