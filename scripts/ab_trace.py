@@ -31,6 +31,9 @@ C3_VARIANTS = [
     ("sweep tri_min 6", dict(TERRA_B200_TRI_MIN="6")),
     ("sweep tri_min 12", dict(TERRA_B200_TRI_MIN="12")),
 ]
+# grid over the two run-time knobs of the rounds kernels: --only grid
+C3_VARIANTS += [(f"grid refetch {r} tri_min {t}", dict(TERRA_B200_REFETCH=str(r), TERRA_B200_TRI_MIN=str(t)))
+                for r in (20, 22, 24, 26) for t in (6, 8, 10)]
 C2_VARIANTS = [
     ("default (v8 + fused raygen)", dict()),
     ("v6 (binary tree, 7 CTAs)", dict(TERRA_B200_INCOHERENT="v6")),

@@ -48,8 +48,8 @@ extern "C" void terra_log(const char* fmt, ...);
 #endif
 #define TB_STACK_SMEM         16           // traversal stack entries held in shared memory ...
 #define TB_STACK_LOCAL        112          // ... deeper entries spill to local memory
-#define TB_TRI_MIN            8            // rounds kernel: parked leaves needed before a triangle round
-#define TB_REFETCH_ROUNDS     22           // rounds kernel: refill the warp when fewer lanes own a ray (swept on B200 with k_trace_v6: 18/22/26/29)
+#define TB_TRI_MIN            6            // rounds kernels: parked leaves needed before a triangle round (grid of profiles/r3c_grid.jsonl)
+#define TB_REFETCH_ROUNDS     24           // rounds kernels: refill the warp when fewer lanes own a ray (grid of profiles/r3c_grid.jsonl: 20 / 22 / 24 / 26)
 #define TB_REFETCH_BELOW      20           // dynamic fetch: refill the warp when fewer lanes are busy
 #define TB_SHADE_THREADS      256
 #ifndef TB_SHADE_MIN_BLOCKS
@@ -1500,7 +1500,7 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         const bool spill7 = rows7 < d->stack_bound4;
         c.stack_smem = rows7;
         c.q4nodes = d->d_q4nodes;
-        const size_t smem7 = (size_t)(rows7 + 3) * TB_TRACE_THREADS * 8 + (size_t)TB_LEAN_WORDS * TB_TRACE_THREADS * 4;
+        const size_t smem7 = (size_t)(rows7 + 3) * TB_TRACE_THREADS * 8 + (size_t)TB_LEAN_WORDS * TB_TRACE_THREADS * 4 + (TB_TRACE_THREADS / 32) * 8;
         const int grid7 = d->sm_count * TB_V7_CTAS_PER_SM;
         if (spill7) k_trace_v7<COUNT, true><<<grid7, TB_TRACE_THREADS, smem7, st>>>(c);
         else        k_trace_v7<COUNT, false><<<grid7, TB_TRACE_THREADS, smem7, st>>>(c);
@@ -1521,7 +1521,7 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
         if (rows8 > cap8) rows8 = cap8;
         const bool spill8 = rows8 < d->stack_bound;
         c.stack_smem = rows8;
-        const size_t smem8 = (size_t)(rows8 + 3) * TB_TRACE_THREADS * 4 + (size_t)TB_LEAN_WORDS * TB_TRACE_THREADS * 4;
+        const size_t smem8 = (size_t)(rows8 + 3) * TB_TRACE_THREADS * 4 + (size_t)TB_LEAN_WORDS * TB_TRACE_THREADS * 4 + (TB_TRACE_THREADS / 32) * 8;
         const int grid8 = d->sm_count * TB_V8_CTAS_PER_SM;
         if (spill8) k_trace_v8<COUNT, true><<<grid8, TB_TRACE_THREADS, smem8, st>>>(c);
         else        k_trace_v8<COUNT, false><<<grid8, TB_TRACE_THREADS, smem8, st>>>(c);

@@ -116,6 +116,45 @@ __device__ __forceinline__ void tb_sts32(unsigned addr, int v) {
     asm volatile("st.shared.b32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
 }
 
+// Refill of the lean rounds kernels (k_trace_v7, k_trace_v8). Rays are handed out in blocks of TB_REFILL_BLOCK queue
+// positions per warp, and the block after the one in use is reserved one refill ahead: the atomic's round trip (2.4 % of
+// all stall samples sat on the shuffle behind it, ncu r2y) is over long before its result is read, and a refill that
+// still finds enough positions in its block issues no atomic at all (+1.6 % on C3 1M, profiles/r3d; an L2 prefetch of
+// the block's rays on top of it measured nothing). {next, end} of the block in use live in 8 bytes of shared memory per
+// warp (`wstate`), the position reserved ahead in lane 0's `pre`. Returns the calling lane's queue position (lanes of
+// idle_mask only; >= total: no ray left for it) and sets `drained` when this warp will find no further ray.
+#define TB_REFILL_BLOCK 32      /* >= 32: a refill takes at most one block switch */
+__device__ __forceinline__ int tb_refill_init(unsigned lane, unsigned wstate, int* cursor) {
+    int pre = 0;
+    if (lane == 0) {
+        tb_sts64(wstate, make_int2(0, 0));
+        pre = atomicAdd(cursor, TB_REFILL_BLOCK);
+    }
+    __syncwarp();
+    return pre;
+}
+__device__ __forceinline__ int tb_refill_position(unsigned idle_mask, unsigned lane, unsigned wstate, int& pre, int* cursor, int total, bool& drained) {
+    const int want = __popc(idle_mask);
+    const int2 blk = tb_lds64(wstate);
+    const int avail = blk.y - blk.x;
+    const int rank = __popc(idle_mask & ((1u << lane) - 1u));
+    int q = blk.x + rank;
+    if (want > avail) {                                             // warp-uniform: the block in use runs out
+        const int nb = __shfl_sync(0xffffffffu, pre, 0);
+        q = rank < avail ? q : nb + (rank - avail);
+        if (lane == 0) {
+            tb_sts64(wstate, make_int2(nb + (want - avail), nb + TB_REFILL_BLOCK));
+            pre = atomicAdd(cursor, TB_REFILL_BLOCK);
+        }
+        if (nb + (want - avail) >= total) drained = true;          // blocks are handed out in increasing order
+    } else {
+        if (lane == 0) tb_sts32(wstate, blk.x + want);
+        if (blk.x + want >= total) drained = true;
+    }
+    __syncwarp();
+    return q;
+}
+
 __device__ __forceinline__ void tb_ld_qnode(const uint4* np, uint4& qa, uint4& qb) {
     asm volatile("ld.global.nc.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(qa.x), "=r"(qa.y), "=r"(qa.z), "=r"(qa.w), "=r"(qb.x), "=r"(qb.y), "=r"(qb.z), "=r"(qb.w) : "l"(np));

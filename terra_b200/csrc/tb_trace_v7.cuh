@@ -30,6 +30,67 @@ __device__ __forceinline__ void tb_sts64_if(bool p, unsigned addr, int2 v) {
     asm volatile("{ .reg .pred q; setp.ne.u32 q, %3, 0; @q st.shared.v2.b32 [%0], {%1, %2}; }" :: "r"(addr), "r"(v.x), "r"(v.y), "r"((unsigned)p) : "memory");
 }
 
+// Pop for the 4-wide kernel: the entry carries its box's entry distance; one that the closest hit has culled since it
+// was pushed leaves the lane in POP state (it pops again at the next step).
+template <bool SPILL, int ROW>
+__device__ __forceinline__ void tb_v7_pop(int& cur, unsigned& sp, float cull_t, unsigned smem_end, const int2* l_stack) {
+    int2 e;
+    if (SPILL && sp > smem_end) e = l_stack[(sp - smem_end) / ROW - 1];
+    else e = tb_lds64(sp - ROW);
+    const bool need = cur == TB_REF_POP;
+    const int popped = __int_as_float(e.y) > cull_t ? TB_REF_POP : e.x;
+    cur = need ? popped : cur;
+    sp = need ? sp - ROW : sp;
+}
+
+// Node step: four boxes, the hit children ordered by entry distance with a 5-comparator network on (key, ref) pairs —
+// key = the bits of tmin (>= 0: they order as unsigned) with the slot number in the two low bits, so keys are distinct
+// and a stored tmin is rounded DOWN (culls conservatively) — the nearest becomes the lane's node, the others are pushed
+// far to near.
+template <bool SPILL, int ROW>
+__device__ __forceinline__ void tb_v7_node_step(const TbSelRay& sr, const uint4& qa, const uint4& qb, const uint4& qc, const uint4& qd, float cull_t,
+                                                int& cur, unsigned& sp, unsigned smem_end, int2* l_stack) {
+    float t0, t1, t2, t3;
+    // the cull distance is folded into the exit distance (a box entered at or beyond cull_t holds no closer hit)
+    const bool h0 = tb_box_sel_cull(sr, qa.x, qa.y, qa.z, cull_t, &t0);
+    const bool h1 = tb_box_sel_cull(sr, qa.w, qb.x, qb.y, cull_t, &t1);
+    const bool h2 = tb_box_sel_cull(sr, qb.z, qb.w, qc.x, cull_t, &t2);
+    const bool h3 = tb_box_sel_cull(sr, qc.y, qc.z, qc.w, cull_t, &t3);
+    unsigned k0 = h0 ? (__float_as_uint(t0) & ~3u) : 0xffffffffu;
+    unsigned k1 = h1 ? ((__float_as_uint(t1) & ~3u) | 1u) : 0xffffffffu;
+    unsigned k2 = h2 ? ((__float_as_uint(t2) & ~3u) | 2u) : 0xffffffffu;
+    unsigned k3 = h3 ? ((__float_as_uint(t3) & ~3u) | 3u) : 0xffffffffu;
+    int r0 = (int)qd.x, r1 = (int)qd.y, r2 = (int)qd.z, r3 = (int)qd.w;
+#define TB_CSWAP(KA, RA, KB, RB) { const bool s_ = KA > KB; const unsigned kl_ = s_ ? KB : KA, kh_ = s_ ? KA : KB; \
+                       const int rl_ = s_ ? RB : RA, rh_ = s_ ? RA : RB; KA = kl_; KB = kh_; RA = rl_; RB = rh_; }
+    TB_CSWAP(k0, r0, k1, r1) TB_CSWAP(k2, r2, k3, r3) TB_CSWAP(k0, r0, k2, r2) TB_CSWAP(k1, r1, k3, r3) TB_CSWAP(k1, r1, k2, r2)
+#undef TB_CSWAP
+    // misses sort to the end: entry j is a hit iff kj != ~0. The key itself is stored as the entry's distance:
+    // at most 3 ulp above the box's tmin, far inside the 1e-5 margin of cull_t.
+    if (!SPILL || sp + 2 * ROW < smem_end) {
+        tb_sts64_if(k3 != 0xffffffffu, sp, make_int2(r3, (int)k3)); sp += k3 != 0xffffffffu ? ROW : 0;
+        tb_sts64_if(k2 != 0xffffffffu, sp, make_int2(r2, (int)k2)); sp += k2 != 0xffffffffu ? ROW : 0;
+        tb_sts64_if(k1 != 0xffffffffu, sp, make_int2(r1, (int)k1)); sp += k1 != 0xffffffffu ? ROW : 0;
+    } else {                        // near the end of the shared rows: entries from smem_end on live in local memory
+        if (k3 != 0xffffffffu) {
+            if (sp >= smem_end) l_stack[(sp - smem_end) / ROW] = make_int2(r3, (int)k3); else tb_sts64(sp, make_int2(r3, (int)k3));
+            sp += ROW;
+        }
+        if (k2 != 0xffffffffu) {
+            if (sp >= smem_end) l_stack[(sp - smem_end) / ROW] = make_int2(r2, (int)k2); else tb_sts64(sp, make_int2(r2, (int)k2));
+            sp += ROW;
+        }
+        if (k1 != 0xffffffffu) {
+            if (sp >= smem_end) l_stack[(sp - smem_end) / ROW] = make_int2(r1, (int)k1); else tb_sts64(sp, make_int2(r1, (int)k1));
+            sp += ROW;
+        }
+    }
+    cur = k0 != 0xffffffffu ? r0 : TB_REF_POP;
+}
+
+#ifndef TB_V7_STEPS
+#define TB_V7_STEPS 2           /* node steps per round (see tb_trace_v8.cuh, step 6b): 1 / 2 / 3 = 4127 / 4243 / 4180 Mrays/s on C3 10M (profiles/r3b) */
+#endif
 #ifndef TB_V7_CTAS_PER_SM
 #define TB_V7_CTAS_PER_SM 7     /* 72 registers, no spills (the ray state a round does not read lives in shared memory, as in
                                    tb_trace_v8.cuh); +6.3 % over 6 CTAs x 80 registers on the 10M-triangle terrain (profiles/r2v) */
@@ -37,7 +98,7 @@ __device__ __forceinline__ void tb_sts64_if(bool p, unsigned addr, int2 v) {
 
 template <bool COUNT, bool SPILL>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v7(TbTraceArgs a) {
-    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][threads] x 8 B entries, then [TB_LEAN_WORDS][threads] words
+    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][threads] x 8 B entries, [TB_LEAN_WORDS][threads] words, [warps] x 8 B refill state
     constexpr int ROW = TB_TRACE_THREADS * 8;
     int2 l_stack[SPILL ? TB_V7_LOCAL : 1];
     const int tid = threadIdx.x;
@@ -63,6 +124,8 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
     bool  drained = false;                         // the ray queue is empty: nothing to refill with, stay in the rounds to the end
     TbSelRay sr;
     memset(&sr, 0, sizeof sr);
+    const unsigned wstate = (unsigned)__cvta_generic_to_shared(s_v6_stack) + (a.stack_smem + 3) * ROW + TB_LEAN_WORDS * LW + (tid >> 5) * 8;
+    int pre = tb_refill_init(lane, wstate, a.cursor);             // lane 0: first queue position of the block reserved ahead
     unsigned n_nodes = 0, n_tris = 0;
     unsigned n_rounds = 0, n_culled = 0, n_second = 0, n_parked = 0, n_empty = 0, n_tri_rounds = 0, n_refills = 0, n_refilled = 0;
 
@@ -71,15 +134,9 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
         const bool idle = cur == TB_REF_DONE && pend == TB_REF_DONE;
         const unsigned idle_mask = __ballot_sync(FULL, idle);
         if (idle_mask && !drained) {
-            const int want = __popc(idle_mask);
-            const int leader = __ffs(idle_mask) - 1;
-            int base = 0;
-            if ((int)lane == leader) base = atomicAdd(a.cursor, want);
-            base = __shfl_sync(FULL, base, leader);
-            if (base + want >= total) drained = true;
             if (COUNT) ++n_refills;
+            const int q = tb_refill_position(idle_mask, lane, wstate, pre, a.cursor, total, drained);
             if (idle) {
-                const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
                 if (q < total) {
                     const int slot = a.queue ? a.queue[q] : q;
                     const float4 o4 = tb_ld_stream(a.ray_o + slot), d4 = tb_ld_stream(a.ray_d + slot);
@@ -111,18 +168,9 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
                 pend = park ? cur : pend;
                 cur = park ? TB_REF_POP : cur;
             }
-            // 2. pop, resolved with selects. An entry the closest hit has culled since it was pushed leaves the lane
-            //    in POP state: it pops again next round (a second pop in the same round, and a pop loop, were measured:
-            //    -1.5 % and -10 %, experiments/README.md)
-            {
-                int2 e;
-                if (SPILL && sp > smem_end) e = l_stack[(sp - smem_end) / ROW - 1];
-                else e = tb_lds64(sp - ROW);
-                const bool need = cur == TB_REF_POP;
-                const int popped = __int_as_float(e.y) > cull_t ? TB_REF_POP : e.x;
-                cur = need ? popped : cur;
-                sp = need ? sp - ROW : sp;
-            }
+            // 2. pop, resolved with selects (a second pop in the same round, and a pop loop, were measured: -1.5 % and -10 %,
+            //    experiments/README.md)
+            tb_v7_pop<SPILL, ROW>(cur, sp, cull_t, smem_end, l_stack);
             // 3. what does this round do?
             const bool is_node = cur >= 0;
             const unsigned node_mask = __ballot_sync(FULL, is_node);
@@ -150,48 +198,10 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
                 const float4* tp = a.tris + (size_t)(~pend) * 3;
                 ta = __ldg(tp); tb = __ldg(tp + 1); tc = __ldg(tp + 2);
             }
-            // 5. node step: four boxes, the hit children ordered by entry distance with a 5-comparator network on
-            //    (key, ref) pairs — key = the bits of tmin (>= 0: they order as unsigned) with the slot number in the
-            //    two low bits, so keys are distinct and a stored tmin is rounded DOWN (culls conservatively) — the
-            //    nearest becomes the lane's node, the others are pushed far to near
+            // 5. node step
             if (is_node) {
                 if (COUNT) ++n_nodes;
-                float t0, t1, t2, t3;
-                // the cull distance is folded into the exit distance (a box entered at or beyond cull_t holds no closer hit)
-                const bool h0 = tb_box_sel_cull(sr, qa.x, qa.y, qa.z, cull_t, &t0);
-                const bool h1 = tb_box_sel_cull(sr, qa.w, qb.x, qb.y, cull_t, &t1);
-                const bool h2 = tb_box_sel_cull(sr, qb.z, qb.w, qc.x, cull_t, &t2);
-                const bool h3 = tb_box_sel_cull(sr, qc.y, qc.z, qc.w, cull_t, &t3);
-                unsigned k0 = h0 ? (__float_as_uint(t0) & ~3u) : 0xffffffffu;
-                unsigned k1 = h1 ? ((__float_as_uint(t1) & ~3u) | 1u) : 0xffffffffu;
-                unsigned k2 = h2 ? ((__float_as_uint(t2) & ~3u) | 2u) : 0xffffffffu;
-                unsigned k3 = h3 ? ((__float_as_uint(t3) & ~3u) | 3u) : 0xffffffffu;
-                int r0 = (int)qd.x, r1 = (int)qd.y, r2 = (int)qd.z, r3 = (int)qd.w;
-#define TB_CSWAP(KA, RA, KB, RB) { const bool s_ = KA > KB; const unsigned kl_ = s_ ? KB : KA, kh_ = s_ ? KA : KB; \
-                                   const int rl_ = s_ ? RB : RA, rh_ = s_ ? RA : RB; KA = kl_; KB = kh_; RA = rl_; RB = rh_; }
-                TB_CSWAP(k0, r0, k1, r1) TB_CSWAP(k2, r2, k3, r3) TB_CSWAP(k0, r0, k2, r2) TB_CSWAP(k1, r1, k3, r3) TB_CSWAP(k1, r1, k2, r2)
-#undef TB_CSWAP
-                // misses sort to the end: entry j is a hit iff kj != ~0. The key itself is stored as the entry's distance:
-                // at most 3 ulp above the box's tmin, far inside the 1e-5 margin of cull_t.
-                if (!SPILL || sp + 2 * ROW < smem_end) {
-                    tb_sts64_if(k3 != 0xffffffffu, sp, make_int2(r3, (int)k3)); sp += k3 != 0xffffffffu ? ROW : 0;
-                    tb_sts64_if(k2 != 0xffffffffu, sp, make_int2(r2, (int)k2)); sp += k2 != 0xffffffffu ? ROW : 0;
-                    tb_sts64_if(k1 != 0xffffffffu, sp, make_int2(r1, (int)k1)); sp += k1 != 0xffffffffu ? ROW : 0;
-                } else {                        // near the end of the shared rows: entries from smem_end on live in local memory
-                    if (k3 != 0xffffffffu) {
-                        if (sp >= smem_end) l_stack[(sp - smem_end) / ROW] = make_int2(r3, (int)k3); else tb_sts64(sp, make_int2(r3, (int)k3));
-                        sp += ROW;
-                    }
-                    if (k2 != 0xffffffffu) {
-                        if (sp >= smem_end) l_stack[(sp - smem_end) / ROW] = make_int2(r2, (int)k2); else tb_sts64(sp, make_int2(r2, (int)k2));
-                        sp += ROW;
-                    }
-                    if (k1 != 0xffffffffu) {
-                        if (sp >= smem_end) l_stack[(sp - smem_end) / ROW] = make_int2(r1, (int)k1); else tb_sts64(sp, make_int2(r1, (int)k1));
-                        sp += ROW;
-                    }
-                }
-                cur = k0 != 0xffffffffu ? r0 : TB_REF_POP;
+                tb_v7_node_step<SPILL, ROW>(sr, qa, qb, qc, qd, cull_t, cur, sp, smem_end, l_stack);
             }
             // 6. triangle step for the parked leaves
             if (do_tri) {
@@ -220,6 +230,29 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V7_CTAS_PER_SM) k_trace_v
                     }
                 }
                 pend = TB_REF_DONE;
+            }
+            // 6b. further node steps of the round (tb_trace_v8.cuh): the round's bookkeeping is paid once for TB_V7_STEPS steps
+#pragma unroll
+            for (int step = 1; step < TB_V7_STEPS; ++step) {
+                const float cull2 = best_t + best_t * 1e-5f;                 // the triangle step may have moved the closest hit
+                tb_v7_pop<SPILL, ROW>(cur, sp, cull2, smem_end, l_stack);
+                const bool is_node2 = cur >= 0;
+                if (COUNT) {
+                    ++n_rounds;
+                    if (!is_node2) {
+                        if (cur == TB_REF_POP) ++n_culled;
+                        else if (cur != TB_REF_DONE) ++n_second;
+                        else if (pend != TB_REF_DONE) ++n_parked;
+                        else ++n_empty;
+                    }
+                }
+                if (is_node2) {
+                    uint4 qe, qf, qg, qh;
+                    tb_ld_qnode(a.q4nodes + (size_t)cur * 4, qe, qf);
+                    tb_ld_qnode(a.q4nodes + (size_t)cur * 4 + 2, qg, qh);
+                    if (COUNT) ++n_nodes;
+                    tb_v7_node_step<SPILL, ROW>(sr, qe, qf, qg, qh, cull2, cur, sp, smem_end, l_stack);
+                }
             }
             // 7. leave the rounds when the warp is done or has too few rays left to be worth a round
             const unsigned live = __ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE);

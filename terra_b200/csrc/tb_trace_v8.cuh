@@ -17,9 +17,45 @@
 #define TB_V8_CTAS_PER_SM 8
 #endif
 
+#ifndef TB_V8_STEPS
+#define TB_V8_STEPS 3           /* node steps per round, see step 6b: 1 / 2 / 3 / 4 = 5360 / 5849 / 5972 / 5977 Mrays/s on C3 1M (profiles/r3a, r3b) */
+#endif
+
+// Pop: entry [sp - ROW] becomes the lane's node when the lane asked for one (cur == POP). Unconditional read (the row
+// below entry 0 is the sentinel, the row below that is padding), resolved with selects.
+template <bool SPILL, int ROW>
+__device__ __forceinline__ void tb_v8_pop(int& cur, unsigned& sp, unsigned smem_end, const int* l_stack) {
+    int e;
+    if (SPILL && sp > smem_end) e = l_stack[(sp - smem_end) / ROW - 1];
+    else e = tb_lds32(sp - ROW);
+    const bool need = cur == TB_REF_POP;
+    cur = need ? e : cur;
+    sp = need ? sp - ROW : sp;
+}
+
+// Node step: both child boxes, near child next, far child pushed.
+template <bool SPILL, int ROW>
+__device__ __forceinline__ void tb_v8_node_step(const TbSelRay& sr, const uint4& qa, const uint4& qb, float cull_t, int& cur, unsigned& sp,
+                                                unsigned smem_end, int* l_stack) {
+    const int ref0 = (int)qb.z, ref1 = (int)qb.w;
+    float tmin0, tmin1;
+    bool hit0 = tb_box_sel(sr, qa.x, qa.y, qa.z, &tmin0);
+    bool hit1 = tb_box_sel(sr, qa.w, qb.x, qb.y, &tmin1);
+    hit0 = hit0 && !(tmin0 > cull_t);
+    hit1 = hit1 && !(tmin1 > cull_t);
+    const bool near1 = tmin1 < tmin0;
+    const bool both = hit0 && hit1;
+    const int far = near1 ? ref0 : ref1;
+    if (SPILL && sp >= smem_end) l_stack[(sp - smem_end) / ROW] = far;
+    else tb_sts32(sp, far);                                      // scratch row when !both
+    sp += both ? ROW : 0;
+    const int one = hit0 ? ref0 : (hit1 ? ref1 : TB_REF_POP);
+    cur = both ? (near1 ? ref1 : ref0) : one;
+}
+
 template <bool COUNT, bool SPILL>
 __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v8(TbTraceArgs a) {
-    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][threads] x 4 B entries, then [TB_LEAN_WORDS][threads] words
+    extern __shared__ __align__(16) unsigned char s_v6_stack[];    // [stack_smem + 3][threads] x 4 B entries, [TB_LEAN_WORDS][threads] words, [warps] x 8 B refill state
     constexpr int ROW = TB_TRACE_THREADS * 4;                      // one row of stack entries: the child reference alone
     constexpr int LW = TB_TRACE_THREADS * 4;                       // one row of lean words
     int l_stack[SPILL ? TB_V6_LOCAL : 1];
@@ -39,6 +75,8 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v
     bool  drained = false;                         // the ray queue is empty: nothing to refill with, stay in the rounds to the end
     TbSelRay sr;
     memset(&sr, 0, sizeof sr);
+    const unsigned wstate = (unsigned)__cvta_generic_to_shared(s_v6_stack) + (a.stack_smem + 3) * ROW + TB_LEAN_WORDS * LW + (tid >> 5) * 8;
+    int pre = tb_refill_init(lane, wstate, a.cursor);             // lane 0: first queue position of the block reserved ahead
     unsigned n_nodes = 0, n_tris = 0;
     unsigned n_rounds = 0, n_culled = 0, n_second = 0, n_parked = 0, n_empty = 0, n_tri_rounds = 0, n_refills = 0, n_refilled = 0;
 
@@ -48,14 +86,9 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v
         const unsigned idle_mask = __ballot_sync(FULL, idle);
         if (idle_mask && !drained) {
             const int want = __popc(idle_mask);
-            const int leader = __ffs(idle_mask) - 1;
-            int base = 0;
-            if ((int)lane == leader) base = atomicAdd(a.cursor, want);
-            base = __shfl_sync(FULL, base, leader);
-            if (base + want >= total) drained = true;
             if (COUNT) ++n_refills;
+            const int q = tb_refill_position(idle_mask, lane, wstate, pre, a.cursor, total, drained);
             if (idle) {
-                const int q = base + __popc(idle_mask & ((1u << lane) - 1u));
                 if (q < total) {
                     const int slot = a.queue ? a.queue[q] : q;
                     const float4 o4 = tb_ld_stream(a.ray_o + slot), d4 = tb_ld_stream(a.ray_d + slot);
@@ -89,14 +122,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v
             }
             // 2. pop. An entry carries no distance: one that the closest hit has culled since it was pushed is fetched
             //    and fails both box tests (1.2 of 23 node fetches per ray on C3 1M) — the price of the half-size stack.
-            {
-                int e;
-                if (SPILL && sp > smem_end) e = l_stack[(sp - smem_end) / ROW - 1];
-                else e = tb_lds32(sp - ROW);
-                const bool need = cur == TB_REF_POP;
-                cur = need ? e : cur;
-                sp = need ? sp - ROW : sp;
-            }
+            tb_v8_pop<SPILL, ROW>(cur, sp, smem_end, l_stack);
             // 3. what does this round do?
             const bool is_node = cur >= 0;
             const unsigned node_mask = __ballot_sync(FULL, is_node);
@@ -124,20 +150,7 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v
             // 5. node step
             if (is_node) {
                 if (COUNT) ++n_nodes;
-                const int ref0 = (int)qb.z, ref1 = (int)qb.w;
-                float tmin0, tmin1;
-                bool hit0 = tb_box_sel(sr, qa.x, qa.y, qa.z, &tmin0);
-                bool hit1 = tb_box_sel(sr, qa.w, qb.x, qb.y, &tmin1);
-                hit0 = hit0 && !(tmin0 > cull_t);
-                hit1 = hit1 && !(tmin1 > cull_t);
-                const bool near1 = tmin1 < tmin0;
-                const bool both = hit0 && hit1;
-                const int far = near1 ? ref0 : ref1;
-                if (SPILL && sp >= smem_end) l_stack[(sp - smem_end) / ROW] = far;
-                else tb_sts32(sp, far);                                      // scratch row when !both
-                sp += both ? ROW : 0;
-                const int one = hit0 ? ref0 : (hit1 ? ref1 : TB_REF_POP);
-                cur = both ? (near1 ? ref1 : ref0) : one;
+                tb_v8_node_step<SPILL, ROW>(sr, qa, qb, cull_t, cur, sp, smem_end, l_stack);
             }
             // 6. triangle step for the parked leaves: the watertight test's ray constants come back from shared memory
             if (do_tri) {
@@ -164,6 +177,30 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v
                     }
                 }
                 pend = TB_REF_DONE;
+            }
+            // 6b. further node steps of the round: a round's bookkeeping (park, two ballots, the triangle-round decision, the
+            //     exit test: 44 of its ~95 warp instructions, ncu r2y) is paid once for TB_V8_STEPS node steps. A lane whose
+            //     step ended on a leaf sits the rest of the round out (the leaf is parked at the top of the next round);
+            //     every other lane pops if it must and goes on.
+#pragma unroll
+            for (int step = 1; step < TB_V8_STEPS; ++step) {
+                const float cull2 = best_t + best_t * 1e-5f;                 // the triangle step may have moved the closest hit
+                tb_v8_pop<SPILL, ROW>(cur, sp, smem_end, l_stack);
+                const bool is_node2 = cur >= 0;
+                if (COUNT) {
+                    ++n_rounds;
+                    if (!is_node2) {
+                        if (cur != TB_REF_DONE) ++n_second;
+                        else if (pend != TB_REF_DONE) ++n_parked;
+                        else ++n_empty;
+                    }
+                }
+                if (is_node2) {
+                    uint4 qc, qd;
+                    tb_ld_qnode(a.qnodes + (size_t)cur * 2, qc, qd);
+                    if (COUNT) ++n_nodes;
+                    tb_v8_node_step<SPILL, ROW>(sr, qc, qd, cull2, cur, sp, smem_end, l_stack);
+                }
             }
             // 7. leave the rounds when the warp is done or has too few rays left to be worth a round
             const unsigned live = __ballot_sync(FULL, cur != TB_REF_DONE || pend != TB_REF_DONE);
