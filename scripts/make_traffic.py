@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """profiles/traffic.json from the raw pages of the round's `ncu --set full` captures (gpurun_out/<tag>_*_raw.csv, made by
-scripts/gpu_r2q.sh) and the plain bench lines of the same commands: DRAM bytes per ray and issue figures per kernel and
+scripts/gpu_closing.sh) and the plain bench lines of the same commands: DRAM bytes per ray and issue figures per kernel and
 workload, stamped with the sha of the kernel sources they were taken from (bench.py ignores entries of other code).
 usage: python scripts/make_traffic.py <tag>"""
 import csv
@@ -56,12 +56,13 @@ c2 = line("plain_c2")
 paths = c2["config"]["width"] * c2["config"]["height"] * c2["config"]["spp"]
 rpp = c2["extra"]["rays_per_path"]
 kt = rows("k_trace")
-out = {"_comment": "ncu --set full --clock-control none captures of scripts/gpu_r2q.sh; per-ray figures = sums over the captured launches / "
+out = {"_comment": "ncu --set full --clock-control none captures of scripts/gpu_closing.sh; per-ray figures = sums over the captured launches / "
                    "the rays those launches traced (C2: the five trace launches of one 1080p x 32 spp wave; C3: one 8M-ray launch). "
                    "bench.py multiplies dram_bytes_per_ray by its rays_per_launch and ignores entries whose kernel_sources_sha is not the tree's."}
 out["k_trace_packet_c2"] = entry([l for l in kt if "k_trace_packet" in l["Kernel Name"]], paths, f"profiles/{tag}_k_trace_metrics.md (launch 0)")
-out["k_trace_v6_c2"] = entry([l for l in kt if "k_trace_v6" in l["Kernel Name"]], paths * (rpp - 1), f"profiles/{tag}_k_trace_metrics.md (launches 1-4)")
-out["k_trace_v6_c3_1m"] = entry(rows("c3_k_trace"), line("plain_c3")["config"]["rays"], f"profiles/{tag}_c3_k_trace_metrics.md")
-out["k_trace_v6_c3_10m"] = entry(rows("c3_10m_k_trace"), line("plain_c3_10m")["config"]["rays"], f"profiles/{tag}_c3_10m_k_trace_metrics.md")
+# keys = "<kernel the library names for incoherent launches>_<workload>", as bench.py looks them up
+out["k_trace_v8_c2"] = entry([l for l in kt if "k_trace_v8" in l["Kernel Name"]], paths * (rpp - 1), f"profiles/{tag}_k_trace_metrics.md (launches 1-4)")
+out["k_trace_v8_c3_1m"] = entry(rows("c3_k_trace"), line("plain_c3")["config"]["rays"], f"profiles/{tag}_c3_k_trace_metrics.md")
+out["k_trace_v7_c3_10m"] = entry(rows("c3_10m_k_trace"), line("plain_c3_10m")["config"]["rays"], f"profiles/{tag}_c3_10m_k_trace_metrics.md")
 (REPO / "profiles" / "traffic.json").write_text(json.dumps(out, indent=1) + "\n")
 print(json.dumps({k: {a: (round(b, 3) if isinstance(b, float) else b) for a, b in v.items() if a not in ("capture",)} for k, v in out.items() if k != "_comment"}, indent=1))

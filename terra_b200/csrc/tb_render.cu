@@ -62,7 +62,8 @@ extern "C" void terra_log(const char* fmt, ...);
 #define TB_K_V6_ID            2            // = TB_K_V6 / TB_K_PACKET below (the device is created before the enum is seen)
 #define TB_K_PACKET_ID        3
 #define TB_K_V7_ID            4
-#define TB_V7_MIN_MB          100          // k_trace_v7 by default for scenes whose nodes + triangles exceed this (L2: 126 MB)
+#define TB_V7_MIN_MB          400          // k_trace_v7 by default for scenes whose quantised nodes + triangles exceed this (L2: 126 MB; C3 at
+                                           // 3M triangles = 240 MB: v8 4931 / v7 4689 Mrays/s, at 10M = 800 MB: 3324 / 4290, profiles/r3f, r3e)
 #define TB_K_V8_ID            5
 #define TB_V8_SMEM_DEPTH      40           // k_trace_v8: rows of the shared stack, 4 bytes per entry (deeper trees: + local memory)
 #define TB_LEAN_WORDS         10           // k_trace_v7 / v8: words of per-ray state kept in shared memory behind the stack rows
@@ -1548,8 +1549,8 @@ static void tb_launch_trace_kernel(TbDevice* d, cudaStream_t st, TbTraceArgs& c,
 static int tb_trace_kind(const TbDevice* d, bool coherent) {
     int kind = d->trace_kind;
     if (kind == TB_K_AUTO) kind = coherent ? d->coherent_kind : d->incoherent_kind;
-    // incoherent rays: the 4-wide tree pays when the geometry does not fit L2 and a node fetch is a DRAM round trip
-    // (r2s A/B, 1M / 3M / 10M triangles: -5 % / +6.5 % / +15.5 % against the binary tree)
+    // incoherent rays: the 4-wide tree pays when the geometry is several times L2 and most node fetches are DRAM round
+    // trips (v7 against v8 at 1M / 3M / 10M triangles: -14 % / -5 % / +29 %, profiles/r3e, r3f)
     if (kind == TB_K_AUTO && !coherent)
         kind = d->d_q4nodes && (size_t)d->sc.n_nodes * 32 + (size_t)d->sc.n_tris * 48 >= d->v7_min_bytes ? TB_K_V7 : TB_K_V8;
     if (kind == TB_K_AUTO) kind = TB_K_PACKET;

@@ -18,7 +18,8 @@
 #endif
 
 #ifndef TB_V8_STEPS
-#define TB_V8_STEPS 3           /* node steps per round, see step 6b: 1 / 2 / 3 / 4 = 5360 / 5849 / 5972 / 5977 Mrays/s on C3 1M (profiles/r3a, r3b) */
+#define TB_V8_STEPS 4           /* node steps per round, see step 6b: 1 / 2 / 3 / 4 = 5360 / 5849 / 5972 / 5977 Mrays/s on C3 1M (profiles/r3a, r3b);
+                                   with a leaf parked at every step 4 steps give another 1 % there and on the C2 frame (profiles/r3f) */
 #endif
 
 // Pop: entry [sp - ROW] becomes the lane's node when the lane asked for one (cur == POP). Unconditional read (the row
@@ -180,11 +181,17 @@ __global__ void __launch_bounds__(TB_TRACE_THREADS, TB_V8_CTAS_PER_SM) k_trace_v
             }
             // 6b. further node steps of the round: a round's bookkeeping (park, two ballots, the triangle-round decision, the
             //     exit test: 44 of its ~95 warp instructions, ncu r2y) is paid once for TB_V8_STEPS node steps. A lane whose
-            //     step ended on a leaf sits the rest of the round out (the leaf is parked at the top of the next round);
-            //     every other lane pops if it must and goes on.
+            //     step ended on a leaf parks it if the parking slot is free and pops; with the slot taken it sits the rest
+            //     of the round out (triangle rounds are decided once per round).
 #pragma unroll
             for (int step = 1; step < TB_V8_STEPS; ++step) {
                 const float cull2 = best_t + best_t * 1e-5f;                 // the triangle step may have moved the closest hit
+                {                                                            // park, as at the top of the round
+                    const bool is_leaf = (unsigned)cur > (unsigned)TB_REF_POP;
+                    const bool park = is_leaf && pend == TB_REF_DONE;
+                    pend = park ? cur : pend;
+                    cur = park ? TB_REF_POP : cur;
+                }
                 tb_v8_pop<SPILL, ROW>(cur, sp, smem_end, l_stack);
                 const bool is_node2 = cur >= 0;
                 if (COUNT) {
