@@ -24,6 +24,7 @@ REPO = Path(__file__).resolve().parent.parent
 ORACLE_LIB = REPO / "oracle" / "libterra_oracle.so"
 REFERENCE_LIB = REPO / "oracle" / "_ref" / "libterra_ref.so"
 REFERENCE_ENVLIT_LIB = REPO / "oracle" / "_ref" / "libterra_ref_envlit.so"   # reference with Terra.c:1056 restored ("patched oracle")
+REFERENCE_DEAD_LIB = REPO / "oracle" / "_ref" / "libterra_ref_dead.so"       # the reference's #if 0 GGX / glass presets (ref_dead_presets.c)
 
 
 def _bind_reference_shim(lib, sig):
@@ -269,7 +270,7 @@ def harness_api():
     import types
     ns = types.ModuleType("terra_b200_harness_api")
     ns.__dict__.update({k: v for k, v in vars(api).items() if not k.startswith("__")})
-    for k in ("ORACLE_LIB", "REFERENCE_LIB", "REFERENCE_ENVLIT_LIB", "OracleLib", "OracleScene", "run_bsdf_callbacks",
+    for k in ("ORACLE_LIB", "REFERENCE_LIB", "REFERENCE_ENVLIT_LIB", "REFERENCE_DEAD_LIB", "OracleLib", "OracleScene", "run_bsdf_callbacks",
               "reference_distribution_2d_sample", "BSDF_SAMPLE", "BSDF_PDF", "BSDF_EVAL"):
         setattr(ns, k, globals()[k])
     return ns

@@ -497,7 +497,8 @@ static f3 o_phong_eval(const TerraShadingSurface* s, const f3* wi, const f3* wo)
 /* GGX rough dielectric — dead code in the reference (TerraPresets.c:298-394), old
  * {sample, weight, shade} API. Restated for {sample, pdf, eval}: pdf := weight, eval := shade
  * without its trailing *NoL; the cached half vector is recomputed as normalize(wi + wo).
- * Slots: [0]=albedo [1]=(roughness, metalness, ior). PARITY UNPINNED. */
+ * Slots: [0]=albedo [1]=(roughness, metalness, ior). Pinned against the dead code compiled through
+ * ref_dead_presets.c: directions bit-identical, weight / shade within 1e-4 (the recomputed half vector). */
 static float ggx_chi(float v) { return v <= 0.f ? 0.f : 1.f; }
 static float ggx_G1(f3 v, f3 n, f3 h, float a2) {                                       /* :307-314 */
     float VoH = dot(v, h), VoN = dot(v, n);
@@ -563,7 +564,8 @@ static f3 o_ggx_eval(const TerraShadingSurface* s, const f3* wi, const f3* wo) {
  * fresnel weight in attributes[2].x (the way Phong leaves its lobe pick); pdf returns it; eval =
  * albedo * weight / (n.wi), so that terra_trace's f/pdf*(n.wi) yields the old shade/weight = albedo
  * for both the reflected and the transmitted (n.wi < 0) direction. Slots: [0]=albedo [1].x=ior
- * [2].x=state (reset to its constant 0 at every hit by terra_surface_init). PARITY UNPINNED. */
+ * [2].x=state (reset to its constant 0 at every hit by terra_surface_init). Pinned against the dead code
+ * compiled through ref_dead_presets.c: directions and weights bit-identical, from outside and from inside. */
 static f3 o_glass_sample(const TerraShadingSurface* s, float e1, float e2, float e3, const f3* wo) {
     (void)e1; (void)e2;
     float* state = &((TerraShadingSurface*)s)->attributes[2].x;

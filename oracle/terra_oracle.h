@@ -13,7 +13,9 @@
  * GGX and Glass exist in the reference only as dead code (src/TerraPresets.c:298-465): the
  * oracle restates them for the live {sample,pdf,eval} signature and they run inside the
  * unmodified reference terra_render through the function-pointer table. No reference test or
- * vector pins those two: PARITY UNPINNED for GGX/Glass.
+ * vector covers those two; they are pinned against the dead code itself, compiled through the
+ * adapter of the retired API in oracle/ref_dead_presets.c (tests/golden/bsdf_dead.npz): sampled
+ * directions and glass weights bit-identical, GGX weight / shade within 1e-4 relative.
  *
  * Types come from include/terra_b200.h (layout-identical to the reference's public headers).
  */

@@ -4,7 +4,10 @@
 //                    {sample, weight, shade} API (src/TerraPresets.c:298-394, :396-464). They are
 //                    re-expressed here for the live signature: pdf := weight, eval := shade
 //                    without its trailing *NoL (terra_trace multiplies NoL itself, Terra.c:1078).
-//                    Parity for these two is UNPINNED by any reference test.
+//                    No reference TEST or live code path covers these two; the pin is the dead
+//                    code itself, compiled through an adapter of the retired API (oracle/ref_dead_presets.c):
+//                    these functions reproduce its sampled directions and the glass weights bit for bit and
+//                    the GGX weight / shade to 1e-4 (tests/test_presets_textures.py, tests/golden/bsdf_dead.npz).
 // On the device the functions are dispatched by enum after the material sort; on the host they
 // back the function pointers that terra_bsdf_*_init installs (classification is by pointer
 // identity, include/terra_b200.h) — terra_render never calls the host versions.

@@ -137,6 +137,25 @@ def bsdf_kat_inputs(n=256, seed=9):
     return e, wo.astype(np.float32), nrm.astype(np.float32)
 
 
+# GGX / glass known-answer cases run through the reference's DEAD presets (oracle/ref_dead_presets.c) and through the
+# restatements: attribute slots of include/terra_b200.h, and whether the outgoing direction is flipped to the far side
+# of the normal (glass only: a path leaving the medium, total internal reflection).
+DEAD_PRESET_CASES = {
+    "ggx_metal": ("ggx", [(0.8, 0.6, 0.3), (0.2, 1.0, 1.5)], False),
+    "ggx_plastic": ("ggx", [(0.4, 0.5, 0.6), (0.5, 0.0, 1.5)], False),
+    "ggx_mixed": ("ggx", [(0.4, 0.5, 0.6), (0.35, 0.4, 1.33)], False),
+    "ggx_rough_half_metal": ("ggx", [(0.9, 0.9, 0.9), (0.8, 0.5, 2.0)], False),
+    "glass": ("glass", [(0.98, 0.97, 0.96), (1.5, 0, 0), (0, 0, 0)], False),
+    "glass_from_inside": ("glass", [(0.9, 0.8, 0.7), (1.5, 0, 0), (0, 0, 0)], True),
+    "glass_diamond_from_inside": ("glass", [(1.0, 1.0, 1.0), (2.4, 0, 0), (0, 0, 0)], True),
+}
+
+
+def dead_preset_inputs(flip_wo):
+    e, wo, n = bsdf_kat_inputs(1024, seed=31)
+    return e, (-wo if flip_wo else wo), n
+
+
 class no_commit:
     """Context manager: build scenes through a library's public API but skip terra_scene_commit
     (for the product, commit is the host->device crossing and needs a GPU). The oracle only needs

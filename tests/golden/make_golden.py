@@ -123,6 +123,16 @@ def main():
                                                          [(0.9, 0.9, 0.9), (0.1, 0.1, 0.1), (60, 60, 60), (0, 0, 0)], e, wo, nrm)
     np.savez_compressed(OUT / "bsdf.npz", **out)
 
+    # 4b. GGX / glass known answers from the reference's DEAD presets (TerraPresets.c:13-28, 298-465), compiled through
+    #     the adapter of the retired API in oracle/ref_dead_presets.c (oracle/Makefile, _ref/libterra_ref_dead.so):
+    #     wi.xyz, weight (-> pdf), shade.xyz (-> eval, with the trailing * NoL the retired API carried)
+    dead = C.CDLL(str(api.REFERENCE_DEAD_LIB))
+    out = {}
+    for name, (preset, attrs, flip) in cases.DEAD_PRESET_CASES.items():
+        e, wo, nrm = cases.dead_preset_inputs(flip)
+        out[name] = api.run_bsdf_callbacks(ora, getattr(dead, f"ref_dead_bsdf_{preset}_init"), attrs, e, wo, nrm)[:, :7]
+    np.savez_compressed(OUT / "bsdf_dead.npz", **out)
+
     # 5. textures (Terra.c:368-477): read / point + bilinear sample / lat-long, three address modes
     rng = np.random.default_rng(17)
     tex8 = rng.integers(0, 256, (7, 5, 3), dtype=np.uint8)

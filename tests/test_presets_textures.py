@@ -43,14 +43,65 @@ def test_oracle_presets_match_reference_fixture(api, oracle, case):
 
 @pytest.mark.parametrize("case", list(PRESET_ATTRS))
 def test_product_host_presets_match_oracle(api, prod, oracle, case):
-    """GGX / Glass have no live reference implementation (PARITY UNPINNED): the oracle's
-    restatement of TerraPresets.c:298-464 and the product's are written independently and must agree."""
+    """GGX / Glass have no live reference implementation: the oracle's restatement of
+    TerraPresets.c:298-464 and the product's are written independently and must agree bit for bit (both are held
+    against the reference's dead code below)."""
     e, wo, n = cases.bsdf_kat_inputs()
     a = api.run_bsdf_callbacks(oracle, init_of(oracle, case, "terra_oracle_bsdf_"), PRESET_ATTRS[case], e, wo, n)
     b = api.run_bsdf_callbacks(oracle, init_of(prod, case, "terra_bsdf_"), PRESET_ATTRS[case], e, wo, n)
     if case == "glass":     # state slot differs: oracle keeps it in attributes[2].x, column 7 reads slot 3
         a, b = a[:, :7], b[:, :7]
     assert same(a, b)
+
+
+def _dead_vs_restatement(got, want, wo, n, preset):
+    """got: (wi, pdf, f) of a restatement; want: (wi, weight, shade) of the reference's dead preset."""
+    assert np.array_equal(bits(got[:, :3]), bits(want[:, :3])), "sampled directions differ from the reference's dead code"
+    wi, pdf, f = got[:, :3].astype(np.float64), got[:, 3].astype(np.float64), got[:, 4:7].astype(np.float64)
+    weight, shade = want[:, 3].astype(np.float64), want[:, 4:7].astype(np.float64)
+    nol = (wi * n).sum(1)
+    if preset == "glass":
+        # weight: the fresnel term sample() left behind, bit for bit; shade = albedo * fresnel = eval * (n.wi), the
+        # form the live integrator's f / pdf * (n.wi) turns back into albedo (eval divides by its own float32 n.wi:
+        # 3e-6 relative against the float64 product here at grazing directions)
+        assert np.array_equal(bits(got[:, 3]), bits(want[:, 3]))
+        assert np.allclose(f * nol[:, None], shade, rtol=1e-5, atol=0)
+        return
+    # GGX. The retired API cached the half vector in sample(); the live restatement recomputes it as
+    # normalize(wi + wo) — a few ulp apart, amplified by D's 1 - NoH^2: 6e-5 relative at most on these inputs.
+    # Where sample() clamps HoV to 0 it returns wi = -wo, which has no half vector: the restatement answers pdf = 0,
+    # f = 0 there and the dead code a finite weight with shade = 0 (NoL = 0) — the estimator is 0 on both sides.
+    degenerate = np.linalg.norm(wi + wo, axis=1) == 0
+    assert (pdf[degenerate] == 0).all() and (f[degenerate] == 0).all() and (shade[degenerate] == 0).all()
+    ok = ~degenerate
+    assert np.allclose(pdf[ok], weight[ok], rtol=1e-4, atol=0)
+    assert np.allclose(f[ok] * np.maximum(nol[ok], 0)[:, None], shade[ok], rtol=1e-4, atol=1e-7)   # shade = eval * NoL
+    assert 0.5 < ok.mean()
+
+
+@pytest.mark.parametrize("case", list(cases.DEAD_PRESET_CASES))
+def test_ggx_glass_restatements_match_the_reference_dead_code(api, prod, oracle, case):
+    """The pin of GGX / glass: the reference's own `#if 0` presets (TerraPresets.c:13-28, 298-465), compiled through the
+    adapter of the retired {sample, weight, shade} API in oracle/ref_dead_presets.c, produced tests/golden/bsdf_dead.npz;
+    the oracle's restatement AND the product's host callbacks (tb_bsdf.h, what the kernels compile) must reproduce it:
+    sampled directions and glass weights bit for bit, GGX weight / shade to 1e-4 relative."""
+    preset, attrs, flip = cases.DEAD_PRESET_CASES[case]
+    e, wo, n = cases.dead_preset_inputs(flip)
+    want = golden("bsdf_dead.npz")[case]
+    for lib, prefix in ((oracle, "terra_oracle_bsdf_"), (prod, "terra_bsdf_")):
+        got = api.run_bsdf_callbacks(oracle, getattr(lib, f"{prefix}{preset}_init"), attrs, e, wo, n)
+        _dead_vs_restatement(got, want, wo.astype(np.float64), n.astype(np.float64), preset)
+
+
+def test_dead_code_fixture_is_what_the_compiled_dead_code_gives(api, oracle):
+    """Where the reference was compiled (oracle/_ref): the committed fixture equals a fresh run of the dead presets."""
+    if not api.REFERENCE_DEAD_LIB.exists():
+        pytest.skip("oracle/_ref/libterra_ref_dead.so not built on this box")
+    dead = C.CDLL(str(api.REFERENCE_DEAD_LIB))
+    for case, (preset, attrs, flip) in cases.DEAD_PRESET_CASES.items():
+        e, wo, n = cases.dead_preset_inputs(flip)
+        got = api.run_bsdf_callbacks(oracle, getattr(dead, f"ref_dead_bsdf_{preset}_init"), attrs, e, wo, n)[:, :7]
+        assert same(got, golden("bsdf_dead.npz")[case]), case
 
 
 def test_ggx_energy_and_glass_weights(api, oracle):
