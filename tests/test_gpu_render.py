@@ -69,6 +69,44 @@ def test_device_bsdf_known_answers(api, gpu, oracle, case):
     s.destroy()
 
 
+@pytest.mark.parametrize("case", list(cases.DEAD_PRESET_CASES))
+def test_device_ggx_glass_against_the_reference_dead_code(api, gpu, case):
+    """The device's GGX / glass sample, pdf, eval against the reference's own `#if 0` presets compiled through the adapter
+    of the retired API (oracle/ref_dead_presets.c -> tests/golden/bsdf_dead.npz), with no restatement in between: sampled
+    direction within 1e-5 (device sinf / cosf / atanf against glibc's), glass weight within 1e-6, GGX weight and
+    shade = eval x NoL within 2e-4 relative (1e-4 for the recomputed half vector + the device's libm), the degenerate
+    wi = -wo samples giving 0 on both sides."""
+    preset, a, flip = cases.DEAD_PRESET_CASES[case]
+    e, wo, n = cases.dead_preset_inputs(flip)
+    s = api.Scene(gpu)
+    tri = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 0, 1], [1, 0, 1], [0, 1, 1]]], np.float32)
+    o = s.add_object(tri)
+    if preset == "ggx":
+        s.set_ggx(o, a[0], a[1][0], a[1][1], a[1][2])
+    else:
+        s.set_glass(o, a[0], a[1][0])
+    s.set_options()
+    s.commit()
+    out = np.zeros((len(e), 8), np.float32)
+    gpu.terra_b200_bsdf_kat(s.h, 0, len(e), e.ctypes.data, wo.ctypes.data, n.ctypes.data, out.ctypes.data)
+    s.destroy()
+    want = golden("bsdf_dead.npz")[case].astype(np.float64)
+    got = out[:, :7].astype(np.float64)
+    assert np.isfinite(got).all()
+    assert np.abs(got[:, :3] - want[:, :3]).max() <= 1e-5
+    wi, pdf, f = want[:, :3], got[:, 3], got[:, 4:7]          # the reference's direction: the one both sides mean
+    nol = (wi * n).sum(1)
+    if preset == "glass":
+        assert np.allclose(pdf, want[:, 3], rtol=1e-6, atol=0)
+        assert np.allclose(f * nol[:, None], want[:, 4:7], rtol=2e-5, atol=0)
+        return
+    degenerate = np.linalg.norm(wi + wo, axis=1) < 1e-6
+    assert np.abs(pdf[degenerate]).max(initial=0) <= 1e-6 and np.abs(want[degenerate, 4:7]).max(initial=0) == 0
+    ok = ~degenerate
+    assert np.allclose(pdf[ok], want[ok, 3], rtol=2e-4, atol=1e-7)
+    assert np.allclose(f[ok] * np.maximum(nol[ok], 0)[:, None], want[ok, 4:7], rtol=2e-4, atol=1e-6)
+
+
 # ----------------------------------------------------------------------------- converged images
 def cpu_render(api, scenes, ref_or_none, oracle, build, w, h, spp, seed, nproc):
     """(results) from the CPU renderer: reference tile farm when available, else the oracle."""
