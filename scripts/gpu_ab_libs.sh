@@ -19,6 +19,12 @@ if [ -n "${C2:-}" ]; then
     echo "$n c2 rc=$?"
   done
 fi
+if [ -n "${C5:-}" ]; then
+  for n in "$@"; do
+    TERRA_B200_LIB=$PWD/terra_b200/ab/libterra_b200_$n.so timeout 600 python scripts/ab_trace.py c5 --steps 5 --spp 16 --only "default" >> $OUT/${TAG}_ab_libs.jsonl 2>> $OUT/${TAG}_ab_libs.err
+    echo "$n c5 rc=$?"
+  done
+fi
 python - <<P
 import json
 for l in open("$OUT/${TAG}_ab_libs.jsonl"):
@@ -27,6 +33,6 @@ for l in open("$OUT/${TAG}_ab_libs.jsonl"):
     if d['ab'] == 'c3':
         print(f"{b:20s} {d['variant'][:24]:24s} {d['tris']:>9d} {d['mrays_per_s']:8.1f} sum={d.get('hit_checksum')} nodes={d['nodes_per_ray']:.2f}")
     else:
-        print(f"{b:20s} {d['ab']} {d['variant'][:24]:24s} {d['mpaths_per_s']:8.1f} Mpaths/s trace {d['trace_ms_per_frame']:.2f} ms")
+        print(f"{b:20s} {d['ab']} {d['variant'][:24]:24s} {d['mpaths_per_s']:8.1f} Mpaths/s frame {d['ms']:.2f} ms trace {d['trace_ms_per_frame']:.2f} ms rest {d['ms'] - d['trace_ms_per_frame']:.2f} ms")
 P
 tail -3 $OUT/${TAG}_ab_libs.err
