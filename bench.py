@@ -70,7 +70,7 @@ def line_config(args, wl, world):
     return {"workload": wl["name"], "width": args.width or wl["w"], "height": args.height or wl["h"], "spp": args.spp or wl["spp"],
             "bounces": wl["bounces"], "integrator": INTEGRATORS[args.integrator], "split": args.split if world > 1 else "none",
             "bvh": args.bvh, "ggx_glass": "restated from the reference's dead code (TerraPresets.c:298-465) and pinned against that code compiled through an adapter of its retired API (tests/golden/bsdf_dead.npz); no live reference path renders them (SURVEY Q5)",
-            "l2": "flushed between timed iterations (256 MiB write); path-state waves (up to 64M slots x 80 B) exceed L2"}
+            "l2": "flushed between timed iterations (256 MiB write); path-state waves (up to 128M slots x 80 B) exceed L2"}
 
 
 def build_scene(lib, scenes, workload, spp, integrator=0):

@@ -1422,9 +1422,13 @@ __global__ void k_counters(int* c, int mode, int value) {
     }
 }
 
+// Path slots per wave. A wave's bounce launches shrink (C2: 100 % -> 30 % -> 12 % -> 5 % -> 2 % of its paths) and every
+// launch ends in a tail of half-empty warps, so larger waves mean fewer, longer launches: 64M / 128M / 256M slots =
+// 5947 / 6059 / 6075 Mpaths/s on the C2 frame (profiles/r3n). 128M slots = 10 GB of path state for the simple integrator,
+// 24 GB for direct / MIS; a render only reserves what its region x samples need.
 static size_t tb_batch_capacity() {
     const char* e = getenv("TERRA_B200_BATCH");
-    size_t cap = e ? (size_t)strtoull(e, NULL, 10) : ((size_t)1 << 26);
+    size_t cap = e ? (size_t)strtoull(e, NULL, 10) : ((size_t)1 << 27);
     if (cap < 1024) cap = 1024;
     if (cap > ((size_t)1 << 28)) cap = (size_t)1 << 28;
     return cap;

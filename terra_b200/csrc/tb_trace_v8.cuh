@@ -10,6 +10,17 @@
 // pointer instead of the slot (a ray ends by popping the sentinel below entry 0: sp == bottom - ROW; an idle lane
 // has sp == bottom).
 //
+// With the eighth CTA in (64 registers, no spills), three more changes against k_trace_v6, each measured on the B200
+// with the hit records compared bit for bit (experiments/README.md, profiles/r2_summary.md section 6):
+//   - a stack entry is the 4-byte child reference alone: half the shared memory per row (L1 keeps ~100 KB beside
+//     8 CTAs' stacks), no entry distance — the ~5 % of entries that the closest hit has culled by the time they are
+//     popped are fetched and fail both box tests;
+//   - a round's bookkeeping (park, two ballots, triangle-round decision, exit test: 44 of ~95 warp instructions) is
+//     paid once per TB_V8_STEPS node steps (step 6b);
+//   - refills take queue positions from a block the warp reserved one refill earlier (tb_refill_position): no atomic
+//     round trip on the refill's critical path.
+// C3 1M: 4.95 (v6) -> 6.2 Grays/s, 0.51 of the probed L2 stream peak in algorithmic bytes.
+//
 // Same answer as every other trace kernel: same nodes, same tb_triangle, equal t -> smaller rank.
 #pragma once
 
